@@ -1,0 +1,142 @@
+"""Regenerates the committed golden fixtures in this directory.
+
+Run ONLY in the build container (needs /root/reference for the upstream cross
+check):   python tests/golden/make_golden.py
+
+Fixtures
+  oracle_v{1,2,3}_{A,B}.npz  mel + fp64-oracle audio (stored fp32) + a few interior taps'
+                              checksums, for synthetic weight variants A/B at B=2, T=9.
+                              Weights are NOT stored: they are re-derived from the seed by
+                              neuraltexttospeech_b200.synthetic.synthetic_weights.
+  upstream_v{1,2,3}.npz       audio produced by the *importable upstream PyTorch generator*
+                              that the reference vendors (FastSpeech2_TF/FastSpeech2/hifigan/
+                              models.py:112-165 for ResBlock1 configs; NVIDIA DLE
+                              PyTorch/SpeechSynthesis/HiFi-GAN/hifigan/models.py for the
+                              ResBlock2 config) on the same folded weights.  The oracle in
+                              compat="upstream" mode must reproduce it (tests/test_oracle.py).
+                              This pins conv / transposed-conv placement, the weight-norm
+                              fold axes, the MRF order and the residual wiring.  The two
+                              reference quirks (causal k=3 convs, slope 0.3) are NOT covered
+                              by any runnable reference code here: "parity unpinned" for them.
+"""
+import os
+import sys
+import types
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+
+from neuraltexttospeech_b200.hparams import HParams            # noqa: E402
+from neuraltexttospeech_b200.synthetic import synthetic_mel, synthetic_weights  # noqa: E402
+from oracle import hifigan_oracle as O                          # noqa: E402
+
+REF = "/root/reference"
+
+
+def _upstream_generator(h):
+    """Build the vendored upstream torch generator with weight norm removed."""
+    import torch
+    if h.resblock == "1":
+        sys.path.insert(0, os.path.join(REF, "FastSpeech2_TF/FastSpeech2"))
+        # the package __init__ pulls the whole FastSpeech2 tree; load the module file directly
+        import importlib.util
+        spec = importlib.util.spec_from_file_location(
+            "upstream_hifigan_models", os.path.join(REF, "FastSpeech2_TF/FastSpeech2/hifigan/models.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        gen = mod.Generator(h)
+    else:
+        base = os.path.join(REF, "FastPitch_TF/DeepLearningExamples/PyTorch/SpeechSynthesis/HiFi-GAN")
+        # DLE's module imports common.{monkey_patch,stft,utils}; stub what is not arithmetic
+        common = types.ModuleType("common")
+        common.monkey_patch = types.ModuleType("common.monkey_patch")
+        stft = types.ModuleType("common.stft"); stft.STFT = object
+        utils = types.ModuleType("common.utils")
+
+        class AttrDict(dict):
+            def __init__(self, *a, **k):
+                super().__init__(*a, **k); self.__dict__ = self
+
+        utils.AttrDict = AttrDict
+        utils.init_weights = lambda m, mean=0.0, std=0.01: None
+        utils.get_padding = lambda k, d=1: int((k * d - d) / 2)
+        sys.modules.update({"common": common, "common.monkey_patch": common.monkey_patch,
+                            "common.stft": stft, "common.utils": utils})
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("dle_hifigan_models", os.path.join(base, "hifigan/models.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        gen = mod.Generator(dict(vars(h)))
+        for group in gen.resblocks:          # DLE's ResBlock2 lists lrelu_slope in __constants__
+            for rb in group:                 # but never assigns it; give it the module constant
+                if not hasattr(rb, "lrelu_slope"):
+                    rb.lrelu_slope = mod.LRELU_SLOPE
+    gen.remove_weight_norm()
+    return gen.eval()
+
+
+def _load_folded(gen, h, weights):
+    import torch
+    folded = O.fold_all(h, weights, np.float64)
+
+    def put(module, name, kind):
+        w, b = folded[name]
+        wt = torch.from_numpy(np.ascontiguousarray(np.transpose(w, (2, 1, 0)))).float()
+        assert tuple(module.weight.shape) == tuple(wt.shape), (name, module.weight.shape, wt.shape)
+        module.weight.data.copy_(wt)
+        module.bias.data.copy_(torch.from_numpy(b).float())
+
+    put(gen.conv_pre, "conv_pre", "conv")
+    put(gen.conv_post, "conv_post", "conv")
+    for i, up in enumerate(gen.ups):
+        put(up, f"ups.{i}", "convT")
+    blocks = list(gen.resblocks)
+    if blocks and isinstance(blocks[0], torch.nn.Sequential):      # DLE groups them per stage
+        blocks = [rb for group in blocks for rb in group]
+    for n, rb in enumerate(blocks):
+        if h.resblock == "1":
+            for m in range(3):
+                put(rb.convs1[m], f"resblocks.{n}.convs1.{m}", "conv")
+                put(rb.convs2[m], f"resblocks.{n}.convs2.{m}", "conv")
+        else:
+            for m in range(2):
+                put(rb.convs[m], f"resblocks.{n}.convs.{m}", "conv")
+
+
+def main():
+    import torch
+    torch.manual_seed(0)
+    B, T = 2, 9
+    for v in "123":
+        h = HParams.builtin(v)
+        mel = synthetic_mel(B, T, h.num_mels, seed=1234 + int(v))
+        for variant in "AB":
+            w = synthetic_weights(h, variant)
+            taps = {}
+            audio = O.generator_forward(h, w, mel, "numpy64", "reference", taps=taps)
+            np.savez_compressed(
+                os.path.join(HERE, f"oracle_v{v}_{variant}.npz"),
+                mel=mel, audio=audio.astype(np.float32),
+                conv_pre_sum=np.float64(taps["conv_pre"].sum()),
+                stage0_sum=np.float64(taps["stage.0"].sum()),
+                stage_last_abs_sum=np.float64(np.abs(taps[f"stage.{len(h.upsample_rates) - 1}"]).sum()))
+        # upstream cross-check fixture (variant B: non-trivial g and b)
+        w = synthetic_weights(h, "B")
+        if os.path.isdir(REF):
+            gen = _upstream_generator(h)
+            _load_folded(gen, h, w)
+            with torch.no_grad():
+                y = gen(torch.from_numpy(mel).permute(0, 2, 1).contiguous())   # NCT in, [B,1,L] out
+            y = y.permute(0, 2, 1).contiguous().numpy()
+            mine = O.generator_forward(h, w, mel, "numpy64", "upstream")
+            err = float(np.abs(mine - y).max())
+            print(f"v{v}: upstream torch vs oracle(compat=upstream) max-abs {err:.3e}; amp {np.abs(y).max():.3f}")
+            assert err < 2e-5, err
+            np.savez_compressed(os.path.join(HERE, f"upstream_v{v}.npz"), mel=mel, audio=y.astype(np.float32))
+
+
+if __name__ == "__main__":
+    main()
