@@ -1,0 +1,138 @@
+/*
+ * hifigan_b200.h -- C ABI of libhifigan_b200.so
+ *
+ * Drop-in boundary for ONE path of dmmagdal/NeuralTextToSpeech: the HiFi-GAN
+ * generator forward pass, `Generator.call(mel) -> audio`
+ * (reference HiFiGAN_TF/model.py:115-173).  The reference has no FFI of its own
+ * (the boundary there is the Python class `Generator(keras.Model)`); these entry
+ * points are what a ctypes binding of that class needs -- see INTEGRATION.md for
+ * the reference-side stub.  Plain pointers and sizes only, no torch/TF types.
+ *
+ * All functions return 0 on success or a negative hfg_status; the message is
+ * available from hfg_last_error().  Nothing here prints or exits.
+ * A handle is bound to one CUDA device and is not thread-safe (one handle per
+ * GPU / stream).  hfg_forward is asynchronous on `stream` and performs no
+ * allocation; it fails (never falls back to a CPU path) if no CUDA device exists.
+ */
+#ifndef HIFIGAN_B200_H_
+#define HIFIGAN_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HFG_MAX_UPSAMPLES 8
+#define HFG_MAX_KERNELS 8
+#define HFG_MAX_DILATIONS 4
+
+typedef enum {
+  HFG_OK = 0,
+  HFG_ERR_INVALID = -1,   /* bad argument / config / shape  -> ValueError in the shim   */
+  HFG_ERR_STATE = -2,     /* call order (weights missing, not finalised ...)           */
+  HFG_ERR_CUDA = -3,      /* CUDA runtime error                     -> RuntimeError     */
+  HFG_ERR_NOMEM = -4,     /* workspace too small / allocation failed                   */
+  HFG_ERR_UNSUPPORTED = -5
+} hfg_status;
+
+/* Arithmetic of the forward pass (hfg_finalize_weights). */
+typedef enum {
+  HFG_PRECISION_FP32 = 0, /* fp32 FFMA validation mode: <=1e-5 of the fp32 reference    */
+  HFG_PRECISION_FP16 = 1, /* tcgen05 kind::f16, fp16 operands+storage, fp32 accumulate  */
+  HFG_PRECISION_BF16 = 2  /* tcgen05 kind::f16, bf16 operands+storage, fp32 accumulate  */
+} hfg_precision;
+
+/* POD mirror of the hparams fields Generator.__init__ reads
+ * (reference HiFiGAN_TF/model.py:119-143, HiFiGAN_TF/hparams.py:9-41) + num_mels
+ * (the reference lets Keras infer it at first call, model.py:121-125). */
+typedef struct {
+  int32_t num_mels;                                   /* config_v*.json "num_mels" (80)            */
+  int32_t upsample_initial_channel;                   /* 512 / 128 / 256                           */
+  int32_t resblock;                                   /* 1 -> ResBlock1, 2 -> ResBlock2 (model.py:126) */
+  int32_t num_upsamples;
+  int32_t upsample_rates[HFG_MAX_UPSAMPLES];
+  int32_t upsample_kernel_sizes[HFG_MAX_UPSAMPLES];
+  int32_t num_kernels;
+  int32_t resblock_kernel_sizes[HFG_MAX_KERNELS];
+  int32_t num_dilations[HFG_MAX_KERNELS];
+  int32_t resblock_dilation_sizes[HFG_MAX_KERNELS][HFG_MAX_DILATIONS];
+  int32_t compat;  /* 0 = reference semantics (causal k=3,d=1 convs via get_padding,
+                        HiFiGAN_TF/utils.py:29-37; final LeakyReLU slope 0.3, model.py:152);
+                      1 = upstream jik876/hifi-gan semantics (symmetric pads, slope 0.01)  */
+} hfg_config;
+
+typedef struct hfg_ctx* hfg_handle;
+
+/* Replaces Generator.__init__ (model.py:116-152).  `device` = CUDA ordinal. */
+int hfg_create(const hfg_config* cfg, int device, hfg_handle* out);
+
+/* Replaces the Keras variables of each tfa.layers.WeightNormalization wrapper
+ * (model.py:25-66,88-101,121,131,145): name is "<layer>.v" | "<layer>.g" | "<layer>.b"
+ * with <layer> in {conv_pre, ups.<i>, resblocks.<n>.convs1.<m>, resblocks.<n>.convs2.<m>,
+ * resblocks.<n>.convs.<m>, conv_post}; `host` is fp32 in Keras layout
+ * (v: Conv1D [k,Cin,Cout], Conv1DTranspose [k,Cout,Cin]; g: last axis of v; b: [Cout]). */
+int hfg_set_weight(hfg_handle h, const char* name, const float* host, const int64_t* shape, int ndim);
+
+/* Folds weight norm (kernel = g * v / max(||v||, 1e-6), norm over all axes but the last),
+ * repacks for the kernels and uploads.  precision: hfg_precision. */
+int hfg_finalize_weights(hfg_handle h, int precision);
+
+/* Output samples per mel frame (prod(upsample_rates)). */
+int hfg_total_upsample(hfg_handle h, int* out);
+
+/* Device scratch needed by hfg_forward for a [B,T,num_mels] batch. */
+int hfg_workspace_bytes(hfg_handle h, int B, int T, size_t* out);
+
+/* Replaces Generator.call (model.py:155-173).
+ *   mel_dev   : device, fp32, [B, T, num_mels] C-contiguous (channels-last, like the reference)
+ *   audio_dev : device, fp32, [B, T*prod(rates), 1]
+ *   workspace : device, >= hfg_workspace_bytes, 256-byte aligned; caller-owned
+ *   stream    : cudaStream_t (NULL = legacy default stream) */
+int hfg_forward(hfg_handle h, const float* mel_dev, int B, int T, float* audio_dev,
+                void* workspace_dev, size_t workspace_bytes, void* stream);
+
+/* Same call with HOST buffers (what a numpy caller of Generator.call uses): copies mel to the
+ * device, runs hfg_forward in micro-batches on an internal stream and workspace (grown on demand,
+ * kept in the handle), copies audio back and synchronises.  Pinned host memory makes the copies
+ * asynchronous; pageable memory works too. */
+int hfg_forward_host(hfg_handle h, const float* mel_host, int B, int T, float* audio_host);
+
+/* Utterances per micro-batch used by hfg_forward_host (default 16); 0 = whole batch. */
+int hfg_set_option(hfg_handle h, const char* key, long long value);
+
+/* Kernels launched by the last hfg_forward / hfg_forward_host on this handle. */
+int hfg_last_launch_count(hfg_handle h, long long* out);
+
+/* Per-stage device time of the last forward when option "stage_timing" is 1:
+ * out[0]=conv_pre, out[1+i]=stage i (ups[i] + its resblocks), out[1+n]=conv_post. Returns count via n. */
+int hfg_stage_times_ms(hfg_handle h, float* out, int* n);
+
+/* Operator-level entry: ONE tapped convolution (the building block of every layer above),
+ *   out[b, q*out_stride + out_off, co] = epi(bias[co] + sum_j sum_ci lrelu(x[b, q + tap_off[j], ci], in_slope) * w[j][ci][co])
+ * A dilated Conv1D (reference model.py:26-66) is out_stride=1, tap_off[j] = j*d - pad_left; one phase p of a
+ * Conv1DTranspose (model.py:131-136) is out_stride=u, out_off=p.  act: 0 fp32, 1 fp16, 2 bf16 activations;
+ * use_umma: 1 = tcgen05 kernel, 0 = direct FFMA kernel; w_host fp32 [ntaps][c_in][c_out]; res/acc may be NULL;
+ * mrf_mode 0 none, 1 acc=val, 2 acc+=val, 3 out=(acc+val)/mrf_div.  Synchronous; for parity tests. */
+int hfg_op_tapped_conv(int act, int use_umma, const void* x_dev, int B, int x_rows, int c_in,
+                       const float* w_host, const float* bias_host, int c_out, int ntaps, const int* tap_off,
+                       int out_stride, int out_off, float in_slope, const void* res_dev, float* acc_dev,
+                       int mrf_mode, float mrf_div, void* out_dev, void* stream);
+
+/* Pinned host memory helpers for callers without a CUDA runtime binding of their own. */
+int hfg_host_alloc(void** out, size_t bytes);
+int hfg_host_free(void* p);
+
+/* Message of the last error on this handle (or of the last failed hfg_create when h is NULL). */
+const char* hfg_last_error(hfg_handle h);
+
+/* Library/ABI version: major*1000 + minor. */
+int hfg_version(void);
+
+void hfg_destroy(hfg_handle h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HIFIGAN_B200_H_ */

@@ -1,0 +1,643 @@
+// Host-side engine behind the C ABI (include/hifigan_b200.h).
+//
+// Mirrors, as plain C++ control flow, what the reference builds and runs with Keras layers:
+//   Generator.__init__   reference HiFiGAN_TF/model.py:116-152  -> build_layers()
+//   Generator.call       reference HiFiGAN_TF/model.py:155-173  -> run_forward()
+//   ResBlock1/2.call     reference HiFiGAN_TF/model.py:71-80, 106-112
+//   get_padding          reference HiFiGAN_TF/utils.py:29-37    -> conv_pad_left()
+//   tfa WeightNormalization(data_init=False) (call sites model.py:25-66,88-101,121,131,145)
+//                                                               -> fold_weight_norm()
+// There is no CPU compute path here: every arithmetic op is a CUDA kernel launch.
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/hifigan_b200.h"
+#include "kernels.cuh"
+
+using namespace hfg;
+
+namespace {
+
+struct Phase {            // one output phase of a transposed conv (or the single "phase" of a conv)
+  int ntaps = 0;
+  int tap_off[kMaxTaps];
+  size_t w32_off = 0;     // element offset into d_w32
+  size_t wpk_off = 0;     // byte offset into d_wpk
+};
+
+struct Layer {
+  std::string name;
+  bool transposed = false;
+  int k = 0, dil = 1, stride = 1, cin = 0, cout = 0;
+  int cin_pad = 0;        // channel count the kernels see (conv_pre pads num_mels up for the MMA path)
+  std::vector<float> v, g, b;
+  bool has_v = false, has_g = false, has_b = false;
+  std::vector<Phase> phases;
+  float* d_w32 = nullptr;
+  float* d_bias = nullptr;
+  void* d_wpk = nullptr;
+  bool use_umma = false;
+};
+
+thread_local std::string g_create_error;
+
+}  // namespace
+
+struct hfg_ctx {
+  hfg_config cfg{};
+  int device = 0;
+  std::vector<Layer> layers;
+  std::map<std::string, int> index;
+  int total_up = 1;
+  bool finalized = false;
+  int precision = HFG_PRECISION_FP32;
+  ActType act = ACT_F32;
+  std::string err;
+  long long launches = 0;
+  bool stage_timing = false;
+  std::vector<cudaEvent_t> events;
+  std::vector<float> stage_ms;
+  int n_stage_marks = 0;
+  // host-buffer path
+  int micro_batch = 16;
+  cudaStream_t stream = nullptr;
+  void* ws = nullptr; size_t ws_bytes = 0;
+  float* d_mel = nullptr; size_t d_mel_bytes = 0;
+  float* d_audio = nullptr; size_t d_audio_bytes = 0;
+  bool force_ffma = false;
+};
+
+namespace {
+
+int fail(hfg_ctx* h, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+  if (h) h->err = buf; else g_create_error = buf;
+  return code;
+}
+
+#define CUDA_TRY(h, expr)                                                                   \
+  do { cudaError_t e__ = (expr);                                                            \
+       if (e__ != cudaSuccess) return fail(h, HFG_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e__)); } while (0)
+
+size_t act_bytes(ActType a) { return a == ACT_F32 ? 4 : 2; }
+size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// reference HiFiGAN_TF/utils.py:29-37: int pad -> "valid"/"causal"/"same"; returns left zero padding.
+// compat=1 (upstream) pads symmetrically.
+int conv_pad_left(int k, int d, int compat, bool* ok) {
+  const int span = d * (k - 1);
+  *ok = true;
+  if (compat == 1) return span / 2;
+  const int pad = (int)((k * d - d) / 2);
+  if (pad == 0) { *ok = (span == 0); return 0; }   // "valid": only length-preserving for k == 1
+  if (pad == 1) return span;                       // "causal": all padding on the left
+  return span / 2;                                 // "same"
+}
+
+void build_layers(hfg_ctx* h) {
+  const hfg_config& c = h->cfg;
+  auto add = [&](const std::string& name, bool tr, int k, int d, int s, int cin, int cout) {
+    Layer L; L.name = name; L.transposed = tr; L.k = k; L.dil = d; L.stride = s; L.cin = cin; L.cout = cout;
+    L.cin_pad = cin;
+    h->index[name] = (int)h->layers.size();
+    h->layers.push_back(std::move(L));
+  };
+  const int c0 = c.upsample_initial_channel;
+  add("conv_pre", false, 7, 1, 1, c.num_mels, c0);
+  int cprev = c0;
+  h->total_up = 1;
+  for (int i = 0; i < c.num_upsamples; ++i) {
+    const int ch = c0 >> (i + 1);
+    add("ups." + std::to_string(i), true, c.upsample_kernel_sizes[i], 1, c.upsample_rates[i], cprev, ch);
+    h->total_up *= c.upsample_rates[i];
+    for (int j = 0; j < c.num_kernels; ++j) {
+      const int n = i * c.num_kernels + j;
+      for (int m = 0; m < c.num_dilations[j]; ++m) {
+        const std::string base = "resblocks." + std::to_string(n);
+        if (c.resblock == 1) {
+          add(base + ".convs1." + std::to_string(m), false, c.resblock_kernel_sizes[j], c.resblock_dilation_sizes[j][m], 1, ch, ch);
+          add(base + ".convs2." + std::to_string(m), false, c.resblock_kernel_sizes[j], 1, 1, ch, ch);
+        } else {
+          add(base + ".convs." + std::to_string(m), false, c.resblock_kernel_sizes[j], c.resblock_dilation_sizes[j][m], 1, ch, ch);
+        }
+      }
+    }
+    cprev = ch;
+  }
+  add("conv_post", false, 7, 1, 1, cprev, 1);
+}
+
+int validate_config(const hfg_config& c) {
+  if (c.num_mels <= 0 || c.num_mels % 4) return fail(nullptr, HFG_ERR_INVALID, "num_mels must be a positive multiple of 4 (got %d)", c.num_mels);
+  if (c.resblock != 1 && c.resblock != 2) return fail(nullptr, HFG_ERR_INVALID, "resblock must be 1 or 2 (got %d)", c.resblock);
+  if (c.num_upsamples < 1 || c.num_upsamples > HFG_MAX_UPSAMPLES) return fail(nullptr, HFG_ERR_INVALID, "num_upsamples out of range: %d", c.num_upsamples);
+  if (c.num_kernels < 1 || c.num_kernels > HFG_MAX_KERNELS) return fail(nullptr, HFG_ERR_INVALID, "num_kernels out of range: %d", c.num_kernels);
+  if (c.compat != 0 && c.compat != 1) return fail(nullptr, HFG_ERR_INVALID, "compat must be 0 or 1");
+  const int c0 = c.upsample_initial_channel;
+  if (c0 <= 0 || (c0 >> c.num_upsamples) < 8 || ((c0 >> c.num_upsamples) << c.num_upsamples) != c0)
+    return fail(nullptr, HFG_ERR_INVALID, "upsample_initial_channel=%d must be divisible by 2^num_upsamples with >=8 channels left", c0);
+  for (int i = 0; i < c.num_upsamples; ++i) {
+    const int u = c.upsample_rates[i], k = c.upsample_kernel_sizes[i];
+    if (u < 1 || k < u || (k + u - 1) / u > kMaxTaps) return fail(nullptr, HFG_ERR_INVALID, "unsupported upsample rate/kernel %d/%d", u, k);
+  }
+  for (int j = 0; j < c.num_kernels; ++j) {
+    const int k = c.resblock_kernel_sizes[j];
+    if (k < 1 || k > kMaxTaps) return fail(nullptr, HFG_ERR_INVALID, "unsupported resblock kernel size %d", k);
+    if (c.num_dilations[j] < 1 || c.num_dilations[j] > HFG_MAX_DILATIONS) return fail(nullptr, HFG_ERR_INVALID, "bad dilation count");
+    for (int m = 0; m < c.num_dilations[j]; ++m) {
+      bool ok;
+      if (c.resblock_dilation_sizes[j][m] < 1) return fail(nullptr, HFG_ERR_INVALID, "dilation must be >= 1");
+      conv_pad_left(k, c.resblock_dilation_sizes[j][m], c.compat, &ok);
+      if (!ok) return fail(nullptr, HFG_ERR_INVALID, "kernel %d / dilation %d gives a 'valid' (length-changing) conv; the reference's residual add would fail too", k, c.resblock_dilation_sizes[j][m]);
+      conv_pad_left(k, 1, c.compat, &ok);
+      if (!ok) return fail(nullptr, HFG_ERR_INVALID, "kernel %d gives a 'valid' (length-changing) conv", k);
+    }
+  }
+  return HFG_OK;
+}
+
+// tfa WeightNormalization: kernel = l2_normalize(v, axes != last) * g; l2_normalize uses
+// v * rsqrt(max(sum v^2, 1e-12)).  Returns canonical [k][cin][cout] fp32.
+std::vector<float> fold_weight_norm(const Layer& L) {
+  const int k = L.k, last = L.transposed ? L.cin : L.cout, inner = L.transposed ? L.cout : L.cin;
+  std::vector<double> sq(last, 0.0);
+  for (int j = 0; j < k; ++j)
+    for (int a = 0; a < inner; ++a)
+      for (int z = 0; z < last; ++z) { const double t = L.v[((size_t)j * inner + a) * last + z]; sq[z] += t * t; }
+  std::vector<float> w((size_t)k * L.cin * L.cout);
+  for (int j = 0; j < k; ++j)
+    for (int a = 0; a < inner; ++a)
+      for (int z = 0; z < last; ++z) {
+        const double val = (double)L.v[((size_t)j * inner + a) * last + z] / std::sqrt(std::max(sq[z], 1e-12)) * (double)L.g[z];
+        const int ci = L.transposed ? z : a, co = L.transposed ? a : z;
+        w[((size_t)j * L.cin + ci) * L.cout + co] = (float)val;
+      }
+  return w;
+}
+
+void free_layer_device(Layer& L) {
+  if (L.d_w32) cudaFree(L.d_w32);
+  if (L.d_bias) cudaFree(L.d_bias);
+  if (L.d_wpk) cudaFree(L.d_wpk);
+  L.d_w32 = nullptr; L.d_bias = nullptr; L.d_wpk = nullptr;
+}
+
+struct Sizes {
+  size_t max_act_elems = 0;   // largest [B, L, C] activation
+  size_t mel_pad_elems = 0;
+};
+
+Sizes compute_sizes(const hfg_ctx* h, int B, int T) {
+  Sizes s;
+  const hfg_config& c = h->cfg;
+  size_t L = (size_t)T;
+  s.max_act_elems = (size_t)B * L * c.upsample_initial_channel;
+  for (int i = 0; i < c.num_upsamples; ++i) {
+    L *= c.upsample_rates[i];
+    const size_t e = (size_t)B * L * (c.upsample_initial_channel >> (i + 1));
+    if (e > s.max_act_elems) s.max_act_elems = e;
+  }
+  s.mel_pad_elems = (size_t)B * T * h->layers[0].cin_pad;
+  return s;
+}
+
+struct Workspace { char* U; char* P; char* Q; char* T; float* ACC; char* MEL; };
+
+size_t workspace_layout(const hfg_ctx* h, int B, int T, char* base, Workspace* w) {
+  const Sizes s = compute_sizes(h, B, T);
+  const size_t ab = align_up(s.max_act_elems * act_bytes(h->act), 256);
+  const size_t accb = align_up(s.max_act_elems * sizeof(float), 256);
+  const size_t melb = align_up(s.mel_pad_elems * act_bytes(h->act), 256);
+  size_t off = 0;
+  auto take = [&](size_t n) { char* p = base ? base + off : nullptr; off += n; return p; };
+  char* U = take(ab); char* P = take(ab); char* Q = take(ab); char* Tt = take(ab);
+  float* ACC = (float*)take(accb); char* MEL = take(melb);
+  if (w) { w->U = U; w->P = P; w->Q = Q; w->T = Tt; w->ACC = ACC; w->MEL = MEL; }
+  return off;
+}
+
+struct Runner {
+  hfg_ctx* h;
+  cudaStream_t s;
+  int B;
+  cudaError_t status = cudaSuccess;
+
+  void conv(const Layer& L, const void* x, int x_rows, void* out, float in_slope, const void* res,
+            float* acc, int mrf_mode) {
+    if (status != cudaSuccess) return;
+    const int u = L.transposed ? L.stride : 1;
+    for (int p = 0; p < (int)L.phases.size(); ++p) {
+      const Phase& ph = L.phases[p];
+      ConvArgs a{};
+      a.x = x; a.bias = L.d_bias; a.out = out; a.res = res; a.acc = acc;
+      a.B = B; a.x_rows = x_rows; a.n_q = x_rows; a.out_rows = x_rows * u;
+      a.c_in = L.cin_pad; a.c_out = L.cout; a.ntaps = ph.ntaps;
+      for (int j = 0; j < ph.ntaps; ++j) a.tap_off[j] = ph.tap_off[j];
+      a.out_stride = u; a.out_off = p; a.in_slope = in_slope; a.mrf_mode = mrf_mode;
+      a.mrf_div = (float)h->cfg.num_kernels;
+      if (L.use_umma) {
+        a.w = (const char*)L.d_wpk + ph.wpk_off;
+        status = launch_conv_umma(a, h->act, s);
+      } else {
+        a.w = L.d_w32 + ph.w32_off;
+        status = launch_conv_ffma(a, h->act, s);
+      }
+      h->launches++;
+      if (status != cudaSuccess) return;
+    }
+  }
+};
+
+int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev, char* ws, cudaStream_t s) {
+  const hfg_config& c = h->cfg;
+  Workspace w;
+  workspace_layout(h, B, T, ws, &w);
+  Runner r{h, s, B};
+  const float kSlope = 0.1f;                                    // LRELU_SLOPE, reference model.py:14
+  const float kFinalSlope = c.compat == 0 ? 0.3f : 0.01f;       // keras LeakyReLU() default, model.py:152
+  int mark = 0;
+  auto stamp = [&]() { if (h->stage_timing && mark < (int)h->events.size()) cudaEventRecord(h->events[mark++], s); };
+  stamp();
+
+  // conv_pre (model.py:156)
+  const Layer& pre = h->layers[h->index["conv_pre"]];
+  const void* x0 = mel_dev;
+  if (h->act != ACT_F32 || pre.cin_pad != pre.cin) {
+    cudaError_t e = launch_cast_pad(mel_dev, w.MEL, (long long)B * T, pre.cin, pre.cin_pad, h->act, s);
+    h->launches++;
+    if (e != cudaSuccess) return fail(h, HFG_ERR_CUDA, "cast_pad launch failed: %s", cudaGetErrorString(e));
+    x0 = w.MEL;
+  }
+  r.conv(pre, x0, T, w.P, 1.0f, nullptr, nullptr, MRF_NONE);
+  stamp();
+
+  char* x = w.P;          // current stage input
+  int L = T;
+  for (int i = 0; i < c.num_upsamples; ++i) {
+    const Layer& up = h->layers[h->index["ups." + std::to_string(i)]];
+    r.conv(up, x, L, w.U, kSlope, nullptr, nullptr, MRF_NONE);   // model.py:159-160
+    L *= up.stride;
+    char* next_x = nullptr;
+    for (int j = 0; j < c.num_kernels; ++j) {                   // model.py:162-166
+      const int n = i * c.num_kernels + j;
+      const int nd = c.num_dilations[j];
+      const int mrf_last = c.num_kernels == 1 ? MRF_NONE : (j == 0 ? MRF_FIRST : (j == c.num_kernels - 1 ? MRF_FINAL : MRF_ADD));
+      const char* rcur = w.U;
+      for (int m = 0; m < nd; ++m) {
+        const bool last = (m == nd - 1);
+        char* rnext = (rcur == w.P) ? w.Q : w.P;
+        const int mode = last ? mrf_last : MRF_NONE;
+        if (last && (mode == MRF_FINAL || mode == MRF_NONE)) next_x = rnext;
+        const std::string base = "resblocks." + std::to_string(n);
+        if (c.resblock == 1) {                                   // ResBlock1.call model.py:71-80
+          const Layer& c1 = h->layers[h->index[base + ".convs1." + std::to_string(m)]];
+          const Layer& c2 = h->layers[h->index[base + ".convs2." + std::to_string(m)]];
+          r.conv(c1, rcur, L, w.T, kSlope, nullptr, nullptr, MRF_NONE);
+          r.conv(c2, w.T, L, rnext, kSlope, rcur, w.ACC, mode);
+        } else {                                                 // ResBlock2.call model.py:106-112
+          const Layer& c1 = h->layers[h->index[base + ".convs." + std::to_string(m)]];
+          r.conv(c1, rcur, L, rnext, kSlope, rcur, w.ACC, mode);
+        }
+        rcur = rnext;
+      }
+    }
+    x = next_x;                                                  // x = xs / num_kernels (model.py:167)
+    stamp();
+  }
+  if (r.status != cudaSuccess) return fail(h, HFG_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(r.status));
+
+  // leakyReLU(0.3) -> conv_post -> tanh (model.py:169-171)
+  const Layer& post = h->layers[h->index["conv_post"]];
+  PostArgs pa{};
+  pa.x = x; pa.w = post.d_w32; pa.out = audio_dev; pa.B = B; pa.rows = L; pa.c_in = post.cin; pa.ntaps = post.k;
+  pa.pad_left = (post.k - 1) / 2; pa.in_slope = kFinalSlope;
+  pa.bias = post.b.empty() ? 0.f : post.b[0];
+  cudaError_t e = launch_conv_post(pa, h->act, s);
+  h->launches++;
+  if (e != cudaSuccess) return fail(h, HFG_ERR_CUDA, "conv_post launch failed: %s", cudaGetErrorString(e));
+  stamp();
+  h->n_stage_marks = mark;
+  return HFG_OK;
+}
+
+}  // namespace
+
+// =============================================================================== C ABI
+extern "C" {
+
+int hfg_version(void) { return 1000; }
+
+int hfg_create(const hfg_config* cfg, int device, hfg_handle* out) {
+  if (!cfg || !out) return fail(nullptr, HFG_ERR_INVALID, "hfg_create: null argument");
+  *out = nullptr;
+  int rc = validate_config(*cfg);
+  if (rc) return rc;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(nullptr, HFG_ERR_CUDA, "no CUDA device available (%s); this library has no CPU fallback", cudaGetErrorString(e));
+  if (device < 0 || device >= ndev) return fail(nullptr, HFG_ERR_INVALID, "device %d out of range [0,%d)", device, ndev);
+  hfg_ctx* h = new hfg_ctx();
+  h->cfg = *cfg; h->device = device;
+  build_layers(h);
+  *out = h;
+  return HFG_OK;
+}
+
+int hfg_set_weight(hfg_handle h, const char* name, const float* host, const int64_t* shape, int ndim) {
+  if (!h) return HFG_ERR_INVALID;
+  if (!name || !host || !shape) return fail(h, HFG_ERR_INVALID, "hfg_set_weight: null argument");
+  std::string full(name);
+  const size_t dot = full.rfind('.');
+  if (dot == std::string::npos) return fail(h, HFG_ERR_INVALID, "weight name '%s' must end in .v/.g/.b", name);
+  const std::string lname = full.substr(0, dot), kind = full.substr(dot + 1);
+  auto it = h->index.find(lname);
+  if (it == h->index.end()) return fail(h, HFG_ERR_INVALID, "unknown layer '%s'", lname.c_str());
+  Layer& L = h->layers[it->second];
+  size_t n = 1;
+  for (int i = 0; i < ndim; ++i) n *= (size_t)shape[i];
+  if (kind == "v") {
+    const int64_t e1 = L.transposed ? L.cout : L.cin, e2 = L.transposed ? L.cin : L.cout;
+    if (ndim != 3 || shape[0] != L.k || shape[1] != e1 || shape[2] != e2)
+      return fail(h, HFG_ERR_INVALID, "%s: expected shape [%d,%lld,%lld] (Keras %s kernel layout)", name, L.k, (long long)e1, (long long)e2,
+                  L.transposed ? "Conv1DTranspose [k,Cout,Cin]" : "Conv1D [k,Cin,Cout]");
+    L.v.assign(host, host + n); L.has_v = true;
+  } else if (kind == "g") {
+    const int64_t e = L.transposed ? L.cin : L.cout;
+    if (n != (size_t)e) return fail(h, HFG_ERR_INVALID, "%s: expected %lld elements (last axis of v)", name, (long long)e);
+    L.g.assign(host, host + n); L.has_g = true;
+  } else if (kind == "b") {
+    if (n != (size_t)L.cout) return fail(h, HFG_ERR_INVALID, "%s: expected %d elements", name, L.cout);
+    L.b.assign(host, host + n); L.has_b = true;
+  } else {
+    return fail(h, HFG_ERR_INVALID, "weight name '%s' must end in .v/.g/.b", name);
+  }
+  h->finalized = false;
+  return HFG_OK;
+}
+
+int hfg_finalize_weights(hfg_handle h, int precision) {
+  if (!h) return HFG_ERR_INVALID;
+  if (precision < 0 || precision > 2) return fail(h, HFG_ERR_INVALID, "precision must be 0 (fp32), 1 (fp16) or 2 (bf16)");
+  for (const Layer& L : h->layers)
+    if (!L.has_v || !L.has_g || !L.has_b) return fail(h, HFG_ERR_STATE, "layer '%s' is missing %s", L.name.c_str(), !L.has_v ? "v" : (!L.has_g ? "g" : "b"));
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  h->precision = precision;
+  h->act = precision == HFG_PRECISION_FP32 ? ACT_F32 : (precision == HFG_PRECISION_FP16 ? ACT_F16 : ACT_BF16);
+  const hfg_config& c = h->cfg;
+  for (Layer& L : h->layers) {
+    free_layer_device(L);
+    const std::vector<float> w = fold_weight_norm(L);   // canonical [k][cin][cout]
+    const bool is_post = (L.name == "conv_post");
+    // phases and tap tables
+    L.phases.clear();
+    L.cin_pad = L.cin;
+    if (!L.transposed) {
+      bool ok; Phase ph; ph.ntaps = L.k;
+      const int pl = (L.name == "conv_pre" || is_post) ? (L.dil * (L.k - 1)) / 2 : conv_pad_left(L.k, L.dil, c.compat, &ok);
+      for (int j = 0; j < L.k; ++j) ph.tap_off[j] = j * L.dil - pl;
+      L.phases.push_back(ph);
+    } else {
+      const int u = L.stride, P = (L.k - u) / 2;
+      for (int p = 0; p < u; ++p) {
+        Phase ph;
+        for (int j = (p + P) % u; j < L.k; j += u) ph.tap_off[ph.ntaps++] = (p + P - j) / u;   // exact: (p+P-j) % u == 0
+        L.phases.push_back(ph);
+      }
+    }
+    // tensor-core eligibility (engine option "force_ffma" keeps everything on the direct kernel)
+    int max_taps = 0, max_span = 0;
+    for (const Phase& ph : L.phases) {
+      max_taps = ph.ntaps > max_taps ? ph.ntaps : max_taps;
+      int mn = ph.tap_off[0], mx = ph.tap_off[0];
+      for (int j = 1; j < ph.ntaps; ++j) { mn = std::min(mn, ph.tap_off[j]); mx = std::max(mx, ph.tap_off[j]); }
+      max_span = std::max(max_span, mx - mn);
+    }
+    int cin_mma = L.cin;
+    if (L.name == "conv_pre") cin_mma = (int)align_up((size_t)L.cin, 64);
+    L.use_umma = !is_post && h->act != ACT_F32 && !h->force_ffma && umma_supported(cin_mma, L.cout, max_taps, max_span);
+    if (L.use_umma) L.cin_pad = cin_mma;
+    // fp32 weights per phase, [ntaps][cin_pad][cout]
+    std::vector<float> w32;
+    for (Phase& ph : L.phases) {
+      ph.w32_off = w32.size();
+      w32.resize(w32.size() + (size_t)ph.ntaps * L.cin_pad * L.cout, 0.f);
+    }
+    for (size_t p = 0; p < L.phases.size(); ++p) {
+      Phase& ph = L.phases[p];
+      for (int t = 0; t < ph.ntaps; ++t) {
+        int j;
+        if (!L.transposed) j = t;
+        else { const int u = L.stride, P = (L.k - u) / 2; j = ((int)p + P) % u + t * u; }
+        for (int ci = 0; ci < L.cin; ++ci)
+          memcpy(&w32[ph.w32_off + ((size_t)t * L.cin_pad + ci) * L.cout], &w[((size_t)j * L.cin + ci) * L.cout], sizeof(float) * L.cout);
+      }
+    }
+    if (L.use_umma) {
+      size_t total = 0;
+      for (Phase& ph : L.phases) { ph.wpk_off = total; total += align_up(umma_packed_weight_bytes(L.cin_pad, L.cout, ph.ntaps), 256); }
+      std::vector<char> pk(total);
+      for (Phase& ph : L.phases) umma_pack_weights(&w32[ph.w32_off], ph.ntaps, L.cin_pad, L.cout, h->act, pk.data() + ph.wpk_off);
+      CUDA_TRY(h, cudaMalloc(&L.d_wpk, total));
+      CUDA_TRY(h, cudaMemcpy(L.d_wpk, pk.data(), total, cudaMemcpyHostToDevice));
+    } else {
+      CUDA_TRY(h, cudaMalloc((void**)&L.d_w32, w32.size() * sizeof(float)));
+      CUDA_TRY(h, cudaMemcpy(L.d_w32, w32.data(), w32.size() * sizeof(float), cudaMemcpyHostToDevice));
+    }
+    std::vector<float> bias(align_up((size_t)L.cout, 4), 0.f);
+    memcpy(bias.data(), L.b.data(), sizeof(float) * L.cout);
+    CUDA_TRY(h, cudaMalloc((void**)&L.d_bias, bias.size() * sizeof(float)));
+    CUDA_TRY(h, cudaMemcpy(L.d_bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
+  }
+  if (h->events.empty()) {
+    h->events.resize(c.num_upsamples + 3);
+    for (auto& ev : h->events) CUDA_TRY(h, cudaEventCreate(&ev));
+  }
+  h->finalized = true;
+  return HFG_OK;
+}
+
+int hfg_total_upsample(hfg_handle h, int* out) {
+  if (!h || !out) return HFG_ERR_INVALID;
+  *out = h->total_up;
+  return HFG_OK;
+}
+
+int hfg_workspace_bytes(hfg_handle h, int B, int T, size_t* out) {
+  if (!h || !out) return HFG_ERR_INVALID;
+  if (!h->finalized) return fail(h, HFG_ERR_STATE, "hfg_workspace_bytes: weights not finalised");
+  if (B < 0 || T < 0) return fail(h, HFG_ERR_INVALID, "negative batch or frame count");
+  *out = workspace_layout(h, B, T, nullptr, nullptr) + 256;
+  return HFG_OK;
+}
+
+int hfg_forward(hfg_handle h, const float* mel_dev, int B, int T, float* audio_dev, void* workspace_dev,
+                size_t workspace_bytes, void* stream) {
+  if (!h) return HFG_ERR_INVALID;
+  if (!h->finalized) return fail(h, HFG_ERR_STATE, "hfg_forward: weights not finalised");
+  if (B < 0 || T < 0) return fail(h, HFG_ERR_INVALID, "negative batch or frame count");
+  h->launches = 0;
+  if (B == 0 || T == 0) return HFG_OK;                 // empty batch / empty utterances: nothing to synthesise
+  if (!mel_dev || !audio_dev || !workspace_dev) return fail(h, HFG_ERR_INVALID, "hfg_forward: null device pointer");
+  if ((uintptr_t)mel_dev % 16 || (uintptr_t)audio_dev % 4) return fail(h, HFG_ERR_INVALID, "mel must be 16-byte aligned");
+  char* ws = (char*)align_up((size_t)(uintptr_t)workspace_dev, 256);
+  const size_t need = workspace_layout(h, B, T, nullptr, nullptr);
+  if ((size_t)(ws - (char*)workspace_dev) + need > workspace_bytes)
+    return fail(h, HFG_ERR_NOMEM, "workspace too small: need %zu bytes, got %zu", need + 256, workspace_bytes);
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  return run_forward(h, mel_dev, B, T, audio_dev, ws, (cudaStream_t)stream);
+}
+
+int hfg_forward_host(hfg_handle h, const float* mel_host, int B, int T, float* audio_host) {
+  if (!h) return HFG_ERR_INVALID;
+  if (!h->finalized) return fail(h, HFG_ERR_STATE, "hfg_forward_host: weights not finalised");
+  if (B < 0 || T < 0) return fail(h, HFG_ERR_INVALID, "negative batch or frame count");
+  h->launches = 0;
+  if (B == 0 || T == 0) return HFG_OK;
+  if (!mel_host || !audio_host) return fail(h, HFG_ERR_INVALID, "hfg_forward_host: null host pointer");
+  CUDA_TRY(h, cudaSetDevice(h->device));
+  if (!h->stream) CUDA_TRY(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  const int mb = (h->micro_batch <= 0 || h->micro_batch > B) ? B : h->micro_batch;
+  const size_t mel_elems = (size_t)T * h->cfg.num_mels, aud_elems = (size_t)T * h->total_up;
+  const size_t need_ws = workspace_layout(h, mb, T, nullptr, nullptr);
+  if (need_ws > h->ws_bytes) {
+    if (h->ws) cudaFree(h->ws);
+    h->ws = nullptr; h->ws_bytes = 0;
+    CUDA_TRY(h, cudaMalloc(&h->ws, need_ws));
+    h->ws_bytes = need_ws;
+  }
+  if ((size_t)B * mel_elems * 4 > h->d_mel_bytes) {
+    if (h->d_mel) cudaFree(h->d_mel);
+    h->d_mel = nullptr; h->d_mel_bytes = 0;
+    CUDA_TRY(h, cudaMalloc((void**)&h->d_mel, (size_t)B * mel_elems * 4));
+    h->d_mel_bytes = (size_t)B * mel_elems * 4;
+  }
+  if ((size_t)B * aud_elems * 4 > h->d_audio_bytes) {
+    if (h->d_audio) cudaFree(h->d_audio);
+    h->d_audio = nullptr; h->d_audio_bytes = 0;
+    CUDA_TRY(h, cudaMalloc((void**)&h->d_audio, (size_t)B * aud_elems * 4));
+    h->d_audio_bytes = (size_t)B * aud_elems * 4;
+  }
+  long long launches = 0;
+  CUDA_TRY(h, cudaMemcpyAsync(h->d_mel, mel_host, (size_t)B * mel_elems * 4, cudaMemcpyHostToDevice, h->stream));
+  for (int b0 = 0; b0 < B; b0 += mb) {
+    const int nb = (B - b0 < mb) ? B - b0 : mb;
+    int rc = run_forward(h, h->d_mel + (size_t)b0 * mel_elems, nb, T, h->d_audio + (size_t)b0 * aud_elems, (char*)h->ws, h->stream);
+    launches += h->launches; h->launches = 0;
+    if (rc) return rc;
+    CUDA_TRY(h, cudaMemcpyAsync(audio_host + (size_t)b0 * aud_elems, h->d_audio + (size_t)b0 * aud_elems,
+                                (size_t)nb * aud_elems * 4, cudaMemcpyDeviceToHost, h->stream));
+  }
+  h->launches = launches;
+  CUDA_TRY(h, cudaStreamSynchronize(h->stream));
+  return HFG_OK;
+}
+
+int hfg_set_option(hfg_handle h, const char* key, long long value) {
+  if (!h || !key) return HFG_ERR_INVALID;
+  const std::string k(key);
+  if (k == "micro_batch") { if (value < 0) return fail(h, HFG_ERR_INVALID, "micro_batch must be >= 0"); h->micro_batch = (int)value; return HFG_OK; }
+  if (k == "stage_timing") { h->stage_timing = value != 0; return HFG_OK; }
+  if (k == "force_ffma") { h->force_ffma = value != 0; h->finalized = false; return HFG_OK; }
+  return fail(h, HFG_ERR_INVALID, "unknown option '%s'", key);
+}
+
+int hfg_last_launch_count(hfg_handle h, long long* out) {
+  if (!h || !out) return HFG_ERR_INVALID;
+  *out = h->launches;
+  return HFG_OK;
+}
+
+int hfg_stage_times_ms(hfg_handle h, float* out, int* n) {
+  if (!h || !out || !n) return HFG_ERR_INVALID;
+  if (!h->stage_timing || h->n_stage_marks < 2) return fail(h, HFG_ERR_STATE, "stage timing not enabled or no forward ran");
+  CUDA_TRY(h, cudaEventSynchronize(h->events[h->n_stage_marks - 1]));
+  const int cnt = h->n_stage_marks - 1;
+  if (*n < cnt) return fail(h, HFG_ERR_INVALID, "need room for %d floats", cnt);
+  for (int i = 0; i < cnt; ++i) CUDA_TRY(h, cudaEventElapsedTime(&out[i], h->events[i], h->events[i + 1]));
+  *n = cnt;
+  return HFG_OK;
+}
+
+// Single tapped-conv operator (kernels.cuh ConvArgs) on caller-provided device buffers; packs and
+// uploads the weights on every call -- meant for operator-level parity tests, not for speed.
+int hfg_op_tapped_conv(int act, int use_umma, const void* x_dev, int B, int x_rows, int c_in,
+                       const float* w_host, const float* bias_host, int c_out, int ntaps, const int* tap_off,
+                       int out_stride, int out_off, float in_slope, const void* res_dev, float* acc_dev,
+                       int mrf_mode, float mrf_div, void* out_dev, void* stream) {
+  if (act < 0 || act > 2 || !x_dev || !w_host || !bias_host || !tap_off || ntaps < 1 || ntaps > kMaxTaps)
+    return fail(nullptr, HFG_ERR_INVALID, "hfg_op_tapped_conv: bad argument");
+  ConvArgs a{};
+  a.x = x_dev; a.out = out_dev; a.res = res_dev; a.acc = acc_dev;
+  a.B = B; a.x_rows = x_rows; a.n_q = x_rows; a.out_rows = x_rows * out_stride;
+  a.c_in = c_in; a.c_out = c_out; a.ntaps = ntaps;
+  int mn = tap_off[0], mx = tap_off[0];
+  for (int j = 0; j < ntaps; ++j) { a.tap_off[j] = tap_off[j]; mn = std::min(mn, tap_off[j]); mx = std::max(mx, tap_off[j]); }
+  a.out_stride = out_stride; a.out_off = out_off; a.in_slope = in_slope; a.mrf_mode = mrf_mode; a.mrf_div = mrf_div;
+  cudaStream_t s = (cudaStream_t)stream;
+  float* d_bias = nullptr; void* d_w = nullptr;
+  std::vector<float> bias(align_up((size_t)c_out, 4), 0.f);
+  memcpy(bias.data(), bias_host, sizeof(float) * c_out);
+  CUDA_TRY(nullptr, cudaMalloc((void**)&d_bias, bias.size() * 4));
+  CUDA_TRY(nullptr, cudaMemcpy(d_bias, bias.data(), bias.size() * 4, cudaMemcpyHostToDevice));
+  a.bias = d_bias;
+  cudaError_t e;
+  if (use_umma) {
+    if (act == ACT_F32 || !umma_supported(c_in, c_out, ntaps, mx - mn)) {
+      cudaFree(d_bias);
+      return fail(nullptr, HFG_ERR_UNSUPPORTED, "tcgen05 kernel does not cover c_in=%d c_out=%d ntaps=%d span=%d act=%d", c_in, c_out, ntaps, mx - mn, act);
+    }
+    const size_t nb = umma_packed_weight_bytes(c_in, c_out, ntaps);
+    std::vector<char> pk(nb);
+    umma_pack_weights(w_host, ntaps, c_in, c_out, (ActType)act, pk.data());
+    CUDA_TRY(nullptr, cudaMalloc(&d_w, nb));
+    CUDA_TRY(nullptr, cudaMemcpy(d_w, pk.data(), nb, cudaMemcpyHostToDevice));
+    a.w = d_w;
+    e = launch_conv_umma(a, (ActType)act, s);
+  } else {
+    const size_t nb = (size_t)ntaps * c_in * c_out * 4;
+    CUDA_TRY(nullptr, cudaMalloc(&d_w, nb));
+    CUDA_TRY(nullptr, cudaMemcpy(d_w, w_host, nb, cudaMemcpyHostToDevice));
+    a.w = d_w;
+    e = launch_conv_ffma(a, (ActType)act, s);
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  cudaFree(d_bias); cudaFree(d_w);
+  if (e != cudaSuccess) return fail(nullptr, HFG_ERR_CUDA, "tapped conv failed: %s", cudaGetErrorString(e));
+  return HFG_OK;
+}
+
+int hfg_host_alloc(void** out, size_t bytes) {
+  if (!out) return HFG_ERR_INVALID;
+  cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault);
+  if (e != cudaSuccess) return fail(nullptr, HFG_ERR_CUDA, "cudaHostAlloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+  return HFG_OK;
+}
+
+int hfg_host_free(void* p) {
+  if (!p) return HFG_OK;
+  return cudaFreeHost(p) == cudaSuccess ? HFG_OK : HFG_ERR_CUDA;
+}
+
+const char* hfg_last_error(hfg_handle h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+void hfg_destroy(hfg_handle h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  for (Layer& L : h->layers) free_layer_device(L);
+  for (auto& ev : h->events) cudaEventDestroy(ev);
+  if (h->ws) cudaFree(h->ws);
+  if (h->d_mel) cudaFree(h->d_mel);
+  if (h->d_audio) cudaFree(h->d_audio);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+}
+
+}  // extern "C"

@@ -1,0 +1,71 @@
+// Internal interface between the engine (engine.cu) and the kernel translation units.
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace hfg {
+
+constexpr int kMaxTaps = 16;
+
+enum ActType : int { ACT_F32 = 0, ACT_F16 = 1, ACT_BF16 = 2 };
+
+// MRF fusion in the epilogue of the last conv of a resblock
+// (reference HiFiGAN_TF/model.py:161-167: xs = rb0(x)+rb1(x)+rb2(x); x = xs / num_kernels).
+enum MrfMode : int {
+  MRF_NONE = 0,    // out = val
+  MRF_FIRST = 1,   // acc = val
+  MRF_ADD = 2,     // acc += val
+  MRF_FINAL = 3    // out = (acc + val) / num_kernels
+};
+
+// One "tapped GEMM": out[b, q*out_stride + out_off, co] =
+//     epilogue( bias[co] + sum_j sum_ci act(x[b, q + tap_off[j], ci]) * w[j][ci][co] )
+// A stride-1 (dilated) Conv1D is out_stride=1, tap_off[j] = j*d - pad_left.
+// One output phase p of a Conv1DTranspose (stride u) is out_stride=u, out_off=p with the
+// k/u taps j == (p+P) mod u at input offsets (p+P-j)/u   (polyphase, no zero insertion).
+struct ConvArgs {
+  const void* x;        // [B, x_rows, c_in] activations (ActType)
+  const void* w;        // FFMA: fp32 [ntaps][c_in][c_out]; UMMA: packed 16-bit tiles
+  const float* bias;    // [c_out] fp32
+  void* out;            // [B, out_rows, c_out] (ActType)
+  const void* res;      // residual, indexed like out (ActType) or nullptr
+  float* acc;           // MRF accumulator fp32, indexed like out, or nullptr
+  int B;
+  int x_rows;           // rows per batch item in x
+  int n_q;              // q range per batch item
+  int out_rows;         // rows per batch item in out
+  int c_in, c_out;
+  int ntaps;
+  int tap_off[kMaxTaps];
+  int out_stride, out_off;
+  float in_slope;       // leaky-relu slope applied to x while staging (1 = identity)
+  int mrf_mode;
+  float mrf_div;        // num_kernels
+};
+
+// conv_post + tanh (reference model.py:169-171): C_out = 1
+struct PostArgs {
+  const void* x;        // [B, rows, c_in]
+  const float* w;       // fp32 [ntaps][c_in]
+  float bias;
+  float* out;           // fp32 [B, rows]
+  int B, rows, c_in, ntaps, pad_left;
+  float in_slope;
+};
+
+// fp32 / generic direct kernels (conv_ffma.cu)
+cudaError_t launch_conv_ffma(const ConvArgs& a, ActType act, cudaStream_t s);
+cudaError_t launch_conv_post(const PostArgs& a, ActType act, cudaStream_t s);
+cudaError_t launch_cast_pad(const float* src, void* dst, long long rows, int c_src, int c_dst,
+                            ActType act, cudaStream_t s);
+
+// tcgen05 implicit-GEMM kernels (conv_umma.cu)
+bool umma_supported(int c_in, int c_out, int ntaps, int span);
+size_t umma_packed_weight_bytes(int c_in, int c_out, int ntaps);
+// host-side repack of fp32 [ntaps][c_in][c_out] into the kernel's smem-image tiles (16-bit)
+void umma_pack_weights(const float* w, int ntaps, int c_in, int c_out, ActType act, void* dst_host);
+cudaError_t launch_conv_umma(const ConvArgs& a, ActType act, cudaStream_t s);
+
+}  // namespace hfg

@@ -1,0 +1,221 @@
+"""Drop-in `Generator` for reference HiFiGAN_TF/model.py:115-173.
+
+Same constructor argument (`hparams`), same `call(mel) -> audio` / `__call__(mel, training=...)`
+signature and channels-last layout ([B, T, num_mels] -> [B, T*prod(upsample_rates), 1], fp32,
+reference HiFiGAN_TF/train.py:70-74).  All arithmetic runs in hand-written sm_100a CUDA kernels
+reached through the C ABI of libhifigan_b200.so (ctypes); no TensorFlow, no Triton, no CPU path.
+
+Differences to the Keras model that are on purpose:
+  * forward only: `training=True` raises NotImplementedError (`.trainable_variables`, `.save`
+    are training/serialisation surface, out of scope -- SURVEY.md section 8b);
+  * weights are given explicitly (`load_weights`) under the names of SURVEY.md section 8b, in the
+    Keras layouts; weight norm (tfa WeightNormalization, data_init=False) is folded once at
+    load instead of on every call;
+  * `precision`: "fp32" (FFMA validation mode), "fp16" (tcgen05 tensor cores, default) or "bf16".
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Mapping, Optional, Union
+
+import numpy as np
+
+from . import _lib
+from .hparams import coerce_hparams
+from .synthetic import synthetic_weights
+from .topology import enumerate_layers, total_upsample
+
+try:                                    # torch is plumbing only (device buffers / streams)
+    import torch
+except Exception:                       # pragma: no cover
+    torch = None
+
+
+def _config_from_hparams(h, compat: str) -> _lib.HfgConfig:
+    if compat not in ("reference", "upstream"):
+        raise ValueError("compat must be 'reference' or 'upstream'")
+    cfg = _lib.HfgConfig()
+    cfg.num_mels = int(h.num_mels)
+    cfg.upsample_initial_channel = int(h.upsample_initial_channel)
+    # reference model.py:126: ResBlock1 if hparams.resblock == '1' else ResBlock2
+    cfg.resblock = 1 if h.resblock == "1" else 2
+    rates, ksz = list(h.upsample_rates), list(h.upsample_kernel_sizes)
+    if len(rates) != len(ksz):
+        raise ValueError("upsample_rates and upsample_kernel_sizes differ in length")
+    if len(rates) > _lib.HFG_MAX_UPSAMPLES:
+        raise ValueError("too many upsample stages")
+    cfg.num_upsamples = len(rates)
+    for i, (u, k) in enumerate(zip(rates, ksz)):
+        cfg.upsample_rates[i] = int(u)
+        cfg.upsample_kernel_sizes[i] = int(k)
+    rks, rds = list(h.resblock_kernel_sizes), list(h.resblock_dilation_sizes)
+    if len(rks) != len(rds):
+        raise ValueError("resblock_kernel_sizes and resblock_dilation_sizes differ in length")
+    if len(rks) > _lib.HFG_MAX_KERNELS:
+        raise ValueError("too many resblock kernels")
+    cfg.num_kernels = len(rks)
+    for j, (k, ds) in enumerate(zip(rks, rds)):
+        ds = list(ds)
+        # ResBlock1 consumes dilation[0..2], ResBlock2 dilation[0..1] (model.py:21-66, 84-101)
+        need = 3 if cfg.resblock == 1 else 2
+        if len(ds) < need:
+            raise ValueError(f"resblock_dilation_sizes[{j}] needs {need} entries")
+        ds = ds[:need]
+        cfg.resblock_kernel_sizes[j] = int(k)
+        cfg.num_dilations[j] = len(ds)
+        for m, d in enumerate(ds):
+            cfg.resblock_dilation_sizes[j][m] = int(d)
+    cfg.compat = 0 if compat == "reference" else 1
+    return cfg
+
+
+class Generator:
+    def __init__(self, hparams, precision: str = "fp16", device: int = 0, compat: str = "reference"):
+        self.hparams = coerce_hparams(hparams)
+        if precision not in _lib.PRECISIONS:
+            raise ValueError(f"precision must be one of {sorted(_lib.PRECISIONS)}")
+        self.precision = precision
+        self.device = int(device)
+        self.compat = compat
+        self.num_kernels = len(self.hparams.resblock_kernel_sizes)
+        self.num_upsamples = len(self.hparams.upsample_rates)
+        self._layers = enumerate_layers(self.hparams)
+        self._total_up = total_upsample(self.hparams)
+        self._lib = _lib.load()
+        self._handle = C.c_void_p()
+        cfg = _config_from_hparams(self.hparams, compat)
+        _lib.check(self._lib.hfg_create(C.byref(cfg), self.device, C.byref(self._handle)), None, "hfg_create")
+        self._weights_loaded = False
+        self._ws = None           # torch workspace for the device-pointer path
+
+    # ------------------------------------------------------------------ weights
+    def load_weights(self, weights: Union[str, Mapping[str, np.ndarray]]) -> "Generator":
+        """weights: mapping (or .npz path) with '<layer>.v', '<layer>.g', '<layer>.b' per layer."""
+        if isinstance(weights, str):
+            weights = dict(np.load(weights))
+        for L in self._layers:
+            for suffix, shape in (("v", L.v_shape), ("g", L.g_shape), ("b", L.b_shape)):
+                key = f"{L.name}.{suffix}"
+                if key not in weights:
+                    raise ValueError(f"missing weight {key!r}")
+                arr = np.ascontiguousarray(np.asarray(weights[key], dtype=np.float32))
+                if tuple(arr.shape) != tuple(shape):
+                    raise ValueError(f"{key}: shape {tuple(arr.shape)} != expected {tuple(shape)}")
+                shp = (C.c_int64 * arr.ndim)(*arr.shape)
+                _lib.check(self._lib.hfg_set_weight(self._handle, key.encode(), arr.ctypes.data_as(C.c_void_p),
+                                                    shp, arr.ndim), self._handle, key)
+        _lib.check(self._lib.hfg_finalize_weights(self._handle, _lib.PRECISIONS[self.precision]),
+                   self._handle, "hfg_finalize_weights")
+        self._weights_loaded = True
+        return self
+
+    def init_random(self, seed: int = 1234, variant: str = "A") -> Dict[str, np.ndarray]:
+        """Glorot-uniform v, g = ||v||, b = 0 (variant 'A': what Keras/tfa produce at random init,
+        reference model.py:26-29 defaults) or perturbed g / non-zero b (variant 'B')."""
+        w = synthetic_weights(self.hparams, variant, seed)
+        self.load_weights(w)
+        return w
+
+    def set_option(self, key: str, value: int) -> None:
+        _lib.check(self._lib.hfg_set_option(self._handle, key.encode(), int(value)), self._handle, key)
+        if key == "force_ffma":
+            self._weights_loaded = False
+
+    # ------------------------------------------------------------------ forward
+    def __call__(self, x, training: bool = False):
+        if training:
+            raise NotImplementedError("this Generator is forward-only (inference); training=True is not supported")
+        return self.call(x)
+
+    def call(self, x):
+        """mel [B, T, num_mels] fp32 -> audio [B, T*prod(rates), 1] fp32 (reference model.py:155-173).
+        numpy in -> numpy out (host path, includes H2D/D2H); torch CUDA tensor in -> torch CUDA out
+        (device path, asynchronous on the current stream); torch CPU tensor in -> torch CPU out."""
+        if not self._weights_loaded:
+            raise RuntimeError("weights not loaded: call load_weights() or init_random() first")
+        if torch is not None and isinstance(x, torch.Tensor):
+            if x.is_cuda:
+                return self._call_device(x)
+            return torch.from_numpy(self._call_host(x.detach().numpy()))
+        return self._call_host(np.asarray(x))
+
+    def _check_shape(self, shape):
+        if len(shape) != 3 or int(shape[2]) != int(self.hparams.num_mels):
+            raise ValueError(f"mel must be [B, T, {self.hparams.num_mels}] (channels-last), got {tuple(shape)}")
+
+    def _call_host(self, mel: np.ndarray, out: Optional[np.ndarray] = None) -> np.ndarray:
+        self._check_shape(mel.shape)
+        mel = np.ascontiguousarray(mel, dtype=np.float32)
+        B, T = int(mel.shape[0]), int(mel.shape[1])
+        if out is None:
+            out = np.empty((B, T * self._total_up, 1), dtype=np.float32)
+        _lib.check(self._lib.hfg_forward_host(self._handle, mel.ctypes.data_as(C.c_void_p), B, T,
+                                              out.ctypes.data_as(C.c_void_p)), self._handle, "hfg_forward_host")
+        return out
+
+    def forward_host_ptr(self, mel_ptr: int, B: int, T: int, audio_ptr: int) -> None:
+        """Raw host-pointer entry (pinned buffers from hfg_host_alloc / torch pin_memory)."""
+        _lib.check(self._lib.hfg_forward_host(self._handle, C.c_void_p(mel_ptr), B, T, C.c_void_p(audio_ptr)),
+                   self._handle, "hfg_forward_host")
+
+    def workspace_bytes(self, B: int, T: int) -> int:
+        n = C.c_size_t()
+        _lib.check(self._lib.hfg_workspace_bytes(self._handle, B, T, C.byref(n)), self._handle)
+        return int(n.value)
+
+    def _call_device(self, mel, out=None):
+        self._check_shape(mel.shape)
+        if mel.dtype != torch.float32:
+            mel = mel.float()
+        mel = mel.contiguous()
+        if mel.device.index != self.device:
+            raise ValueError(f"mel is on cuda:{mel.device.index}, generator on cuda:{self.device}")
+        B, T = int(mel.shape[0]), int(mel.shape[1])
+        if out is None:
+            out = torch.empty((B, T * self._total_up, 1), dtype=torch.float32, device=mel.device)
+        if B == 0 or T == 0:
+            return out
+        need = self.workspace_bytes(B, T)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = None
+            self._ws = torch.empty(need, dtype=torch.uint8, device=mel.device)
+        stream = torch.cuda.current_stream(mel.device).cuda_stream
+        _lib.check(self._lib.hfg_forward(self._handle, C.c_void_p(mel.data_ptr()), B, T, C.c_void_p(out.data_ptr()),
+                                         C.c_void_p(self._ws.data_ptr()), self._ws.numel(), C.c_void_p(stream)),
+                   self._handle, "hfg_forward")
+        return out
+
+    # ------------------------------------------------------------------ introspection
+    def last_launch_count(self) -> int:
+        n = C.c_longlong()
+        _lib.check(self._lib.hfg_last_launch_count(self._handle, C.byref(n)), self._handle)
+        return int(n.value)
+
+    def stage_times_ms(self):
+        buf = (C.c_float * 16)()
+        n = C.c_int(16)
+        _lib.check(self._lib.hfg_stage_times_ms(self._handle, buf, C.byref(n)), self._handle)
+        return [float(buf[i]) for i in range(n.value)]
+
+    def summary(self, print_fn=print) -> None:
+        """Layer table (the Keras `.summary()` surface touched by reference gan.py:192)."""
+        print_fn(f"Generator(resblock={self.hparams.resblock!r}, precision={self.precision}, compat={self.compat})")
+        total = 0
+        for L in self._layers:
+            n = L.kernel * L.c_in * L.c_out + L.c_out
+            total += n
+            print_fn(f"  {L.name:28s} {L.kind:5s} k={L.kernel:<2d} d={L.dilation:<2d} s={L.stride:<2d} "
+                     f"{L.c_in:>4d}->{L.c_out:<4d} pad={L.padding:6s} params={n}")
+        print_fn(f"  total effective params: {total}")
+
+    def close(self) -> None:
+        if getattr(self, "_handle", None) is not None and self._handle:
+            self._lib.hfg_destroy(self._handle)
+            self._handle = C.c_void_p()
+        self._ws = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

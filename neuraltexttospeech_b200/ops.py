@@ -1,0 +1,41 @@
+"""Operator-level access to the CUDA kernels (hfg_op_tapped_conv) for parity tests.
+
+torch is used only to own the device buffers."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+
+_ACT = {"fp32": 0, "fp16": 1, "bf16": 2}
+
+
+def tapped_conv(x, w: np.ndarray, bias: np.ndarray, tap_off: Sequence[int], *, engine: str = "umma",
+                out_stride: int = 1, out_off: int = 0, in_slope: float = 1.0, res=None, acc=None,
+                mrf_mode: int = 0, mrf_div: float = 3.0, out=None):
+    """x: torch CUDA tensor [B, rows, c_in] (float32 / float16 / bfloat16); w: fp32 [ntaps, c_in, c_out]."""
+    import torch
+    lib = _lib.load()
+    act = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}[x.dtype]
+    B, rows, c_in = (int(v) for v in x.shape)
+    ntaps, c_in_w, c_out = (int(v) for v in w.shape)
+    if c_in_w != c_in or len(tap_off) != ntaps:
+        raise ValueError("weight / tap shapes do not match the input")
+    x = x.contiguous()
+    w = np.ascontiguousarray(w, dtype=np.float32)
+    bias = np.ascontiguousarray(bias, dtype=np.float32)
+    if out is None:
+        out = torch.zeros((B, rows * out_stride, c_out), dtype=x.dtype, device=x.device)
+    taps = (C.c_int * ntaps)(*[int(t) for t in tap_off])
+    rc = lib.hfg_op_tapped_conv(act, 1 if engine == "umma" else 0, C.c_void_p(x.data_ptr()), B, rows, c_in,
+                                w.ctypes.data_as(C.c_void_p), bias.ctypes.data_as(C.c_void_p), c_out, ntaps, taps,
+                                out_stride, out_off, float(in_slope),
+                                C.c_void_p(res.data_ptr()) if res is not None else None,
+                                C.c_void_p(acc.data_ptr()) if acc is not None else None,
+                                int(mrf_mode), float(mrf_div), C.c_void_p(out.data_ptr()),
+                                C.c_void_p(torch.cuda.current_stream(x.device).cuda_stream))
+    _lib.check(rc, None, "hfg_op_tapped_conv")
+    return out

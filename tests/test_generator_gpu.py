@@ -1,0 +1,158 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI (ctypes), against the CPU
+oracle on the same seeded inputs and against the committed golden fixtures.
+
+Tolerances (BASELINE.json north_star): fp32 FFMA validation mode max-abs <= 1e-5;
+tensor-core path max-abs <= 2e-3 and SNR >= 40 dB."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from neuraltexttospeech_b200 import Generator, HParams
+from neuraltexttospeech_b200.synthetic import synthetic_mel, synthetic_weights
+from oracle import hifigan_oracle as O
+
+FP32_TOL = 1e-5
+TC_TOL = 2e-3
+TC_SNR = 40.0
+
+
+def snr_db(ref, out):
+    return 10 * np.log10((ref.astype(np.float64) ** 2).sum() / max(((out - ref).astype(np.float64) ** 2).sum(), 1e-30))
+
+
+@pytest.fixture(scope="module")
+def gens():
+    cache = {}
+
+    def get(v, precision, variant="B", compat="reference"):
+        key = (v, precision, variant, compat)
+        if key not in cache:
+            h = HParams.builtin(v)
+            cache[key] = Generator(h, precision=precision, compat=compat).load_weights(synthetic_weights(h, variant))
+        return cache[key]
+
+    yield get
+    for g in cache.values():
+        g.close()
+
+
+@pytest.mark.parametrize("v", "123")
+@pytest.mark.parametrize("variant", "AB")
+def test_fp32_mode_matches_golden(v, variant, gens, golden_dir):
+    z = np.load(os.path.join(golden_dir, f"oracle_v{v}_{variant}.npz"))
+    out = gens(v, "fp32", variant)(z["mel"])
+    assert out.shape == z["audio"].shape and out.dtype == np.float32
+    assert np.abs(out - z["audio"]).max() <= FP32_TOL
+
+
+@pytest.mark.parametrize("v", "123")
+def test_fp32_upstream_compat_matches_vendored_torch_fixture(v, gens, golden_dir):
+    z = np.load(os.path.join(golden_dir, f"upstream_v{v}.npz"))
+    out = gens(v, "fp32", "B", "upstream")(z["mel"])
+    assert np.abs(out - z["audio"]).max() <= 2e-5
+
+
+@pytest.mark.parametrize("v", "123")
+@pytest.mark.parametrize("variant", "AB")
+def test_fp16_tensor_core_mode_matches_golden(v, variant, gens, golden_dir):
+    z = np.load(os.path.join(golden_dir, f"oracle_v{v}_{variant}.npz"))
+    out = gens(v, "fp16", variant)(z["mel"])
+    assert np.abs(out - z["audio"]).max() <= TC_TOL
+    assert snr_db(z["audio"], out) >= TC_SNR
+
+
+@pytest.mark.parametrize("v,B,T", [("1", 2, 40), ("2", 3, 33), ("3", 2, 57), ("1", 1, 1), ("3", 5, 2)])
+def test_against_oracle_seeded(v, B, T, gens):
+    h = HParams.builtin(v)
+    w = synthetic_weights(h, "B")
+    mel = synthetic_mel(B, T, h.num_mels, seed=7 + T)
+    ref = O.generator_forward(h, w, mel, "torch32")
+    out32 = gens(v, "fp32")(mel)
+    assert np.abs(out32 - ref).max() <= FP32_TOL
+    out16 = gens(v, "fp16")(mel)
+    assert np.abs(out16 - ref).max() <= TC_TOL and snr_db(ref, out16) >= TC_SNR
+
+
+def test_config1_shape_v1_batch1_256_frames(gens):
+    # BASELINE.json configs[0]: V1, batch 1, 80-mel x 256 frames -> 65,536 samples
+    h = HParams.builtin("1")
+    w = synthetic_weights(h, "A")
+    mel = synthetic_mel(1, 256, 80)
+    ref = O.generator_forward(h, w, mel, "torch32")
+    assert ref.shape == (1, 65536, 1)
+    out = gens("1", "fp16", "A")(mel)
+    assert out.shape == (1, 65536, 1)
+    assert np.abs(out - ref).max() <= TC_TOL and snr_db(ref, out) >= TC_SNR
+    out32 = gens("1", "fp32", "A")(mel)
+    assert np.abs(out32 - ref).max() <= FP32_TOL
+
+
+def test_device_tensor_path_equals_host_path(gens):
+    import torch
+    g = gens("1", "fp16")
+    mel = synthetic_mel(3, 20, 80, seed=3)
+    host = g(mel)
+    dev = g(torch.from_numpy(mel).cuda())
+    assert dev.is_cuda and dev.shape == (3, 20 * 256, 1)
+    assert np.array_equal(dev.cpu().numpy(), host)
+    assert g.last_launch_count() > 50
+
+
+def test_batch_independence_and_micro_batching(gens):
+    # utterances are independent: a batch equals its items run alone, for any micro-batch split
+    g = gens("3", "fp16")
+    mel = synthetic_mel(5, 17, 80, seed=11)
+    g.set_option("micro_batch", 2)
+    a = g(mel)
+    g.set_option("micro_batch", 0)
+    b = g(mel)
+    g.set_option("micro_batch", 16)
+    assert np.array_equal(a, b)
+    for i in range(5):
+        assert np.array_equal(g(mel[i:i + 1]), a[i:i + 1])
+
+
+def test_edge_cases(gens):
+    g = gens("1", "fp16")
+    assert g(np.zeros((0, 10, 80), np.float32)).shape == (0, 2560, 1)      # empty batch
+    assert g(np.zeros((2, 0, 80), np.float32)).shape == (2, 0, 1)          # empty utterances
+    with pytest.raises(ValueError):
+        g(np.zeros((2, 10, 64), np.float32))                                # wrong mel width
+    with pytest.raises(NotImplementedError):
+        g(np.zeros((1, 4, 80), np.float32), training=True)
+    out = g(np.full((1, 3, 80), -11.5129, np.float32))                      # silence-floor mel
+    assert np.isfinite(out).all() and np.abs(out).max() <= 1.0
+
+
+def test_time_shift_consistency_full_size_property():
+    """Size-independent property at the bench size (V1, 10 s utterances): away from the edges the
+    generator is shift-equivariant -- shifting the mel by s frames shifts the audio by 256*s."""
+    h = HParams.builtin("1")
+    g = Generator(h, precision="fp16").load_weights(synthetic_weights(h, "A"))
+    T, s = 862, 3
+    mel = synthetic_mel(2, T + s, 80, seed=5)
+    a = g(mel[:, :T])
+    b = g(mel[:, s:])
+    rf = 40           # receptive field of the whole stack in mel frames is < 40
+    lo, hi = rf * 256, (T - s - rf) * 256
+    assert a.shape == (2, 220672, 1)
+    assert np.abs(a[:, lo + s * 256: hi + s * 256] - b[:, lo:hi]).max() <= 1e-6
+    g.close()
+
+
+def test_weight_errors():
+    h = HParams.builtin("2")
+    g = Generator(h, precision="fp32")
+    w = synthetic_weights(h, "A")
+    with pytest.raises(RuntimeError):
+        g(np.zeros((1, 4, 80), np.float32))          # weights not loaded
+    bad = dict(w); bad["ups.0.v"] = np.transpose(bad["ups.0.v"], (0, 2, 1))
+    with pytest.raises(ValueError):
+        g.load_weights(bad)                           # Conv1DTranspose kernel must be [k, Cout, Cin]
+    missing = dict(w); del missing["conv_post.g"]
+    with pytest.raises(ValueError):
+        g.load_weights(missing)
+    g.close()

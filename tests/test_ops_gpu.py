@@ -1,0 +1,99 @@
+"""Operator-level parity on the GPU: each tapped-conv kernel (direct FFMA and tcgen05) against a
+numpy restatement of the same op, over the channel shapes the three stock configs use."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def ref_tapped_conv(x, w, bias, tap_off, out_stride=1, out_off=0, in_slope=1.0, res=None):
+    """numpy fp64 restatement of kernels.cuh ConvArgs semantics."""
+    B, rows, cin = x.shape
+    xa = np.where(x >= 0, x, x * in_slope).astype(np.float64)
+    out = np.zeros((B, rows * out_stride, w.shape[2]))
+    val = np.zeros((B, rows, w.shape[2]))
+    for j, off in enumerate(tap_off):
+        lo, hi = max(0, -off), min(rows, rows - off)
+        if hi > lo:
+            val[:, lo:hi] += xa[:, lo + off:hi + off] @ w[j].astype(np.float64)
+    val += bias
+    out[:, out_off::out_stride] = val
+    if res is not None:
+        out[:, out_off::out_stride] += res[:, out_off::out_stride]
+    return out
+
+
+SHAPES = [  # (c_in, c_out, taps, B, rows)
+    (32, 32, [-2, -1, 0], 2, 700),                       # causal k=3 (reference quirk Q1)
+    (32, 32, [5 * j - 25 for j in range(11)], 1, 1300),  # k=11, d=5
+    (64, 64, [3 * j - 9 for j in range(7)], 2, 520),
+    (128, 128, [j - 5 for j in range(11)], 1, 300),
+    (256, 256, [5 * j - 25 for j in range(11)], 1, 270),
+    (512, 256, [-1, 0], 1, 140),                         # one phase of ups[0]
+    (256, 128, [0, 1], 1, 200),
+    (128, 64, [-1, 0], 1, 600),
+    (64, 32, [0, 1], 2, 515),
+    (128, 256, [j - 3 for j in range(7)], 2, 130),       # conv_pre (mel padded 80 -> 128), half of C_out=512
+    (128, 512, [j - 3 for j in range(7)], 1, 130),       # conv_pre, N split over grid.y
+    (128, 128, [12 * j - 36 for j in range(7)], 1, 400), # V3 k=7 d=12
+]
+
+
+@pytest.mark.parametrize("cin,cout,taps,B,rows", SHAPES)
+@pytest.mark.parametrize("engine,dtype", [("ffma", "float32"), ("umma", "float16"), ("umma", "bfloat16"), ("ffma", "float16")])
+def test_tapped_conv(cin, cout, taps, B, rows, engine, dtype):
+    import torch
+    from neuraltexttospeech_b200.ops import tapped_conv
+    rng = np.random.default_rng(cin * 1000 + cout + len(taps))
+    tdt = getattr(torch, dtype)
+    x = rng.standard_normal((B, rows, cin)).astype(np.float32)
+    w = (rng.standard_normal((len(taps), cin, cout)) / np.sqrt(cin * len(taps))).astype(np.float32)
+    bias = rng.uniform(-0.1, 0.1, cout).astype(np.float32)
+    res = rng.standard_normal((B, rows, cout)).astype(np.float32)
+    xt = torch.from_numpy(x).cuda().to(tdt)
+    rt = torch.from_numpy(res).cuda().to(tdt)
+    xq, rq = xt.float().cpu().numpy(), rt.float().cpu().numpy()
+    wq = w if dtype == "float32" else torch.from_numpy(w).to(tdt).float().numpy()
+    if engine == "ffma":
+        wq = w                                            # the direct kernel keeps fp32 weights
+    ref = ref_tapped_conv(xq, wq, bias, taps, in_slope=0.1, res=rq)
+    if dtype != "float32":                                # the kernel rounds the activated input to 16 bit
+        xa = torch.from_numpy(np.where(xq >= 0, xq, xq * np.float32(0.1))).to(tdt).float().numpy()
+        if engine == "umma":
+            ref = ref_tapped_conv(xa, wq, bias, taps, in_slope=1.0, res=rq)
+    out = tapped_conv(xt, w, bias, taps, engine=engine, in_slope=0.1, res=rt).float().cpu().numpy()
+    tol = {"float32": 2e-5, "float16": 4e-3, "bfloat16": 3e-2}[dtype]   # output rounding of O(1) values
+    assert np.abs(out - ref).max() <= tol
+
+
+@pytest.mark.parametrize("engine,dtype", [("ffma", "float32"), ("umma", "float16")])
+def test_transposed_phase_and_mrf_modes(engine, dtype):
+    import torch
+    from neuraltexttospeech_b200.ops import tapped_conv
+    rng = np.random.default_rng(5)
+    tdt = getattr(torch, dtype)
+    B, rows, cin, cout, u = 2, 300, 64, 32, 2
+    x = torch.from_numpy(rng.standard_normal((B, rows, cin)).astype(np.float32)).cuda().to(tdt)
+    bias = rng.uniform(-0.1, 0.1, cout).astype(np.float32)
+    out = torch.zeros((B, rows * u, cout), dtype=tdt, device="cuda")
+    ref = np.zeros((B, rows * u, cout))
+    for p in range(u):
+        w = (rng.standard_normal((2, cin, cout)) / 12).astype(np.float32)
+        taps = [-1, 0] if p == 0 else [0, 1]
+        tapped_conv(x, w, bias, taps, engine=engine, out_stride=u, out_off=p, in_slope=0.1, out=out)
+        wq = w if engine == "ffma" else torch.from_numpy(w).to(tdt).float().numpy()
+        xq = x.float().cpu().numpy()
+        xa = torch.from_numpy(np.where(xq >= 0, xq, xq * np.float32(0.1))).to(tdt).float().numpy()
+        ref += ref_tapped_conv(xa, wq, bias, taps, out_stride=u, out_off=p)      # other phases' rows stay 0
+    tol = 2e-5 if dtype == "float32" else 4e-3
+    assert np.abs(out.float().cpu().numpy() - ref).max() <= tol
+    # MRF: acc = v0; acc += v1; out = (acc + v2) / 3   (reference model.py:161-167)
+    acc = torch.zeros((B, rows, cout), dtype=torch.float32, device="cuda")
+    ws = [(rng.standard_normal((3, cin, cout)) / 14).astype(np.float32) for _ in range(3)]
+    taps = [-1, 0, 1]
+    tapped_conv(x, ws[0], bias, taps, engine=engine, acc=acc, mrf_mode=1)
+    tapped_conv(x, ws[1], bias, taps, engine=engine, acc=acc, mrf_mode=2)
+    fin = tapped_conv(x, ws[2], bias, taps, engine=engine, acc=acc, mrf_mode=3, mrf_div=3.0)
+    xq = x.float().cpu().numpy()
+    tot = sum(ref_tapped_conv(xq, w if engine == "ffma" else torch.from_numpy(w).to(tdt).float().numpy(), bias, taps) for w in ws) / 3
+    assert np.abs(fin.float().cpu().numpy() - tot).max() <= tol
