@@ -47,7 +47,7 @@ __host__ __device__ constexpr uint32_t tmem_cols(int need) { return need <= 32 ?
 __host__ __device__ inline int slab_rows_padded(int rows, int chunks) {
   // bank-conflict-free staging stores: R_pad mod 8 == 1 when a quarter-warp spans 8 chunks,
   // 2 / 4 when a row has only 4 / 2 chunks
-  const int want = chunks >= 8 ? 1 : (8 / chunks);
+  const int want = chunks >= 8 ? 1 : (chunks >= 2 ? 8 / chunks : 0);
   int r = rows;
   while (r % 8 != want) ++r;
   return r;
@@ -381,16 +381,15 @@ bool umma_supported(int c_in, int c_out, int ntaps, int span) {
   if (ntaps < 1 || ntaps > kMaxTaps || span < 0 || span > kMaxSpan) return false;
   const int n = kNTile(c_out);
   if (c_out % n) return false;
-  {
-    const int mblk = kMBlk(c_in, n), nst = kStages(c_in, n), kb = kKBlk(c_in);
-    const size_t smem = (size_t)nst * n * kb * 2 + (size_t)(c_in / 8) * slab_rows_padded(mblk * 128 + span, c_in / 8) * 16 +
-                        n * sizeof(float) + (2 * nst + 2) * sizeof(uint64_t) + 16;
-    if (smem > kMaxSmem) return false;
-  }
   static const int combos[][2] = {{512, 256}, {256, 256}, {128, 256}, {256, 128}, {128, 128}, {128, 64},
                                   {64, 64}, {64, 32}, {32, 32}, {32, 16}, {16, 16}};
-  for (auto& c : combos) if (c[0] == c_in && c[1] == n) return true;
-  return false;
+  bool listed = false;
+  for (auto& c : combos) if (c[0] == c_in && c[1] == n) listed = true;
+  if (!listed) return false;          // (also keeps slab_rows_padded away from c_in < 16)
+  const int mblk = kMBlk(c_in, n), nst = kStages(c_in, n), kb = kKBlk(c_in);
+  const size_t smem = (size_t)nst * n * kb * 2 + (size_t)(c_in / 8) * slab_rows_padded(mblk * 128 + span, c_in / 8) * 16 +
+                      n * sizeof(float) + (2 * nst + 2) * sizeof(uint64_t) + 16;
+  return smem <= kMaxSmem;
 }
 
 size_t umma_packed_weight_bytes(int c_in, int c_out, int ntaps) { return (size_t)ntaps * c_in * c_out * 2; }
