@@ -43,6 +43,8 @@ struct Layer {
   float* d_bias = nullptr;
   void* d_wpk = nullptr;
   bool use_umma = false;
+  bool use_tc = false;      // persistent tcgen05 kernel (conv_tc.cu): one launch per layer, phases = variants
+  std::vector<size_t> tc_off;   // byte offset of each phase's packed weights in d_wpk
 };
 
 thread_local std::string g_create_error;
@@ -71,6 +73,8 @@ struct hfg_ctx {
   float* d_mel = nullptr; size_t d_mel_bytes = 0;
   float* d_audio = nullptr; size_t d_audio_bytes = 0;
   bool force_ffma = false;
+  int tc_kernel = 1;        // 1 = persistent kernel (conv_tc.cu), 0 = first-generation per-tile kernel (conv_umma.cu)
+  bool need_acc = true, need_sum = false;
 };
 
 namespace {
@@ -208,18 +212,20 @@ Sizes compute_sizes(const hfg_ctx* h, int B, int T) {
   return s;
 }
 
-struct Workspace { char* U; char* P; char* Q; char* T; float* ACC; char* MEL; };
+struct Workspace { char* U; char* P; char* Q; char* T; char* S; float* ACC; char* MEL; };
 
 size_t workspace_layout(const hfg_ctx* h, int B, int T, char* base, Workspace* w) {
   const Sizes s = compute_sizes(h, B, T);
   const size_t ab = align_up(s.max_act_elems * act_bytes(h->act), 256);
-  const size_t accb = align_up(s.max_act_elems * sizeof(float), 256);
+  const size_t accb = h->need_acc ? align_up(s.max_act_elems * sizeof(float), 256) : 0;
+  const size_t sumb = h->need_sum ? ab : 0;
   const size_t melb = align_up(s.mel_pad_elems * act_bytes(h->act), 256);
   size_t off = 0;
   auto take = [&](size_t n) { char* p = base ? base + off : nullptr; off += n; return p; };
   char* U = take(ab); char* P = take(ab); char* Q = take(ab); char* Tt = take(ab);
+  char* S = take(sumb);
   float* ACC = (float*)take(accb); char* MEL = take(melb);
-  if (w) { w->U = U; w->P = P; w->Q = Q; w->T = Tt; w->ACC = ACC; w->MEL = MEL; }
+  if (w) { w->U = U; w->P = P; w->Q = Q; w->T = Tt; w->S = S; w->ACC = ACC; w->MEL = MEL; }
   return off;
 }
 
@@ -229,9 +235,31 @@ struct Runner {
   int B;
   cudaError_t status = cudaSuccess;
 
+  // persistent tcgen05 kernel: the whole layer (all phases of a transposed conv) in one launch
+  void conv_tc(const Layer& L, const void* x, int x_rows, void* out, float in_slope, const void* res,
+               const void* res2, float out_scale) {
+    if (status != cudaSuccess) return;
+    const int u = L.transposed ? L.stride : 1;
+    TcArgs a{};
+    a.x = x; a.out = out; a.res = res; a.res2 = res2; a.bias = L.d_bias;
+    a.B = B; a.x_rows = x_rows; a.n_q = x_rows; a.out_rows = x_rows * u; a.out_stride = u;
+    a.c_in = L.cin_pad; a.c_out = L.cout;
+    a.in_slope = in_slope; a.out_scale = out_scale; a.out_slope = 1.0f;
+    a.nvar = (int)L.phases.size();
+    for (int p = 0; p < a.nvar; ++p) {
+      const Phase& ph = L.phases[p];
+      a.var[p].w = (const char*)L.d_wpk + ph.wpk_off;
+      a.var[p].ntaps = ph.ntaps; a.var[p].out_off = p;
+      for (int j = 0; j < ph.ntaps; ++j) a.var[p].tap_off[j] = ph.tap_off[j];
+    }
+    status = launch_conv_tc(a, h->act, s, nullptr);
+    h->launches++;
+  }
+
   void conv(const Layer& L, const void* x, int x_rows, void* out, float in_slope, const void* res,
             float* acc, int mrf_mode) {
     if (status != cudaSuccess) return;
+    if (L.use_tc) { conv_tc(L, x, x_rows, out, in_slope, res, nullptr, 1.0f); return; }
     const int u = L.transposed ? L.stride : 1;
     for (int p = 0; p < (int)L.phases.size(); ++p) {
       const Phase& ph = L.phases[p];
@@ -251,6 +279,21 @@ struct Runner {
       }
       h->launches++;
       if (status != cudaSuccess) return;
+    }
+  }
+
+  // last conv of resblock j of a stage: residual add + MRF sum / average (reference model.py:79,111,161-167).
+  // tcgen05 path: the running sum xs lives in a 16-bit buffer `sum` (res2); direct path: fp32 `acc`.
+  void conv_mrf(const Layer& L, const void* x, int x_rows, void* out, void* sum, float in_slope, const void* res,
+                float* acc, int j, int nk) {
+    if (L.use_tc) {
+      if (nk == 1) conv_tc(L, x, x_rows, out, in_slope, res, nullptr, 1.0f);
+      else if (j == 0) conv_tc(L, x, x_rows, sum, in_slope, res, nullptr, 1.0f);
+      else if (j < nk - 1) conv_tc(L, x, x_rows, sum, in_slope, res, sum, 1.0f);
+      else conv_tc(L, x, x_rows, out, in_slope, res, sum, 1.0f / (float)nk);
+    } else {
+      const int mode = nk == 1 ? MRF_NONE : (j == 0 ? MRF_FIRST : (j == nk - 1 ? MRF_FINAL : MRF_ADD));
+      conv(L, x, x_rows, out, in_slope, res, acc, mode);
     }
   }
 };
@@ -288,22 +331,22 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
     for (int j = 0; j < c.num_kernels; ++j) {                   // model.py:162-166
       const int n = i * c.num_kernels + j;
       const int nd = c.num_dilations[j];
-      const int mrf_last = c.num_kernels == 1 ? MRF_NONE : (j == 0 ? MRF_FIRST : (j == c.num_kernels - 1 ? MRF_FINAL : MRF_ADD));
       const char* rcur = w.U;
       for (int m = 0; m < nd; ++m) {
         const bool last = (m == nd - 1);
         char* rnext = (rcur == w.P) ? w.Q : w.P;
-        const int mode = last ? mrf_last : MRF_NONE;
-        if (last && (mode == MRF_FINAL || mode == MRF_NONE)) next_x = rnext;
+        if (last && j == c.num_kernels - 1) next_x = rnext;
         const std::string base = "resblocks." + std::to_string(n);
         if (c.resblock == 1) {                                   // ResBlock1.call model.py:71-80
           const Layer& c1 = h->layers[h->index[base + ".convs1." + std::to_string(m)]];
           const Layer& c2 = h->layers[h->index[base + ".convs2." + std::to_string(m)]];
           r.conv(c1, rcur, L, w.T, kSlope, nullptr, nullptr, MRF_NONE);
-          r.conv(c2, w.T, L, rnext, kSlope, rcur, w.ACC, mode);
+          if (last) r.conv_mrf(c2, w.T, L, rnext, w.S, kSlope, rcur, w.ACC, j, c.num_kernels);
+          else r.conv(c2, w.T, L, rnext, kSlope, rcur, nullptr, MRF_NONE);
         } else {                                                 // ResBlock2.call model.py:106-112
           const Layer& c1 = h->layers[h->index[base + ".convs." + std::to_string(m)]];
-          r.conv(c1, rcur, L, rnext, kSlope, rcur, w.ACC, mode);
+          if (last) r.conv_mrf(c1, rcur, L, rnext, w.S, kSlope, rcur, w.ACC, j, c.num_kernels);
+          else r.conv(c1, rcur, L, rnext, kSlope, rcur, nullptr, MRF_NONE);
         }
         rcur = rnext;
       }
@@ -422,8 +465,10 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
     }
     int cin_mma = L.cin;
     if (L.name == "conv_pre") cin_mma = (int)align_up((size_t)L.cin, 64);
-    L.use_umma = !is_post && h->act != ACT_F32 && !h->force_ffma && umma_supported(cin_mma, L.cout, max_taps, max_span);
-    if (L.use_umma) L.cin_pad = cin_mma;
+    const bool tensor_ok = !is_post && h->act != ACT_F32 && !h->force_ffma;
+    L.use_tc = tensor_ok && h->tc_kernel == 1 && (int)L.phases.size() <= kMaxVariants && tc_supported(cin_mma, L.cout, max_taps, max_span);
+    L.use_umma = tensor_ok && !L.use_tc && umma_supported(cin_mma, L.cout, max_taps, max_span);
+    if (L.use_umma || L.use_tc) L.cin_pad = cin_mma;
     // fp32 weights per phase, [ntaps][cin_pad][cout]
     std::vector<float> w32;
     for (Phase& ph : L.phases) {
@@ -440,11 +485,14 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
           memcpy(&w32[ph.w32_off + ((size_t)t * L.cin_pad + ci) * L.cout], &w[((size_t)j * L.cin + ci) * L.cout], sizeof(float) * L.cout);
       }
     }
-    if (L.use_umma) {
+    if (L.use_umma || L.use_tc) {
       size_t total = 0;
       for (Phase& ph : L.phases) { ph.wpk_off = total; total += align_up(umma_packed_weight_bytes(L.cin_pad, L.cout, ph.ntaps), 256); }
       std::vector<char> pk(total);
-      for (Phase& ph : L.phases) umma_pack_weights(&w32[ph.w32_off], ph.ntaps, L.cin_pad, L.cout, h->act, pk.data() + ph.wpk_off);
+      for (Phase& ph : L.phases) {
+        if (L.use_tc) tc_pack_weights(&w32[ph.w32_off], ph.ntaps, L.cin_pad, L.cout, h->act, pk.data() + ph.wpk_off);
+        else umma_pack_weights(&w32[ph.w32_off], ph.ntaps, L.cin_pad, L.cout, h->act, pk.data() + ph.wpk_off);
+      }
       CUDA_TRY(h, cudaMalloc(&L.d_wpk, total));
       CUDA_TRY(h, cudaMemcpy(L.d_wpk, pk.data(), total, cudaMemcpyHostToDevice));
     } else {
@@ -456,6 +504,9 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
     CUDA_TRY(h, cudaMalloc((void**)&L.d_bias, bias.size() * sizeof(float)));
     CUDA_TRY(h, cudaMemcpy(L.d_bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
   }
+  h->need_acc = false; h->need_sum = false;
+  for (const Layer& L : h->layers)
+    if (!L.transposed && L.name != "conv_pre" && L.name != "conv_post") { if (L.use_tc) h->need_sum = true; else h->need_acc = true; }
   if (h->events.empty()) {
     h->events.resize(c.num_upsamples + 3);
     for (auto& ev : h->events) CUDA_TRY(h, cudaEventCreate(&ev));
@@ -546,6 +597,7 @@ int hfg_set_option(hfg_handle h, const char* key, long long value) {
   if (k == "micro_batch") { if (value < 0) return fail(h, HFG_ERR_INVALID, "micro_batch must be >= 0"); h->micro_batch = (int)value; return HFG_OK; }
   if (k == "stage_timing") { h->stage_timing = value != 0; return HFG_OK; }
   if (k == "force_ffma") { h->force_ffma = value != 0; h->finalized = false; return HFG_OK; }
+  if (k == "tc_kernel") { h->tc_kernel = value != 0; h->finalized = false; return HFG_OK; }
   return fail(h, HFG_ERR_INVALID, "unknown option '%s'", key);
 }
 
@@ -589,7 +641,25 @@ int hfg_op_tapped_conv(int act, int use_umma, const void* x_dev, int B, int x_ro
   CUDA_TRY(nullptr, cudaMemcpy(d_bias, bias.data(), bias.size() * 4, cudaMemcpyHostToDevice));
   a.bias = d_bias;
   cudaError_t e;
-  if (use_umma) {
+  if (use_umma == 2) {
+    if (act == ACT_F32 || !tc_supported(c_in, c_out, ntaps, mx - mn)) {
+      cudaFree(d_bias);
+      return fail(nullptr, HFG_ERR_UNSUPPORTED, "persistent tcgen05 kernel does not cover c_in=%d c_out=%d ntaps=%d span=%d act=%d", c_in, c_out, ntaps, mx - mn, act);
+    }
+    if (mrf_mode != MRF_NONE) { cudaFree(d_bias); return fail(nullptr, HFG_ERR_UNSUPPORTED, "use res2/out_scale through the engine for MRF on the persistent kernel"); }
+    const size_t nb = tc_packed_weight_bytes(c_in, c_out, ntaps);
+    std::vector<char> pk(nb);
+    tc_pack_weights(w_host, ntaps, c_in, c_out, (ActType)act, pk.data());
+    CUDA_TRY(nullptr, cudaMalloc(&d_w, nb));
+    CUDA_TRY(nullptr, cudaMemcpy(d_w, pk.data(), nb, cudaMemcpyHostToDevice));
+    TcArgs t{};
+    t.x = x_dev; t.out = out_dev; t.res = res_dev; t.res2 = nullptr; t.bias = d_bias;
+    t.B = B; t.x_rows = x_rows; t.n_q = x_rows; t.out_rows = x_rows * out_stride; t.out_stride = out_stride;
+    t.c_in = c_in; t.c_out = c_out; t.in_slope = in_slope; t.out_scale = 1.0f; t.out_slope = 1.0f;
+    t.nvar = 1; t.var[0].w = d_w; t.var[0].ntaps = ntaps; t.var[0].out_off = out_off;
+    for (int j = 0; j < ntaps; ++j) t.var[0].tap_off[j] = tap_off[j];
+    e = launch_conv_tc(t, (ActType)act, s, nullptr);
+  } else if (use_umma) {
     if (act == ACT_F32 || !umma_supported(c_in, c_out, ntaps, mx - mn)) {
       cudaFree(d_bias);
       return fail(nullptr, HFG_ERR_UNSUPPORTED, "tcgen05 kernel does not cover c_in=%d c_out=%d ntaps=%d span=%d act=%d", c_in, c_out, ntaps, mx - mn, act);

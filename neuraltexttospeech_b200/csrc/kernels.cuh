@@ -68,4 +68,42 @@ size_t umma_packed_weight_bytes(int c_in, int c_out, int ntaps);
 void umma_pack_weights(const float* w, int ntaps, int c_in, int c_out, ActType act, void* dst_host);
 cudaError_t launch_conv_umma(const ConvArgs& a, ActType act, cudaStream_t s);
 
+
+// ---------------------------------------------------------------- persistent tcgen05 kernel (conv_tc.cu)
+// One launch = one layer: every output phase ("variant") of a Conv1DTranspose, or the single
+// variant of a Conv1D.   out[b, q*out_stride + var.out_off, co] =
+//     lrelu_out( (bias[co] + sum_j sum_ci lrelu_in(x[b, q + var.tap_off[j], ci]) * W_var[j][ci][co]
+//                 + res[...] + res2[...]) * out_scale )
+// res / res2 are indexed like out (16-bit, may be NULL): res is the ResBlock skip connection
+// (reference model.py:79,111), res2 the running MRF sum xs (model.py:161-166); out_scale = 1/num_kernels
+// on the last resblock (model.py:167).
+constexpr int kMaxVariants = 8;
+struct TcVariant {
+  const void* w;        // packed weights of this variant (see tc_pack_weights)
+  int ntaps;
+  int out_off;
+  int tap_off[kMaxTaps];
+};
+struct TcArgs {
+  const void* x;
+  void* out;
+  const void* res;
+  const void* res2;
+  const float* bias;
+  int B, x_rows, n_q, out_rows, out_stride;
+  int c_in, c_out;
+  float in_slope, out_scale, out_slope;
+  int nvar;
+  TcVariant var[kMaxVariants];
+};
+struct TcConfig {       // tile configuration chosen for (c_in, c_out); see conv_tc.cu
+  int n, mb, ks, kbw, nst, nsl, pw;
+};
+bool tc_config(int c_in, int c_out, TcConfig* cfg);
+bool tc_supported(int c_in, int c_out, int ntaps, int span);
+size_t tc_packed_weight_bytes(int c_in, int c_out, int ntaps);
+// host-side repack of fp32 [ntaps][c_in][c_out] into the kernel's smem-image weight stages (16-bit)
+void tc_pack_weights(const float* w, int ntaps, int c_in, int c_out, ActType act, void* dst_host);
+cudaError_t launch_conv_tc(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out);
+
 }  // namespace hfg

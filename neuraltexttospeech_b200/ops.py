@@ -30,7 +30,7 @@ def tapped_conv(x, w: np.ndarray, bias: np.ndarray, tap_off: Sequence[int], *, e
     if out is None:
         out = torch.zeros((B, rows * out_stride, c_out), dtype=x.dtype, device=x.device)
     taps = (C.c_int * ntaps)(*[int(t) for t in tap_off])
-    rc = lib.hfg_op_tapped_conv(act, 1 if engine == "umma" else 0, C.c_void_p(x.data_ptr()), B, rows, c_in,
+    rc = lib.hfg_op_tapped_conv(act, {"ffma": 0, "umma": 1, "tc": 2}[engine], C.c_void_p(x.data_ptr()), B, rows, c_in,
                                 w.ctypes.data_as(C.c_void_p), bias.ctypes.data_as(C.c_void_p), c_out, ntaps, taps,
                                 out_stride, out_off, float(in_slope),
                                 C.c_void_p(res.data_ptr()) if res is not None else None,

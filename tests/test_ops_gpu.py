@@ -40,7 +40,7 @@ SHAPES = [  # (c_in, c_out, taps, B, rows)
 
 
 @pytest.mark.parametrize("cin,cout,taps,B,rows", SHAPES)
-@pytest.mark.parametrize("engine,dtype", [("ffma", "float32"), ("umma", "float16"), ("umma", "bfloat16"), ("ffma", "float16")])
+@pytest.mark.parametrize("engine,dtype", [("ffma", "float32"), ("tc", "float16"), ("tc", "bfloat16"), ("umma", "float16"), ("umma", "bfloat16"), ("ffma", "float16")])
 def test_tapped_conv(cin, cout, taps, B, rows, engine, dtype):
     import torch
     from neuraltexttospeech_b200.ops import tapped_conv
@@ -59,7 +59,7 @@ def test_tapped_conv(cin, cout, taps, B, rows, engine, dtype):
     ref = ref_tapped_conv(xq, wq, bias, taps, in_slope=0.1, res=rq)
     if dtype != "float32":                                # the kernel rounds the activated input to 16 bit
         xa = torch.from_numpy(np.where(xq >= 0, xq, xq * np.float32(0.1))).to(tdt).float().numpy()
-        if engine == "umma":
+        if engine in ("umma", "tc"):
             ref = ref_tapped_conv(xa, wq, bias, taps, in_slope=1.0, res=rq)
     out = tapped_conv(xt, w, bias, taps, engine=engine, in_slope=0.1, res=rt).float().cpu().numpy()
     tol = {"float32": 2e-5, "float16": 4e-3, "bfloat16": 3e-2}[dtype]   # output rounding of O(1) values
