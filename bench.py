@@ -139,6 +139,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="v1_b64x10s", choices=sorted(CONFIGS))
     ap.add_argument("--precision", default="fp16", choices=["fp32", "fp16", "bf16"])
+    ap.add_argument("--micro-batch", type=int, default=16)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
@@ -187,7 +188,7 @@ def main():
     # ---------------- device-resident measurement ("value")
     mel_dev = torch.from_numpy(mel_np).cuda()
     out_dev = torch.empty((B, L, 1), dtype=torch.float32, device="cuda")
-    mb = 16                                  # utterances per forward call: keeps the workspace modest
+    mb = max(1, min(args.micro_batch, B))    # utterances per forward call: keeps the workspace modest
     stream = torch.cuda.current_stream()
 
     def step_device():
@@ -216,6 +217,7 @@ def main():
         mel_pin = torch.from_numpy(mel_np).pin_memory()
         out_pin = torch.empty((B, L, 1), dtype=torch.float32).pin_memory()
         mel_h, out_h = mel_pin.numpy(), out_pin.numpy()
+        gen.set_option("micro_batch", mb)
         for _ in range(2):
             gen._call_host(mel_h, out_h)
         barrier()

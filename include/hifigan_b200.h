@@ -102,6 +102,10 @@ int hfg_forward_host(hfg_handle h, const float* mel_host, int B, int T, float* a
 /* Utterances per micro-batch used by hfg_forward_host (default 16); 0 = whole batch. */
 int hfg_set_option(hfg_handle h, const char* key, long long value);
 
+/* Which kernel family each layer was bound to by hfg_finalize_weights: lines "<layer>:<tc|ffma|post>\n"
+ * (tc = persistent tcgen05 kernel, ffma = direct fp32-accumulate kernel, post = conv_post+tanh kernel). */
+int hfg_layer_engines(hfg_handle h, char* buf, size_t cap);
+
 /* Kernels launched by the last hfg_forward / hfg_forward_host on this handle. */
 int hfg_last_launch_count(hfg_handle h, long long* out);
 
@@ -109,15 +113,21 @@ int hfg_last_launch_count(hfg_handle h, long long* out);
  * out[0]=conv_pre, out[1+i]=stage i (ups[i] + its resblocks), out[1+n]=conv_post. Returns count via n. */
 int hfg_stage_times_ms(hfg_handle h, float* out, int* n);
 
-/* Operator-level entry: ONE tapped convolution (the building block of every layer above),
- *   out[b, q*out_stride + out_off, co] = epi(bias[co] + sum_j sum_ci lrelu(x[b, q + tap_off[j], ci], in_slope) * w[j][ci][co])
- * A dilated Conv1D (reference model.py:26-66) is out_stride=1, tap_off[j] = j*d - pad_left; one phase p of a
- * Conv1DTranspose (model.py:131-136) is out_stride=u, out_off=p.  act: 0 fp32, 1 fp16, 2 bf16 activations;
- * use_umma: 1 = tcgen05 kernel, 0 = direct FFMA kernel; w_host fp32 [ntaps][c_in][c_out]; res/acc may be NULL;
- * mrf_mode 0 none, 1 acc=val, 2 acc+=val, 3 out=(acc+val)/mrf_div.  Synchronous; for parity tests. */
-int hfg_op_tapped_conv(int act, int use_umma, const void* x_dev, int B, int x_rows, int c_in,
+/* Operator-level entry: ONE tapped convolution (the building block of every layer above); synchronous, for
+ * parity tests.  A dilated Conv1D (reference model.py:26-66) is out_stride=1, tap_off[j] = j*d - pad_left; one
+ * phase p of a Conv1DTranspose (model.py:131-136) is out_stride=u, out_off=p.  act: 0 fp32, 1 fp16, 2 bf16
+ * activations; w_host fp32 [ntaps][c_in][c_out]; res / res2 / acc may be NULL.
+ *   engine 0, direct FFMA kernel:
+ *     v = bias[co] + sum_j sum_ci lrelu(x[b, q + tap_off[j], ci], in_slope) * w[j][ci][co] + res[...]
+ *     mrf_mode 0: out = lrelu(v, out_slope); 1: acc = v; 2: acc += v; 3: out = lrelu((acc + v) / mrf_div, out_slope)
+ *   engine 1, persistent tcgen05 kernel (16-bit only; x is stored already activated, in_slope must be 1):
+ *     v = bias[co] + sum_j sum_ci x[b, q + tap_off[j], ci] * w[j][ci][co] + unact(res[...]) + res2[...]
+ *     out = lrelu(v * out_scale, out_slope),   unact(y) = y >= 0 ? y : y * res_inv
+ *   out is indexed [b, q*out_stride + out_off, co]; res, res2, acc like out. */
+int hfg_op_tapped_conv(int act, int engine, const void* x_dev, int B, int x_rows, int c_in,
                        const float* w_host, const float* bias_host, int c_out, int ntaps, const int* tap_off,
-                       int out_stride, int out_off, float in_slope, const void* res_dev, float* acc_dev,
+                       int out_stride, int out_off, float in_slope, const void* res_dev, float res_inv,
+                       const void* res2_dev, float out_scale, float out_slope, float* acc_dev,
                        int mrf_mode, float mrf_div, void* out_dev, void* stream);
 
 /* Pinned host memory helpers for callers without a CUDA runtime binding of their own. */

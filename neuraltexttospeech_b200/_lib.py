@@ -45,11 +45,12 @@ SIGNATURES = {
     "hfg_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "hfg_forward_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "hfg_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_longlong]),
+    "hfg_layer_engines": (C.c_int, [C.c_void_p, C.c_char_p, C.c_size_t]),
     "hfg_last_launch_count": (C.c_int, [C.c_void_p, C.POINTER(C.c_longlong)]),
     "hfg_stage_times_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int)]),
     "hfg_op_tapped_conv": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
-                                     C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_int, C.c_float, C.c_void_p,
-                                     C.c_void_p, C.c_int, C.c_float, C.c_void_p, C.c_void_p]),
+                                     C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_float,
+                                     C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_int, C.c_float, C.c_void_p, C.c_void_p]),
     "hfg_host_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),
     "hfg_host_free": (C.c_int, [C.c_void_p]),
     "hfg_last_error": (C.c_char_p, [C.c_void_p]),

@@ -2,7 +2,7 @@
 //
 //  * conv_ffma_kernel : generic tapped conv, fp32 accumulate.  It is the whole forward pass in
 //    the fp32 validation mode (north star: <=1e-5 of the fp32 reference) and the fallback for
-//    shapes the tcgen05 kernel does not cover (V2's 16/8-channel stages).
+//    shapes the tcgen05 kernel (conv_tc.cu) does not cover (V2's 16/8-channel stages).
 //  * conv_post_kernel : lrelu(0.3) -> Conv1D(1, 7) -> tanh  (reference HiFiGAN_TF/model.py:169-171),
 //    a pure bandwidth kernel (C_out = 1), shared by all precisions.
 //  * cast_pad_kernel  : fp32 mel -> 16-bit, channel-padded, for the tensor-core conv_pre.
@@ -145,6 +145,10 @@ conv_ffma_kernel(const ConvArgs a) {
         const float4 s = *reinterpret_cast<const float4*>(a.acc + idx);
         v.x = (s.x + v.x) / a.mrf_div; v.y = (s.y + v.y) / a.mrf_div;
         v.z = (s.z + v.z) / a.mrf_div; v.w = (s.w + v.w) / a.mrf_div;
+      }
+      if (a.out_slope != 1.0f) {
+        v.x = lrelu(v.x, a.out_slope); v.y = lrelu(v.y, a.out_slope);
+        v.z = lrelu(v.z, a.out_slope); v.w = lrelu(v.w, a.out_slope);
       }
       Act4<T>::store(reinterpret_cast<T*>(a.out) + idx, v);
     }

@@ -1,31 +1,36 @@
-// Persistent, warp-specialised tcgen05 / TMEM implicit-GEMM kernel for every 16-bit conv layer of
-// the HiFi-GAN generator (ResBlock1/2 dilated Conv1D chains, polyphase Conv1DTranspose, conv_pre):
+// Persistent, warp-specialised, TMA-fed tcgen05 / TMEM implicit-GEMM kernel for every 16-bit conv layer
+// of the HiFi-GAN generator (ResBlock1/2 dilated Conv1D chains, polyphase Conv1DTranspose, conv_pre):
 // reference HiFiGAN_TF/model.py:71-80, 106-112, 156-167.  sm_100a only.
 //
-// One launch = one layer.  The layer is cut into tiles (utterance b, MB*128 output rows, output
-// phase "variant", N output channels); CTAs are persistent and walk the tile list with a static
-// stride.  Per tile
-//     D[q, co] = sum_j sum_ci lrelu(x[b, q + tap_off[j], ci]) * W[j][ci][co]
-// runs on the tensor cores as sum over (K-slice, tap) of [128 x KS] x [KS x N] MMAs:
+// Storage convention of the 16-bit path: every activation tensor in HBM is stored ALREADY ACTIVATED for
+// its consumer, y = leaky_relu(x, slope) (the reference applies the activation on the consumer side,
+// model.py:73,76,108,159,169).  Where the raw value is needed again -- the ResBlock skip connection
+// x = xt + x, model.py:79,111 -- it is recovered exactly as x = y >= 0 ? y : y / slope.  This is what
+// lets the activation slab go from HBM to the tensor core without passing through registers.
 //
-//   loader warps 0-3   global -> regs -> leaky-relu -> smem, one K-slice (KS input channels) of the
-//                      activation slab [MB*128 + span rows] at a time into an NSL-deep ring, in the
-//                      no-swizzle K-major core-matrix layout  smem[(chunk * R_pad + row) * 16 B]
-//                      (chunk = 8 channels).  Tap j of the dilated conv is the SAME slab addressed at
-//                      row offset tap_off[j]-min_off: no im2col, no per-tap reload; rows outside the
-//                      utterance are zero = TF's zero padding (applied after the activation, lrelu(0)=0).
-//   producer warp 4    streams host-prepacked weight stages [KBW/8 chunks][N rows][16 B] through an
-//                      NST-deep ring with cp.async.bulk + mbarrier complete_tx.
-//   MMA warp 5         one thread issues tcgen05.mma (cta_group::1, kind::f16, M=128, N, K=16) into
-//                      TMEM accumulators (NACC buffers of MB x N columns); tcgen05.commit releases
-//                      weight stages / slab slices and hands the accumulator to the epilogue.
-//   epilogue warps 6-9 tcgen05.ld (one TMEM lane quarter each, thread = output row) -> +bias
-//                      -> +residual (model.py:79,111) -> +MRF partial sum, *1/num_kernels
-//                      (model.py:161-167) -> 16-bit -> the thread's private staging row in smem
-//                      -> cp.async.bulk smem->global of that row (full-line writes, no cross-thread sync).
+// One launch = one layer.  The layer is cut into tiles (utterance b, MB*128 output rows, output phase
+// "variant", N output channels); CTAs are persistent and walk the tile list with a static stride.
+//     D[q, co] = sum_j sum_ci y[b, q + tap_off[j], ci] * W[j][ci][co]
+// runs as sum over (K-slice, tap) of [128 x KS] x [KS x N] MMAs:
 //
-// Loads of tile i+1, MMAs of tile i and the epilogue of tile i-1 overlap (slab ring + TMEM double
-// buffering where 2*MB*N <= 512 columns).
+//   warp 0  slab producer: TMA tensor loads (cp.async.bulk.tensor.3d, SWIZZLE_128B/64B/32B, out-of-bounds
+//           rows zero-filled = TF's zero padding, utterances never bleed into each other) of one K-slice
+//           (KS input channels) of the halo tile [MB*128 + span rows] into an NSL-deep ring.  Tap j of the
+//           dilated conv is the SAME slab addressed at row offset tap_off[j]-min_off (the swizzle is a
+//           function of the absolute smem address, so an unaligned descriptor start is legal): no im2col.
+//   warp 1  weight producer: host-prepacked weight stages [KBW/8 chunks][N rows][16 B] through an NST-deep
+//           ring with cp.async.bulk + mbarrier complete_tx.
+//   warp 2  MMA issuer: one thread issues tcgen05.mma (cta_group::1, kind::f16, M=128, N, K=16) into TMEM
+//           accumulators (NACC buffers of MB x N columns); tcgen05.commit releases weight stages / slab
+//           slices and hands the accumulator to the epilogue.
+//   warp 3  staging producer: TMA-loads the residual tile of each epilogue pass into the staging ring.
+//   warps 4-7 epilogue: tcgen05.ld (one TMEM lane quarter each, thread = output row) -> +bias -> +residual
+//           (model.py:79,111) -> +MRF partial sum, *1/num_kernels (model.py:161-167) -> activation for the
+//           consumer -> 16-bit, in place in the swizzled staging tile -> TMA tensor store.
+//
+// Loads of tile i+1, MMAs of tile i and the epilogue of tile i-1 overlap (slab ring, TMEM double
+// buffering where 2*MB*N <= 512 columns, NSTG-deep staging ring).
+#include <cuda.h>
 #include <cstdio>
 #include <cstring>
 #include <type_traits>
@@ -37,7 +42,7 @@ namespace hfg {
 
 namespace {
 
-constexpr int kTcThreads = 320;
+constexpr int kTcThreads = 256;
 constexpr int kTcMaxSpan = 96;       // largest max_off - min_off supported (V1: 50, V3: 72)
 constexpr size_t kTcMaxSmem = 227 * 1024;
 
@@ -132,12 +137,36 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[32]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+__device__ __forceinline__ void tma_load_3d(void* dst_smem, const CUtensorMap* tm, int c0, int c1, int c2, uint64_t* bar) {
+  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+               ::"r"(smem_u32(dst_smem)), "l"(tm), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(void* dst_smem, const CUtensorMap* tm, int c0, int c1, int c2, int c3, uint64_t* bar) {
+  asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
+               ::"r"(smem_u32(dst_smem)), "l"(tm), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* tm, const void* src_smem, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+               ::"l"(tm), "r"(smem_u32(src_smem)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(tm) : "memory");
+}
+
 // smem matrix descriptor, no swizzle, K-major (cute::UMMA::SmemDescriptor bit layout):
 //  [0,14) start>>4 | [16,30) LBO>>4 (stride between the two 16-byte K chunks of one MMA)
 //  [32,46) SBO>>4 (stride between 8-row groups) | [46,48) version=1 | [61,64) layout=0 (none)
 __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
   return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) |
          ((uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32) | (1ull << 46);
+}
+// K-major operand in a TMA-swizzled tile whose rows are ROWB = 128 / 64 / 32 bytes: 8-row atoms of 8*ROWB bytes
+// (SBO), layout type 2 / 4 / 6, base_offset 0 (verified on B200: the XOR pattern follows the absolute smem
+// address, so `saddr` may sit at any row of the tile).
+template <int ROWB>
+__device__ __forceinline__ uint64_t make_desc_sw(uint32_t saddr) {
+  constexpr uint64_t LT = ROWB == 128 ? 2 : (ROWB == 64 ? 4 : 6);
+  return (uint64_t)((saddr & 0x3FFFF) >> 4) | (1ull << 16) | ((uint64_t)((8 * ROWB) >> 4) << 32) | (1ull << 46) | (LT << 61);
 }
 // instruction descriptor, kind::f16 (cute::UMMA::InstrDescriptor): D=f32, A/B = f16 or bf16, both K-major, M=128
 __host__ __device__ constexpr uint32_t make_idesc(int n, bool bf16) {
@@ -169,145 +198,128 @@ __device__ __forceinline__ float lrelu_f(float v, float s) { return v >= 0.f ? v
 
 // ------------------------------------------------------------------ shared-memory plan
 struct TcSmemPlan {
-  int r_pad;            // padded slab rows
-  int slice_bytes;      // one K-slice of the slab
+  int slice_rows;       // rows of one K-slice buffer (nbox * box_rows)
+  int slice_bytes;
   int stage_bytes;      // one weight stage
-  int stg_pitch;        // staging row pitch in bytes
-  int off_w, off_stg, off_bias, off_bar;
+  int stg_bytes;        // one staging tile [128 rows][PW * 2 bytes]
+  int off_stg, off_w, off_bias, off_bar;
   int total;
 };
 
-__host__ __device__ inline TcSmemPlan tc_plan(int n, int mb, int ks, int kbw, int nst, int nsl, int pw, int span) {
+__host__ __device__ inline TcSmemPlan tc_plan(int n, int ks, int kbw, int nst, int nsl, int nstg, int slice_rows) {
   TcSmemPlan p;
-  p.r_pad = tc_rows_padded(mb * 128 + span, ks / 8);
-  p.slice_bytes = (ks / 8) * p.r_pad * 16;
+  const int pw = n < 64 ? n : 64;
+  p.slice_rows = slice_rows;
+  p.slice_bytes = slice_rows * ks * 2;            // multiple of the swizzle atom (slice_rows % 8 == 0)
   p.stage_bytes = n * kbw * 2;
-  p.stg_pitch = pw * 2 + 16;
+  p.stg_bytes = 128 * pw * 2;
   int off = nsl * p.slice_bytes;
+  off = (off + 1023) & ~1023;
+  p.off_stg = off; off += nstg * p.stg_bytes;
   off = (off + 127) & ~127;
   p.off_w = off; off += nst * p.stage_bytes;
-  p.off_stg = off; off += 2 * 128 * p.stg_pitch;
   p.off_bias = off; off += n * 4;
   off = (off + 15) & ~15;
-  p.off_bar = off; off += (2 * nsl + 2 * nst + 4) * 8 + 16;
+  p.off_bar = off; off += (2 * nsl + 2 * nst + 2 * nstg + 4) * 8 + 16;
   p.total = off;
   return p;
 }
 
 struct TcKArgs {
-  TcArgs c;
+  const float* bias;
+  const void* res2;
+  int n_q, c_out, has_res;
+  float res_inv, out_scale, out_slope;
+  int nvar;
+  TcVariant var[kMaxVariants];
   int min_off, span;
+  int box_rows, nbox;   // slab slice = nbox TMA boxes of box_rows rows
   int tiles_q, n_tiles, total_tiles;
 };
 
 // ------------------------------------------------------------------ the kernel
-template <typename T, int C_IN, int N, int MB, int KS, int KBW, int NST, int NSL, int PW>
-__global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_constant__ TcKArgs ka) {
+template <typename T, int C_IN, int N, int MB, int KS, int KBW, int NST, int NSL, int NSTG>
+__global__ void __launch_bounds__(kTcThreads, 1)
+conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_res,
+               const __grid_constant__ CUtensorMap tm_out, const __grid_constant__ TcKArgs ka) {
   constexpr int NKS = C_IN / KS;                  // K-slices per tile
   constexpr int NKB = KS / KBW;                   // weight stages per (slice, tap)
-  constexpr int CHS = KS / 8;                     // 16-byte chunks per slab row and slice
+  constexpr int ROWB = KS * 2;                    // bytes per slab row within a slice (= swizzle width)
+  constexpr int PW = N < 64 ? N : 64;             // output columns per epilogue pass
+  constexpr int SROWB = PW * 2;                   // bytes per staging row (= swizzle width)
   constexpr int NACC = (2 * MB * N <= 512) ? 2 : 1;
   constexpr int ACC_COLS = MB * N;
   constexpr uint32_t TMEM_COLS = tc_tmem_cols(NACC * ACC_COLS);
   constexpr uint32_t IDESC = make_idesc(N, std::is_same<T, __nv_bfloat16>::value);
   static_assert(C_IN % KS == 0 && KS % KBW == 0 && KBW % 16 == 0 && N % 16 == 0 && N <= 256, "tile config");
-  static_assert(PW % 16 == 0 && N % PW == 0 && PW <= 128, "staging pass width");
-  const TcArgs& a = ka.c;
-  const TcSmemPlan pl = tc_plan(N, MB, KS, KBW, NST, NSL, PW, ka.span);
+  static_assert(KS == 64 || KS == 32 || KS == 16, "K-slice = one swizzle row");
+  static_assert(N % PW == 0, "pass width");
+  const TcSmemPlan pl = tc_plan(N, KS, KBW, NST, NSL, NSTG, ka.nbox * ka.box_rows);
 
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* slab = smem;
-  uint8_t* wst = smem + pl.off_w;
   uint8_t* stg = smem + pl.off_stg;
+  uint8_t* wst = smem + pl.off_w;
   float* bias_s = reinterpret_cast<float*>(smem + pl.off_bias);
   uint64_t* slice_full = reinterpret_cast<uint64_t*>(smem + pl.off_bar);
   uint64_t* slice_empty = slice_full + NSL;
   uint64_t* w_full = slice_empty + NSL;
   uint64_t* w_empty = w_full + NST;
-  uint64_t* acc_full = w_empty + NST;
+  uint64_t* stg_full = w_empty + NST;
+  uint64_t* stg_empty = stg_full + NSTG;
+  uint64_t* acc_full = stg_empty + NSTG;
   uint64_t* acc_empty = acc_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
   if (tid == 0) {
-    for (int s = 0; s < NSL; ++s) { mbar_init(&slice_full[s], 128); mbar_init(&slice_empty[s], 1); }
+    for (int s = 0; s < NSL; ++s) { mbar_init(&slice_full[s], 1); mbar_init(&slice_empty[s], 1); }
     for (int s = 0; s < NST; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
+    for (int s = 0; s < NSTG; ++s) { mbar_init(&stg_full[s], 1); mbar_init(&stg_empty[s], 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 128); }
     fence_mbar_init();
+    tma_prefetch_desc(&tm_x); tma_prefetch_desc(&tm_res); tma_prefetch_desc(&tm_out);
   }
-  if (warp == 5) tmem_alloc(tmem_slot, TMEM_COLS);
+  if (warp == 2) tmem_alloc(tmem_slot, TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  // tile index -> (utterance b, row tile qt, variant v, channel tile nt); nt fastest so that CTAs that
-  // run concurrently share the activation rows in L2
+  // tile index -> (utterance b, row tile qt, variant v, channel tile nt)
   auto decode = [&](int t, int& b, int& qt, int& v, int& nt) {
     nt = t % ka.n_tiles; t /= ka.n_tiles;
-    v = t % a.nvar; t /= a.nvar;
+    v = t % ka.nvar; t /= ka.nvar;
     qt = t % ka.tiles_q; b = t / ka.tiles_q;
   };
 
-  if (warp < 4) {
-    // ===================== loaders: activation slab slices =====================
-    const float slope = a.in_slope;
-    const int rows = MB * 128 + ka.span;
-    const int pieces = rows * CHS;
-    uint32_t scnt = 0;
-    for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x) {
-      int b, qt, v, nt; decode(t, b, qt, v, nt);
-      const int row_base = qt * (MB * 128) + ka.min_off;
-      const T* __restrict__ xb = reinterpret_cast<const T*>(a.x) + (size_t)b * a.x_rows * C_IN;
-#pragma unroll 1
-      for (int s = 0; s < NKS; ++s, ++scnt) {
-        const int pos = scnt % NSL;
-        mbar_wait(&slice_empty[pos], ((scnt / NSL) & 1) ^ 1);
-        uint8_t* dst = slab + pos * pl.slice_bytes;
-        const T* __restrict__ xs = xb + s * KS;
-        constexpr int U = 8;
-#pragma unroll 1
-        for (int i0 = tid; i0 < pieces; i0 += 128 * U) {
-          uint4 v4[U];
-#pragma unroll
-          for (int u = 0; u < U; ++u) {
-            const int idx = i0 + u * 128;
-            const int c = idx % CHS, r = idx / CHS;
-            const int row = row_base + r;
-            v4[u] = make_uint4(0u, 0u, 0u, 0u);
-            if (idx < pieces && row >= 0 && row < a.x_rows)
-              v4[u] = __ldg(reinterpret_cast<const uint4*>(xs + (size_t)row * C_IN + c * 8));
-          }
-#pragma unroll
-          for (int u = 0; u < U; ++u) {
-            const int idx = i0 + u * 128;
-            if (idx < pieces) {
-              const int c = idx % CHS, r = idx / CHS;
-              uint4 w4 = v4[u];
-              if (slope != 1.0f) {
-                float2 f;
-                f = H2<T>::up(w4.x); w4.x = H2<T>::down(lrelu_f(f.x, slope), lrelu_f(f.y, slope));
-                f = H2<T>::up(w4.y); w4.y = H2<T>::down(lrelu_f(f.x, slope), lrelu_f(f.y, slope));
-                f = H2<T>::up(w4.z); w4.z = H2<T>::down(lrelu_f(f.x, slope), lrelu_f(f.y, slope));
-                f = H2<T>::up(w4.w); w4.w = H2<T>::down(lrelu_f(f.x, slope), lrelu_f(f.y, slope));
-              }
-              *reinterpret_cast<uint4*>(dst + ((size_t)c * pl.r_pad + r) * 16) = w4;
-            }
-          }
+  if (warp == 0) {
+    // ===================== slab producer (TMA) =====================
+    if (lane == 0) {
+      uint32_t scnt = 0;
+      const uint32_t box_bytes = (uint32_t)ka.box_rows * ROWB;
+      for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x) {
+        int b, qt, v, nt; decode(t, b, qt, v, nt);
+        const int row_base = qt * (MB * 128) + ka.min_off;
+        for (int s = 0; s < NKS; ++s, ++scnt) {
+          const int pos = scnt % NSL;
+          mbar_wait(&slice_empty[pos], ((scnt / NSL) & 1) ^ 1);
+          mbar_expect_tx(&slice_full[pos], box_bytes * ka.nbox);
+          uint8_t* dst = slab + pos * pl.slice_bytes;
+          for (int bx = 0; bx < ka.nbox; ++bx)
+            tma_load_3d(dst + bx * box_bytes, &tm_x, s * KS, row_base + bx * ka.box_rows, b, &slice_full[pos]);
         }
-        fence_proxy_async();               // generic-proxy smem writes -> visible to the tensor core (async proxy)
-        mbar_arrive(&slice_full[pos]);
       }
     }
-  } else if (warp == 4) {
+  } else if (warp == 1) {
     // ===================== weight producer =====================
     if (lane == 0) {
       uint32_t wcnt = 0;
       for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x) {
         int b, qt, v, nt; decode(t, b, qt, v, nt);
-        const int n_it = NKS * a.var[v].ntaps * NKB;
-        const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(a.var[v].w) + (size_t)nt * n_it * pl.stage_bytes;
+        const int n_it = NKS * ka.var[v].ntaps * NKB;
+        const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(ka.var[v].w) + (size_t)nt * n_it * pl.stage_bytes;
         for (int it = 0; it < n_it; ++it, ++wcnt) {
           const int st = wcnt % NST;
           mbar_wait(&w_empty[st], ((wcnt / NST) & 1) ^ 1);
@@ -316,15 +328,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == 2) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
       const uint32_t slab_addr = smem_u32(slab), wst_addr = smem_u32(wst);
-      const uint32_t a_lbo = (uint32_t)pl.r_pad * 16u;
       uint32_t scnt = 0, wcnt = 0, tcnt = 0;
       for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x, ++tcnt) {
         int b, qt, v, nt; decode(t, b, qt, v, nt);
-        const TcVariant& var = a.var[v];
+        const TcVariant& var = ka.var[v];
         const int abuf = tcnt % NACC;
         mbar_wait(&acc_empty[abuf], ((tcnt / NACC) & 1) ^ 1);
         tc_fence_after();
@@ -349,8 +360,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
               for (int mb = 0; mb < MB; ++mb) {
 #pragma unroll
                 for (int kk = 0; kk < KBW / 16; ++kk) {
-                  const uint32_t chunk = (uint32_t)(kb * (KBW / 8) + kk * 2);
-                  const uint64_t adesc = make_desc(sl + (chunk * pl.r_pad + mb * 128 + row_off) * 16u, a_lbo, 128u);
+                  const uint64_t adesc = make_desc_sw<ROWB>(sl + (mb * 128 + row_off) * ROWB + (kb * KBW + kk * 16) * 2);
                   const uint64_t bdesc = make_desc(wb + (kk * 2) * N * 16, N * 16, 128u);
                   umma_f16(tacc + mb * N, adesc, bdesc, IDESC, (first && kk == 0) ? 0u : 1u);
                 }
@@ -364,12 +374,36 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
         umma_commit(&acc_full[abuf]);             // accumulators of this tile complete
       }
     }
+  } else if (warp == 3) {
+    // ===================== staging producer: residual tiles (or just buffer grants) =====================
+    if (lane == 0) {
+      uint32_t pcnt = 0;
+      for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x) {
+        int b, qt, v, nt; decode(t, b, qt, v, nt);
+        for (int mb = 0; mb < MB; ++mb) {
+          const int q0 = qt * (MB * 128) + mb * 128;
+          for (int p0 = 0; p0 < N; p0 += PW, ++pcnt) {
+            const int buf = pcnt % NSTG;
+            mbar_wait(&stg_empty[buf], ((pcnt / NSTG) & 1) ^ 1);
+            if (ka.has_res && q0 < ka.n_q) {
+              mbar_expect_tx(&stg_full[buf], pl.stg_bytes);
+              tma_load_4d(stg + buf * pl.stg_bytes, &tm_res, nt * N + p0, 0, q0, b, &stg_full[buf]);
+            } else {
+              mbar_arrive(&stg_full[buf]);
+            }
+          }
+        }
+      }
+    }
   } else {
-    // ===================== epilogue warps 6-9 =====================
+    // ===================== epilogue warps 4-7 =====================
     const int quarter = warp & 3;                       // TMEM lane quarter this warp may access
     const int er = quarter * 32 + lane;                 // row of the 128-row block owned by this thread
     const uint32_t lane_base = ((uint32_t)(quarter * 32)) << 16;
+    const int et = tid - 128;                           // 0..127 within the epilogue group
     constexpr int CW = PW >= 32 ? 32 : 16;
+    // XOR term of the TMA swizzle for this thread's staging row (row pitch SROWB, 1024-byte aligned tile)
+    const int sx = SROWB == 128 ? (er & 7) : (SROWB == 64 ? ((er >> 1) & 3) : ((er >> 2) & 1));
     uint32_t tcnt = 0, pcnt = 0;
     int bias_nt = -1;
     for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x, ++tcnt) {
@@ -377,7 +411,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
       const int n0 = nt * N;
       if (nt != bias_nt) {                              // (re)load the bias slice; epilogue-warps-only barrier
         asm volatile("bar.sync 1, 128;" ::: "memory");
-        for (int i = tid - 192; i < N; i += 128) bias_s[i] = a.bias[n0 + i];
+        for (int i = et; i < N; i += 128) bias_s[i] = ka.bias[n0 + i];
         asm volatile("bar.sync 1, 128;" ::: "memory");
         bias_nt = nt;
       }
@@ -385,46 +419,49 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
       mbar_wait(&acc_full[abuf], (tcnt / NACC) & 1);
       tc_fence_after();
       const uint32_t tacc = tmem_base + lane_base + abuf * ACC_COLS;
-      const int out_off = a.var[v].out_off;
+      const int out_off = ka.var[v].out_off;
 #pragma unroll 1
       for (int mb = 0; mb < MB; ++mb) {
-        const int q = qt * (MB * 128) + mb * 128 + er;
-        const bool valid = q < a.n_q;
-        const size_t row_idx = ((size_t)b * a.out_rows + (size_t)(valid ? q : 0) * a.out_stride + out_off) * a.c_out + n0;
+        const int q0 = qt * (MB * 128) + mb * 128;
+        const int q = q0 + er;
+        const bool valid = q < ka.n_q;
+        const bool blk_valid = q0 < ka.n_q;
+        const bool has_res = ka.has_res != 0 && blk_valid;
 #pragma unroll 1
         for (int p0 = 0; p0 < N; p0 += PW, ++pcnt) {
-          uint8_t* my = stg + ((pcnt & 1) * 128 + er) * pl.stg_pitch;
-          bulk_wait_read<1>();                          // the store that last used this staging row has read it
-#pragma unroll 1
+          const int buf = pcnt % NSTG;
+          uint8_t* my = stg + buf * pl.stg_bytes + er * SROWB;
+          mbar_wait(&stg_full[buf], (pcnt / NSTG) & 1);   // residual tile landed / buffer granted
+#pragma unroll
           for (int c0 = 0; c0 < PW; c0 += CW) {
             uint32_t r[32];
             if (CW == 32) tmem_ld32(tacc + mb * N + p0 + c0, r);
             else tmem_ld16(tacc + mb * N + p0 + c0, r);
-            float vv[CW];
-            const size_t idx = row_idx + p0 + c0;
             uint4 rr[CW / 8], rr2[CW / 8];
-            const bool has_res = a.res != nullptr && valid, has_res2 = a.res2 != nullptr && valid;
             if (has_res) {
-              const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(a.res) + idx);
 #pragma unroll
-              for (int i = 0; i < CW / 8; ++i) rr[i] = __ldg(rp + i);
+              for (int i = 0; i < CW / 8; ++i) rr[i] = *reinterpret_cast<const uint4*>(my + (((c0 / 8 + i) ^ sx) * 16));
             }
+            const bool has_res2 = ka.res2 != nullptr && valid;
             if (has_res2) {
-              const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(a.res2) + idx);
+              const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(ka.res2) +
+                                                               ((size_t)b * ka.n_q + q) * ka.c_out + n0 + p0 + c0);
 #pragma unroll
-              for (int i = 0; i < CW / 8; ++i) rr2[i] = __ldg(rp + i);
+              for (int i = 0; i < CW / 8; ++i) rr2[i] = rp[i];
             }
             tmem_ld_wait();
+            float vv[CW];
 #pragma unroll
             for (int i = 0; i < CW; ++i) vv[i] = __uint_as_float(r[i]) + bias_s[p0 + c0 + i];
             if (has_res) {
+              const float ri = ka.res_inv;
 #pragma unroll
               for (int i = 0; i < CW / 8; ++i) {
                 float2 f;
-                f = H2<T>::up(rr[i].x); vv[i * 8 + 0] += f.x; vv[i * 8 + 1] += f.y;
-                f = H2<T>::up(rr[i].y); vv[i * 8 + 2] += f.x; vv[i * 8 + 3] += f.y;
-                f = H2<T>::up(rr[i].z); vv[i * 8 + 4] += f.x; vv[i * 8 + 5] += f.y;
-                f = H2<T>::up(rr[i].w); vv[i * 8 + 6] += f.x; vv[i * 8 + 7] += f.y;
+                f = H2<T>::up(rr[i].x); vv[i * 8 + 0] += lrelu_f(f.x, ri); vv[i * 8 + 1] += lrelu_f(f.y, ri);
+                f = H2<T>::up(rr[i].y); vv[i * 8 + 2] += lrelu_f(f.x, ri); vv[i * 8 + 3] += lrelu_f(f.y, ri);
+                f = H2<T>::up(rr[i].z); vv[i * 8 + 4] += lrelu_f(f.x, ri); vv[i * 8 + 5] += lrelu_f(f.y, ri);
+                f = H2<T>::up(rr[i].w); vv[i * 8 + 6] += lrelu_f(f.x, ri); vv[i * 8 + 7] += lrelu_f(f.y, ri);
               }
             }
             if (has_res2) {
@@ -437,55 +474,122 @@ __global__ void __launch_bounds__(kTcThreads, 1) conv_tc_kernel(const __grid_con
                 f = H2<T>::up(rr2[i].w); vv[i * 8 + 6] += f.x; vv[i * 8 + 7] += f.y;
               }
             }
-            if (a.out_scale != 1.0f) {
+            const float osc = ka.out_scale, osl = ka.out_slope;
 #pragma unroll
-              for (int i = 0; i < CW; ++i) vv[i] *= a.out_scale;
-            }
-            if (a.out_slope != 1.0f) {
-#pragma unroll
-              for (int i = 0; i < CW; ++i) vv[i] = lrelu_f(vv[i], a.out_slope);
-            }
+            for (int i = 0; i < CW; ++i) vv[i] = lrelu_f(vv[i] * osc, osl);
 #pragma unroll
             for (int i = 0; i < CW / 8; ++i) {
               uint4 u;
               u.x = H2<T>::down(vv[i * 8 + 0], vv[i * 8 + 1]); u.y = H2<T>::down(vv[i * 8 + 2], vv[i * 8 + 3]);
               u.z = H2<T>::down(vv[i * 8 + 4], vv[i * 8 + 5]); u.w = H2<T>::down(vv[i * 8 + 6], vv[i * 8 + 7]);
-              *reinterpret_cast<uint4*>(my + (c0 + i * 8) * 2) = u;
+              *reinterpret_cast<uint4*>(my + (((c0 / 8 + i) ^ sx) * 16)) = u;
             }
           }
-          fence_proxy_async();                          // my staging row -> visible to the bulk-copy engine
-          if (valid) bulk_s2g(reinterpret_cast<T*>(a.out) + row_idx + p0, my, PW * 2);
-          bulk_commit();
+          fence_proxy_async();                          // staging writes -> visible to the TMA engine
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (et == 0) {
+            if (blk_valid) tma_store_4d(&tm_out, stg + buf * pl.stg_bytes, n0 + p0, out_off, q0, b);
+            bulk_commit();
+            bulk_wait_read<1>();                        // the previous pass's store has read its tile
+            if (pcnt > 0) mbar_arrive(&stg_empty[(pcnt - 1) % NSTG]);
+          }
         }
       }
       tc_fence_before();
       mbar_arrive(&acc_empty[abuf]);                    // accumulator buffer may be overwritten
     }
-    bulk_wait_all();
+    if (et == 0) bulk_wait_all();
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 5) { __syncwarp(); tc_fence_after(); tmem_dealloc(tmem_base, TMEM_COLS); }
+  if (warp == 2) { __syncwarp(); tc_fence_after(); tmem_dealloc(tmem_base, TMEM_COLS); }
 }
 
 // ------------------------------------------------------------------ host side
 int g_num_sms = 0;
 
-template <typename T, int C_IN, int N, int MB, int KS, int KBW, int NST, int NSL, int PW>
-cudaError_t launch_t(const TcArgs& a, cudaStream_t s, int* grid_out) {
-  TcKArgs ka;
-  ka.c = a;
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+CUtensorMapSwizzle swizzle_for(int inner_bytes) {
+  return inner_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : (inner_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+}
+
+// rank-3 map over activations [B][rows][C] (16-bit), box = [box_c channels][box_rows rows][1]
+bool make_map3(CUtensorMap* m, ActType act, const void* base, int C, int rows, int B, int box_c, int box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return false;
+  cuuint64_t gdim[3] = {(cuuint64_t)C, (cuuint64_t)rows, (cuuint64_t)B};
+  cuuint64_t gstr[2] = {(cuuint64_t)C * 2, (cuuint64_t)C * 2 * (cuuint64_t)rows};
+  cuuint32_t box[3] = {(cuuint32_t)box_c, (cuuint32_t)box_rows, 1};
+  cuuint32_t est[3] = {1, 1, 1};
+  return fn(m, act == ACT_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(base), gdim, gstr,
+            box, est, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(box_c * 2), CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// rank-4 map over outputs viewed as [B][q][u][C] (row q*u + phase), box = [box_c][1][128][1]
+bool make_map4(CUtensorMap* m, ActType act, const void* base, int C, int u, int nq, int B, int box_c) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return false;
+  cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)u, (cuuint64_t)nq, (cuuint64_t)B};
+  cuuint64_t gstr[3] = {(cuuint64_t)C * 2, (cuuint64_t)C * 2 * u, (cuuint64_t)C * 2 * u * (cuuint64_t)nq};
+  cuuint32_t box[4] = {(cuuint32_t)box_c, 1, 128, 1};
+  cuuint32_t est[4] = {1, 1, 1, 1};
+  return fn(m, act == ACT_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<void*>(base), gdim, gstr,
+            box, est, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(box_c * 2), CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// slab slice = nbox boxes of box_rows rows covering MB*128 + span rows with little waste
+void tc_boxes(int rows, int* box_rows, int* nbox) {
+  int best_br = 256, best_pad = 1 << 30;
+  for (int br = 256; br >= 8; br >>= 1) {            // fewest padded rows with at most 24 boxes; ties -> larger box
+    const int nb = (rows + br - 1) / br;
+    if (nb > 24) break;
+    if (nb * br < best_pad) { best_pad = nb * br; best_br = br; }
+  }
+  *box_rows = best_br; *nbox = (rows + best_br - 1) / best_br;
+}
+
+template <typename T, int C_IN, int N, int MB, int KS, int KBW, int NST, int NSL, int NSTG>
+cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out) {
+  constexpr int PW = N < 64 ? N : 64;
+  TcKArgs ka{};
+  ka.bias = a.bias; ka.res2 = a.res2; ka.n_q = a.n_q; ka.c_out = a.c_out; ka.has_res = a.res != nullptr;
+  ka.res_inv = a.res_inv; ka.out_scale = a.out_scale; ka.out_slope = a.out_slope;
+  ka.nvar = a.nvar;
+  for (int v = 0; v < a.nvar; ++v) ka.var[v] = a.var[v];
   int mn = a.var[0].tap_off[0], mx = mn;
   for (int v = 0; v < a.nvar; ++v)
     for (int j = 0; j < a.var[v].ntaps; ++j) { mn = a.var[v].tap_off[j] < mn ? a.var[v].tap_off[j] : mn; mx = a.var[v].tap_off[j] > mx ? a.var[v].tap_off[j] : mx; }
   ka.min_off = mn; ka.span = mx - mn;
   if (ka.span > kTcMaxSpan) return cudaErrorInvalidValue;
-  const TcSmemPlan pl = tc_plan(N, MB, KS, KBW, NST, NSL, PW, ka.span);
+  if ((a.res || a.res2) && a.out_stride != 1) return cudaErrorInvalidValue;
+  tc_boxes(MB * 128 + ka.span, &ka.box_rows, &ka.nbox);
+  const TcSmemPlan pl = tc_plan(N, KS, KBW, NST, NSL, NSTG, ka.nbox * ka.box_rows);
   if ((size_t)pl.total > kTcMaxSmem) return cudaErrorInvalidConfiguration;
   ka.tiles_q = (a.n_q + MB * 128 - 1) / (MB * 128);
   ka.n_tiles = a.c_out / N;
   ka.total_tiles = a.B * ka.tiles_q * a.nvar * ka.n_tiles;
-  auto kern = conv_tc_kernel<T, C_IN, N, MB, KS, KBW, NST, NSL, PW>;
+  CUtensorMap tm_x, tm_res, tm_out;
+  if (!make_map3(&tm_x, act, a.x, C_IN, a.x_rows, a.B, KS, ka.box_rows)) return cudaErrorNotSupported;
+  if (!make_map4(&tm_out, act, a.out, a.c_out, a.out_stride, a.n_q, a.B, PW)) return cudaErrorNotSupported;
+  if (a.res) { if (!make_map4(&tm_res, act, a.res, a.c_out, 1, a.n_q, a.B, PW)) return cudaErrorNotSupported; }
+  else tm_res = tm_out;
+  auto kern = conv_tc_kernel<T, C_IN, N, MB, KS, KBW, NST, NSL, NSTG>;
   static int configured = 0, occ = 1;      // per instantiation
   if (pl.total > configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total);
@@ -506,42 +610,37 @@ cudaError_t launch_t(const TcArgs& a, cudaStream_t s, int* grid_out) {
   int grid = g_num_sms * occ;
   if (grid > ka.total_tiles) grid = ka.total_tiles;
   if (grid_out) *grid_out = grid;
-  kern<<<grid, kTcThreads, pl.total, s>>>(ka);
+  kern<<<grid, kTcThreads, pl.total, s>>>(tm_x, tm_res, tm_out, ka);
   return cudaGetLastError();
 }
 
 struct TcRow { int c_in, c_out_tile; TcConfig cfg; };
-//                 c_in  n     {n,  mb, ks, kbw, nst, nsl, pw}
+//   c_in  n     {n,  mb, ks, kbw, nst, nsl, nstg}
+#define HFG_TC_TABLE(X)            \
+  X(512, 256, 1, 64, 16, 6, 3, 3)  \
+  X(256, 256, 2, 64, 16, 6, 3, 3)  \
+  X(128, 256, 1, 64, 16, 6, 2, 3)  \
+  X(256, 128, 2, 64, 32, 4, 3, 3)  \
+  X(128, 128, 2, 64, 32, 4, 3, 3)  \
+  X(128, 64, 4, 64, 64, 3, 2, 3)   \
+  X(64, 64, 4, 64, 64, 3, 2, 3)    \
+  X(64, 32, 4, 64, 64, 4, 2, 4)    \
+  X(32, 32, 4, 32, 32, 4, 3, 4)    \
+  X(32, 16, 4, 32, 32, 4, 3, 4)    \
+  X(16, 16, 4, 16, 16, 4, 3, 4)
+
 const TcRow kTcTable[] = {
-    {512, 256, {256, 1, 64, 32, 4, 3, 64}},
-    {256, 256, {256, 2, 64, 32, 4, 3, 64}},
-    {128, 256, {256, 1, 64, 32, 4, 2, 64}},
-    {256, 128, {128, 2, 64, 32, 6, 3, 64}},
-    {128, 128, {128, 2, 64, 32, 6, 3, 64}},
-    {128, 64, {64, 4, 64, 64, 4, 2, 64}},
-    {64, 64, {64, 4, 64, 64, 4, 2, 64}},
-    {64, 32, {32, 4, 64, 64, 4, 2, 32}},
-    {32, 32, {32, 4, 32, 32, 4, 2, 32}},
-    {32, 16, {16, 4, 32, 32, 4, 2, 16}},
-    {16, 16, {16, 4, 16, 16, 4, 2, 16}},
+#define X(CI, NN, MB, KS, KBW, NST, NSL, NSTG) {CI, NN, {NN, MB, KS, KBW, NST, NSL, NSTG}},
+    HFG_TC_TABLE(X)
+#undef X
 };
 
 template <typename T>
-cudaError_t launch_shape(const TcArgs& a, cudaStream_t s, int* grid_out) {
+cudaError_t launch_shape(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out) {
   const int ci = a.c_in, n = a.c_out > 256 ? 256 : a.c_out;
-#define HFG_TC(CI, NN, MB, KS, KBW, NST, NSL, PW) if (ci == CI && n == NN) return launch_t<T, CI, NN, MB, KS, KBW, NST, NSL, PW>(a, s, grid_out);
-  HFG_TC(512, 256, 1, 64, 32, 4, 3, 64)
-  HFG_TC(256, 256, 2, 64, 32, 4, 3, 64)
-  HFG_TC(128, 256, 1, 64, 32, 4, 2, 64)
-  HFG_TC(256, 128, 2, 64, 32, 6, 3, 64)
-  HFG_TC(128, 128, 2, 64, 32, 6, 3, 64)
-  HFG_TC(128, 64, 4, 64, 64, 4, 2, 64)
-  HFG_TC(64, 64, 4, 64, 64, 4, 2, 64)
-  HFG_TC(64, 32, 4, 64, 64, 4, 2, 32)
-  HFG_TC(32, 32, 4, 32, 32, 4, 2, 32)
-  HFG_TC(32, 16, 4, 32, 32, 4, 2, 16)
-  HFG_TC(16, 16, 4, 16, 16, 4, 2, 16)
-#undef HFG_TC
+#define X(CI, NN, MB, KS, KBW, NST, NSL, NSTG) if (ci == CI && n == NN) return launch_t<T, CI, NN, MB, KS, KBW, NST, NSL, NSTG>(a, act, s, grid_out);
+  HFG_TC_TABLE(X)
+#undef X
   return cudaErrorInvalidValue;
 }
 
@@ -559,7 +658,9 @@ bool tc_supported(int c_in, int c_out, int ntaps, int span) {
   if (ntaps < 1 || ntaps > kMaxTaps || span < 0 || span > kTcMaxSpan) return false;
   TcConfig c;
   if (!tc_config(c_in, c_out, &c)) return false;
-  return (size_t)tc_plan(c.n, c.mb, c.ks, c.kbw, c.nst, c.nsl, c.pw, span).total <= kTcMaxSmem;
+  int br, nb;
+  tc_boxes(c.mb * 128 + span, &br, &nb);
+  return (size_t)tc_plan(c.n, c.ks, c.kbw, c.nst, c.nsl, c.nstg, br * nb).total <= kTcMaxSmem;
 }
 
 size_t tc_packed_weight_bytes(int c_in, int c_out, int ntaps) { return (size_t)ntaps * c_in * c_out * 2; }
@@ -587,9 +688,10 @@ void tc_pack_weights(const float* w, int ntaps, int c_in, int c_out, ActType act
 }
 
 cudaError_t launch_conv_tc(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out) {
-  if (a.B <= 0 || a.n_q <= 0 || a.nvar < 1 || a.nvar > kMaxVariants) return a.nvar < 1 || a.nvar > kMaxVariants ? cudaErrorInvalidValue : cudaSuccess;
-  if (act == ACT_F16) return launch_shape<__half>(a, s, grid_out);
-  if (act == ACT_BF16) return launch_shape<__nv_bfloat16>(a, s, grid_out);
+  if (a.nvar < 1 || a.nvar > kMaxVariants) return cudaErrorInvalidValue;
+  if (a.B <= 0 || a.n_q <= 0) return cudaSuccess;
+  if (act == ACT_F16) return launch_shape<__half>(a, act, s, grid_out);
+  if (act == ACT_BF16) return launch_shape<__nv_bfloat16>(a, act, s, grid_out);
   return cudaErrorInvalidValue;
 }
 

@@ -42,7 +42,6 @@ struct Layer {
   float* d_w32 = nullptr;
   float* d_bias = nullptr;
   void* d_wpk = nullptr;
-  bool use_umma = false;
   bool use_tc = false;      // persistent tcgen05 kernel (conv_tc.cu): one launch per layer, phases = variants
   std::vector<size_t> tc_off;   // byte offset of each phase's packed weights in d_wpk
 };
@@ -73,7 +72,6 @@ struct hfg_ctx {
   float* d_mel = nullptr; size_t d_mel_bytes = 0;
   float* d_audio = nullptr; size_t d_audio_bytes = 0;
   bool force_ffma = false;
-  int tc_kernel = 1;        // 1 = persistent kernel (conv_tc.cu), 0 = first-generation per-tile kernel (conv_umma.cu)
   bool need_acc = true, need_sum = false;
 };
 
@@ -235,16 +233,17 @@ struct Runner {
   int B;
   cudaError_t status = cudaSuccess;
 
-  // persistent tcgen05 kernel: the whole layer (all phases of a transposed conv) in one launch
-  void conv_tc(const Layer& L, const void* x, int x_rows, void* out, float in_slope, const void* res,
-               const void* res2, float out_scale) {
+  // persistent tcgen05 kernel: the whole layer (all phases of a transposed conv) in one launch; x is
+  // stored already activated (conv_tc.cu), res is stored activated with slope 1/res_inv
+  void conv_tc(const Layer& L, const void* x, int x_rows, void* out, const void* res, float res_inv,
+               const void* res2, float out_scale, float out_slope) {
     if (status != cudaSuccess) return;
     const int u = L.transposed ? L.stride : 1;
     TcArgs a{};
     a.x = x; a.out = out; a.res = res; a.res2 = res2; a.bias = L.d_bias;
     a.B = B; a.x_rows = x_rows; a.n_q = x_rows; a.out_rows = x_rows * u; a.out_stride = u;
     a.c_in = L.cin_pad; a.c_out = L.cout;
-    a.in_slope = in_slope; a.out_scale = out_scale; a.out_slope = 1.0f;
+    a.res_inv = res_inv; a.out_scale = out_scale; a.out_slope = out_slope;
     a.nvar = (int)L.phases.size();
     for (int p = 0; p < a.nvar; ++p) {
       const Phase& ph = L.phases[p];
@@ -256,10 +255,10 @@ struct Runner {
     h->launches++;
   }
 
-  void conv(const Layer& L, const void* x, int x_rows, void* out, float in_slope, const void* res,
-            float* acc, int mrf_mode) {
+  // direct kernel: one launch per output phase; x / res are raw, in_slope applied while staging
+  void conv_ffma(const Layer& L, const void* x, int x_rows, void* out, float in_slope, const void* res,
+                 float* acc, int mrf_mode, float out_slope) {
     if (status != cudaSuccess) return;
-    if (L.use_tc) { conv_tc(L, x, x_rows, out, in_slope, res, nullptr, 1.0f); return; }
     const int u = L.transposed ? L.stride : 1;
     for (int p = 0; p < (int)L.phases.size(); ++p) {
       const Phase& ph = L.phases[p];
@@ -269,33 +268,40 @@ struct Runner {
       a.c_in = L.cin_pad; a.c_out = L.cout; a.ntaps = ph.ntaps;
       for (int j = 0; j < ph.ntaps; ++j) a.tap_off[j] = ph.tap_off[j];
       a.out_stride = u; a.out_off = p; a.in_slope = in_slope; a.mrf_mode = mrf_mode;
-      a.mrf_div = (float)h->cfg.num_kernels;
-      if (L.use_umma) {
-        a.w = (const char*)L.d_wpk + ph.wpk_off;
-        status = launch_conv_umma(a, h->act, s);
-      } else {
-        a.w = L.d_w32 + ph.w32_off;
-        status = launch_conv_ffma(a, h->act, s);
-      }
+      a.mrf_div = (float)h->cfg.num_kernels; a.out_slope = out_slope;
+      a.w = L.d_w32 + ph.w32_off;
+      status = launch_conv_ffma(a, h->act, s);
       h->launches++;
       if (status != cudaSuccess) return;
     }
   }
 
+  // A conv whose input needs activation `slope` (1 = none) and whose output feeds a consumer that would
+  // apply `next_slope`; `next_tc` says whether that consumer wants it stored already activated.
+  void conv(const Layer& L, const void* x, int x_rows, void* out, float slope, const void* res, float next_slope, bool next_tc) {
+    const float os = next_tc ? next_slope : 1.0f;
+    if (L.use_tc) conv_tc(L, x, x_rows, out, res, res ? 1.0f / slope_of_res : 1.0f, nullptr, 1.0f, os);
+    else conv_ffma(L, x, x_rows, out, slope, res, nullptr, MRF_NONE, os);
+  }
+
   // last conv of resblock j of a stage: residual add + MRF sum / average (reference model.py:79,111,161-167).
-  // tcgen05 path: the running sum xs lives in a 16-bit buffer `sum` (res2); direct path: fp32 `acc`.
-  void conv_mrf(const Layer& L, const void* x, int x_rows, void* out, void* sum, float in_slope, const void* res,
-                float* acc, int j, int nk) {
+  // tcgen05 path: the running raw sum xs lives in a 16-bit buffer `sum` (res2); direct path: fp32 `acc`.
+  void conv_mrf(const Layer& L, const void* x, int x_rows, void* out, void* sum, float slope, const void* res,
+                float* acc, int j, int nk, float next_slope, bool next_tc) {
+    const float os = next_tc ? next_slope : 1.0f;
     if (L.use_tc) {
-      if (nk == 1) conv_tc(L, x, x_rows, out, in_slope, res, nullptr, 1.0f);
-      else if (j == 0) conv_tc(L, x, x_rows, sum, in_slope, res, nullptr, 1.0f);
-      else if (j < nk - 1) conv_tc(L, x, x_rows, sum, in_slope, res, sum, 1.0f);
-      else conv_tc(L, x, x_rows, out, in_slope, res, sum, 1.0f / (float)nk);
+      const float ri = 1.0f / slope_of_res;
+      if (nk == 1) conv_tc(L, x, x_rows, out, res, ri, nullptr, 1.0f, os);
+      else if (j == 0) conv_tc(L, x, x_rows, sum, res, ri, nullptr, 1.0f, 1.0f);
+      else if (j < nk - 1) conv_tc(L, x, x_rows, sum, res, ri, sum, 1.0f, 1.0f);
+      else conv_tc(L, x, x_rows, out, res, ri, sum, 1.0f / (float)nk, os);
     } else {
       const int mode = nk == 1 ? MRF_NONE : (j == 0 ? MRF_FIRST : (j == nk - 1 ? MRF_FINAL : MRF_ADD));
-      conv(L, x, x_rows, out, in_slope, res, acc, mode);
+      conv_ffma(L, x, x_rows, out, slope, res, acc, mode, os);
     }
   }
+
+  float slope_of_res = 1.0f;   // slope the residual tensor of the current stage was stored with (1 = raw)
 };
 
 int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev, char* ws, cudaStream_t s) {
@@ -307,10 +313,11 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
   const float kFinalSlope = c.compat == 0 ? 0.3f : 0.01f;       // keras LeakyReLU() default, model.py:152
   int mark = 0;
   auto stamp = [&]() { if (h->stage_timing && mark < (int)h->events.size()) cudaEventRecord(h->events[mark++], s); };
+  auto layer = [&](const std::string& name) -> const Layer& { return h->layers[h->index[name]]; };
   stamp();
 
-  // conv_pre (model.py:156)
-  const Layer& pre = h->layers[h->index["conv_pre"]];
+  // conv_pre (model.py:156); its consumer is ups[0] behind lrelu(0.1)
+  const Layer& pre = layer("conv_pre");
   const void* x0 = mel_dev;
   if (h->act != ACT_F32 || pre.cin_pad != pre.cin) {
     cudaError_t e = launch_cast_pad(mel_dev, w.MEL, (long long)B * T, pre.cin, pre.cin_pad, h->act, s);
@@ -318,15 +325,22 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
     if (e != cudaSuccess) return fail(h, HFG_ERR_CUDA, "cast_pad launch failed: %s", cudaGetErrorString(e));
     x0 = w.MEL;
   }
-  r.conv(pre, x0, T, w.P, 1.0f, nullptr, nullptr, MRF_NONE);
+  r.conv(pre, x0, T, w.P, 1.0f, nullptr, kSlope, layer("ups.0").use_tc);
   stamp();
 
   char* x = w.P;          // current stage input
   int L = T;
+  bool x_preact = layer("ups.0").use_tc;   // is x stored already activated for its consumer?
   for (int i = 0; i < c.num_upsamples; ++i) {
-    const Layer& up = h->layers[h->index["ups." + std::to_string(i)]];
-    r.conv(up, x, L, w.U, kSlope, nullptr, nullptr, MRF_NONE);   // model.py:159-160
+    const Layer& up = layer("ups." + std::to_string(i));
+    const std::string first_rb = "resblocks." + std::to_string(i * c.num_kernels) + (c.resblock == 1 ? ".convs1.0" : ".convs.0");
+    const bool rb_tc = layer(first_rb).use_tc;                   // a stage's resblock convs all share one shape
+    const bool last_stage = (i == c.num_upsamples - 1);
+    const bool next_tc = last_stage ? rb_tc : layer("ups." + std::to_string(i + 1)).use_tc;   // conv_post reads either form
+    const float next_slope = last_stage ? kFinalSlope : kSlope;
+    r.conv(up, x, L, w.U, x_preact ? 1.0f : kSlope, nullptr, kSlope, rb_tc);   // model.py:159-160
     L *= up.stride;
+    r.slope_of_res = rb_tc ? kSlope : 1.0f;
     char* next_x = nullptr;
     for (int j = 0; j < c.num_kernels; ++j) {                   // model.py:162-166
       const int n = i * c.num_kernels + j;
@@ -338,29 +352,30 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
         if (last && j == c.num_kernels - 1) next_x = rnext;
         const std::string base = "resblocks." + std::to_string(n);
         if (c.resblock == 1) {                                   // ResBlock1.call model.py:71-80
-          const Layer& c1 = h->layers[h->index[base + ".convs1." + std::to_string(m)]];
-          const Layer& c2 = h->layers[h->index[base + ".convs2." + std::to_string(m)]];
-          r.conv(c1, rcur, L, w.T, kSlope, nullptr, nullptr, MRF_NONE);
-          if (last) r.conv_mrf(c2, w.T, L, rnext, w.S, kSlope, rcur, w.ACC, j, c.num_kernels);
-          else r.conv(c2, w.T, L, rnext, kSlope, rcur, nullptr, MRF_NONE);
+          const Layer& c1 = layer(base + ".convs1." + std::to_string(m));
+          const Layer& c2 = layer(base + ".convs2." + std::to_string(m));
+          r.conv(c1, rcur, L, w.T, kSlope, nullptr, kSlope, rb_tc);
+          if (last) r.conv_mrf(c2, w.T, L, rnext, w.S, kSlope, rcur, w.ACC, j, c.num_kernels, next_slope, next_tc);
+          else r.conv(c2, w.T, L, rnext, kSlope, rcur, kSlope, rb_tc);
         } else {                                                 // ResBlock2.call model.py:106-112
-          const Layer& c1 = h->layers[h->index[base + ".convs." + std::to_string(m)]];
-          if (last) r.conv_mrf(c1, rcur, L, rnext, w.S, kSlope, rcur, w.ACC, j, c.num_kernels);
-          else r.conv(c1, rcur, L, rnext, kSlope, rcur, nullptr, MRF_NONE);
+          const Layer& c1 = layer(base + ".convs." + std::to_string(m));
+          if (last) r.conv_mrf(c1, rcur, L, rnext, w.S, kSlope, rcur, w.ACC, j, c.num_kernels, next_slope, next_tc);
+          else r.conv(c1, rcur, L, rnext, kSlope, rcur, kSlope, rb_tc);
         }
         rcur = rnext;
       }
     }
     x = next_x;                                                  // x = xs / num_kernels (model.py:167)
+    x_preact = next_tc;
     stamp();
   }
   if (r.status != cudaSuccess) return fail(h, HFG_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(r.status));
 
   // leakyReLU(0.3) -> conv_post -> tanh (model.py:169-171)
-  const Layer& post = h->layers[h->index["conv_post"]];
+  const Layer& post = layer("conv_post");
   PostArgs pa{};
   pa.x = x; pa.w = post.d_w32; pa.out = audio_dev; pa.B = B; pa.rows = L; pa.c_in = post.cin; pa.ntaps = post.k;
-  pa.pad_left = (post.k - 1) / 2; pa.in_slope = kFinalSlope;
+  pa.pad_left = (post.k - 1) / 2; pa.in_slope = x_preact ? 1.0f : kFinalSlope;
   pa.bias = post.b.empty() ? 0.f : post.b[0];
   cudaError_t e = launch_conv_post(pa, h->act, s);
   h->launches++;
@@ -465,10 +480,9 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
     }
     int cin_mma = L.cin;
     if (L.name == "conv_pre") cin_mma = (int)align_up((size_t)L.cin, 64);
-    const bool tensor_ok = !is_post && h->act != ACT_F32 && !h->force_ffma;
-    L.use_tc = tensor_ok && h->tc_kernel == 1 && (int)L.phases.size() <= kMaxVariants && tc_supported(cin_mma, L.cout, max_taps, max_span);
-    L.use_umma = tensor_ok && !L.use_tc && umma_supported(cin_mma, L.cout, max_taps, max_span);
-    if (L.use_umma || L.use_tc) L.cin_pad = cin_mma;
+    L.use_tc = !is_post && h->act != ACT_F32 && !h->force_ffma && (int)L.phases.size() <= kMaxVariants &&
+               tc_supported(cin_mma, L.cout, max_taps, max_span);
+    if (L.use_tc) L.cin_pad = cin_mma;
     // fp32 weights per phase, [ntaps][cin_pad][cout]
     std::vector<float> w32;
     for (Phase& ph : L.phases) {
@@ -485,14 +499,11 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
           memcpy(&w32[ph.w32_off + ((size_t)t * L.cin_pad + ci) * L.cout], &w[((size_t)j * L.cin + ci) * L.cout], sizeof(float) * L.cout);
       }
     }
-    if (L.use_umma || L.use_tc) {
+    if (L.use_tc) {
       size_t total = 0;
-      for (Phase& ph : L.phases) { ph.wpk_off = total; total += align_up(umma_packed_weight_bytes(L.cin_pad, L.cout, ph.ntaps), 256); }
+      for (Phase& ph : L.phases) { ph.wpk_off = total; total += align_up(tc_packed_weight_bytes(L.cin_pad, L.cout, ph.ntaps), 256); }
       std::vector<char> pk(total);
-      for (Phase& ph : L.phases) {
-        if (L.use_tc) tc_pack_weights(&w32[ph.w32_off], ph.ntaps, L.cin_pad, L.cout, h->act, pk.data() + ph.wpk_off);
-        else umma_pack_weights(&w32[ph.w32_off], ph.ntaps, L.cin_pad, L.cout, h->act, pk.data() + ph.wpk_off);
-      }
+      for (Phase& ph : L.phases) tc_pack_weights(&w32[ph.w32_off], ph.ntaps, L.cin_pad, L.cout, h->act, pk.data() + ph.wpk_off);
       CUDA_TRY(h, cudaMalloc(&L.d_wpk, total));
       CUDA_TRY(h, cudaMemcpy(L.d_wpk, pk.data(), total, cudaMemcpyHostToDevice));
     } else {
@@ -597,8 +608,18 @@ int hfg_set_option(hfg_handle h, const char* key, long long value) {
   if (k == "micro_batch") { if (value < 0) return fail(h, HFG_ERR_INVALID, "micro_batch must be >= 0"); h->micro_batch = (int)value; return HFG_OK; }
   if (k == "stage_timing") { h->stage_timing = value != 0; return HFG_OK; }
   if (k == "force_ffma") { h->force_ffma = value != 0; h->finalized = false; return HFG_OK; }
-  if (k == "tc_kernel") { h->tc_kernel = value != 0; h->finalized = false; return HFG_OK; }
   return fail(h, HFG_ERR_INVALID, "unknown option '%s'", key);
+}
+
+int hfg_layer_engines(hfg_handle h, char* buf, size_t cap) {
+  if (!h || !buf || cap == 0) return HFG_ERR_INVALID;
+  if (!h->finalized) return fail(h, HFG_ERR_STATE, "hfg_layer_engines: weights not finalised");
+  std::string out;
+  for (const Layer& L : h->layers)
+    out += L.name + ":" + (L.name == "conv_post" ? "post" : (L.use_tc ? "tc" : "ffma")) + "\n";
+  if (out.size() + 1 > cap) return fail(h, HFG_ERR_NOMEM, "need %zu bytes", out.size() + 1);
+  memcpy(buf, out.c_str(), out.size() + 1);
+  return HFG_OK;
 }
 
 int hfg_last_launch_count(hfg_handle h, long long* out) {
@@ -618,64 +639,56 @@ int hfg_stage_times_ms(hfg_handle h, float* out, int* n) {
   return HFG_OK;
 }
 
-// Single tapped-conv operator (kernels.cuh ConvArgs) on caller-provided device buffers; packs and
-// uploads the weights on every call -- meant for operator-level parity tests, not for speed.
-int hfg_op_tapped_conv(int act, int use_umma, const void* x_dev, int B, int x_rows, int c_in,
+// Single tapped-conv operator on caller-provided device buffers; packs and uploads the weights on every
+// call -- meant for operator-level parity tests, not for speed.  engine 0: direct FFMA kernel (ConvArgs
+// semantics, in_slope applied to x); engine 1: persistent tcgen05 kernel (TcArgs semantics: x already
+// activated, in_slope must be 1; res stored activated with slope 1/res_inv).
+int hfg_op_tapped_conv(int act, int engine, const void* x_dev, int B, int x_rows, int c_in,
                        const float* w_host, const float* bias_host, int c_out, int ntaps, const int* tap_off,
-                       int out_stride, int out_off, float in_slope, const void* res_dev, float* acc_dev,
+                       int out_stride, int out_off, float in_slope, const void* res_dev, float res_inv,
+                       const void* res2_dev, float out_scale, float out_slope, float* acc_dev,
                        int mrf_mode, float mrf_div, void* out_dev, void* stream) {
   if (act < 0 || act > 2 || !x_dev || !w_host || !bias_host || !tap_off || ntaps < 1 || ntaps > kMaxTaps)
     return fail(nullptr, HFG_ERR_INVALID, "hfg_op_tapped_conv: bad argument");
-  ConvArgs a{};
-  a.x = x_dev; a.out = out_dev; a.res = res_dev; a.acc = acc_dev;
-  a.B = B; a.x_rows = x_rows; a.n_q = x_rows; a.out_rows = x_rows * out_stride;
-  a.c_in = c_in; a.c_out = c_out; a.ntaps = ntaps;
   int mn = tap_off[0], mx = tap_off[0];
-  for (int j = 0; j < ntaps; ++j) { a.tap_off[j] = tap_off[j]; mn = std::min(mn, tap_off[j]); mx = std::max(mx, tap_off[j]); }
-  a.out_stride = out_stride; a.out_off = out_off; a.in_slope = in_slope; a.mrf_mode = mrf_mode; a.mrf_div = mrf_div;
+  for (int j = 0; j < ntaps; ++j) { mn = std::min(mn, tap_off[j]); mx = std::max(mx, tap_off[j]); }
   cudaStream_t s = (cudaStream_t)stream;
   float* d_bias = nullptr; void* d_w = nullptr;
   std::vector<float> bias(align_up((size_t)c_out, 4), 0.f);
   memcpy(bias.data(), bias_host, sizeof(float) * c_out);
   CUDA_TRY(nullptr, cudaMalloc((void**)&d_bias, bias.size() * 4));
   CUDA_TRY(nullptr, cudaMemcpy(d_bias, bias.data(), bias.size() * 4, cudaMemcpyHostToDevice));
-  a.bias = d_bias;
   cudaError_t e;
-  if (use_umma == 2) {
-    if (act == ACT_F32 || !tc_supported(c_in, c_out, ntaps, mx - mn)) {
+  if (engine == 1) {
+    if (act == ACT_F32 || in_slope != 1.0f || mrf_mode != MRF_NONE || !tc_supported(c_in, c_out, ntaps, mx - mn)) {
       cudaFree(d_bias);
-      return fail(nullptr, HFG_ERR_UNSUPPORTED, "persistent tcgen05 kernel does not cover c_in=%d c_out=%d ntaps=%d span=%d act=%d", c_in, c_out, ntaps, mx - mn, act);
+      return fail(nullptr, HFG_ERR_UNSUPPORTED, "tcgen05 kernel does not cover c_in=%d c_out=%d ntaps=%d span=%d act=%d in_slope=%g mrf_mode=%d",
+                  c_in, c_out, ntaps, mx - mn, act, in_slope, mrf_mode);
     }
-    if (mrf_mode != MRF_NONE) { cudaFree(d_bias); return fail(nullptr, HFG_ERR_UNSUPPORTED, "use res2/out_scale through the engine for MRF on the persistent kernel"); }
     const size_t nb = tc_packed_weight_bytes(c_in, c_out, ntaps);
     std::vector<char> pk(nb);
     tc_pack_weights(w_host, ntaps, c_in, c_out, (ActType)act, pk.data());
     CUDA_TRY(nullptr, cudaMalloc(&d_w, nb));
     CUDA_TRY(nullptr, cudaMemcpy(d_w, pk.data(), nb, cudaMemcpyHostToDevice));
     TcArgs t{};
-    t.x = x_dev; t.out = out_dev; t.res = res_dev; t.res2 = nullptr; t.bias = d_bias;
+    t.x = x_dev; t.out = out_dev; t.res = res_dev; t.res2 = res2_dev; t.bias = d_bias;
     t.B = B; t.x_rows = x_rows; t.n_q = x_rows; t.out_rows = x_rows * out_stride; t.out_stride = out_stride;
-    t.c_in = c_in; t.c_out = c_out; t.in_slope = in_slope; t.out_scale = 1.0f; t.out_slope = 1.0f;
+    t.c_in = c_in; t.c_out = c_out; t.res_inv = res_inv; t.out_scale = out_scale; t.out_slope = out_slope;
     t.nvar = 1; t.var[0].w = d_w; t.var[0].ntaps = ntaps; t.var[0].out_off = out_off;
     for (int j = 0; j < ntaps; ++j) t.var[0].tap_off[j] = tap_off[j];
     e = launch_conv_tc(t, (ActType)act, s, nullptr);
-  } else if (use_umma) {
-    if (act == ACT_F32 || !umma_supported(c_in, c_out, ntaps, mx - mn)) {
-      cudaFree(d_bias);
-      return fail(nullptr, HFG_ERR_UNSUPPORTED, "tcgen05 kernel does not cover c_in=%d c_out=%d ntaps=%d span=%d act=%d", c_in, c_out, ntaps, mx - mn, act);
-    }
-    const size_t nb = umma_packed_weight_bytes(c_in, c_out, ntaps);
-    std::vector<char> pk(nb);
-    umma_pack_weights(w_host, ntaps, c_in, c_out, (ActType)act, pk.data());
-    CUDA_TRY(nullptr, cudaMalloc(&d_w, nb));
-    CUDA_TRY(nullptr, cudaMemcpy(d_w, pk.data(), nb, cudaMemcpyHostToDevice));
-    a.w = d_w;
-    e = launch_conv_umma(a, (ActType)act, s);
   } else {
+    ConvArgs a{};
+    a.x = x_dev; a.out = out_dev; a.res = res_dev; a.acc = acc_dev;
+    a.B = B; a.x_rows = x_rows; a.n_q = x_rows; a.out_rows = x_rows * out_stride;
+    a.c_in = c_in; a.c_out = c_out; a.ntaps = ntaps;
+    for (int j = 0; j < ntaps; ++j) a.tap_off[j] = tap_off[j];
+    a.out_stride = out_stride; a.out_off = out_off; a.in_slope = in_slope; a.mrf_mode = mrf_mode; a.mrf_div = mrf_div;
+    a.out_slope = out_slope;
     const size_t nb = (size_t)ntaps * c_in * c_out * 4;
     CUDA_TRY(nullptr, cudaMalloc(&d_w, nb));
     CUDA_TRY(nullptr, cudaMemcpy(d_w, w_host, nb, cudaMemcpyHostToDevice));
-    a.w = d_w;
+    a.w = d_w; a.bias = d_bias;
     e = launch_conv_ffma(a, (ActType)act, s);
   }
   if (e == cudaSuccess) e = cudaStreamSynchronize(s);

@@ -27,7 +27,7 @@ enum MrfMode : int {
 // k/u taps j == (p+P) mod u at input offsets (p+P-j)/u   (polyphase, no zero insertion).
 struct ConvArgs {
   const void* x;        // [B, x_rows, c_in] activations (ActType)
-  const void* w;        // FFMA: fp32 [ntaps][c_in][c_out]; UMMA: packed 16-bit tiles
+  const void* w;        // fp32 [ntaps][c_in][c_out]
   const float* bias;    // [c_out] fp32
   void* out;            // [B, out_rows, c_out] (ActType)
   const void* res;      // residual, indexed like out (ActType) or nullptr
@@ -43,6 +43,8 @@ struct ConvArgs {
   float in_slope;       // leaky-relu slope applied to x while staging (1 = identity)
   int mrf_mode;
   float mrf_div;        // num_kernels
+  float out_slope;      // leaky-relu applied to the stored output (MRF_NONE / MRF_FINAL), 1 = none: used when the
+                        // consumer is the tcgen05 kernel, which expects its input already activated
 };
 
 // conv_post + tanh (reference model.py:169-171): C_out = 1
@@ -61,22 +63,16 @@ cudaError_t launch_conv_post(const PostArgs& a, ActType act, cudaStream_t s);
 cudaError_t launch_cast_pad(const float* src, void* dst, long long rows, int c_src, int c_dst,
                             ActType act, cudaStream_t s);
 
-// tcgen05 implicit-GEMM kernels (conv_umma.cu)
-bool umma_supported(int c_in, int c_out, int ntaps, int span);
-size_t umma_packed_weight_bytes(int c_in, int c_out, int ntaps);
-// host-side repack of fp32 [ntaps][c_in][c_out] into the kernel's smem-image tiles (16-bit)
-void umma_pack_weights(const float* w, int ntaps, int c_in, int c_out, ActType act, void* dst_host);
-cudaError_t launch_conv_umma(const ConvArgs& a, ActType act, cudaStream_t s);
-
-
 // ---------------------------------------------------------------- persistent tcgen05 kernel (conv_tc.cu)
 // One launch = one layer: every output phase ("variant") of a Conv1DTranspose, or the single
-// variant of a Conv1D.   out[b, q*out_stride + var.out_off, co] =
-//     lrelu_out( (bias[co] + sum_j sum_ci lrelu_in(x[b, q + var.tap_off[j], ci]) * W_var[j][ci][co]
-//                 + res[...] + res2[...]) * out_scale )
+// variant of a Conv1D.  x is stored already activated for this layer (see conv_tc.cu):
+//   v = bias[co] + sum_j sum_ci x[b, q + var.tap_off[j], ci] * W_var[j][ci][co]
+//       + unact(res[...]) + res2[...]                      unact(y) = y >= 0 ? y : y * res_inv
+//   out[b, q*out_stride + var.out_off, co] = lrelu(v * out_scale, out_slope)
 // res / res2 are indexed like out (16-bit, may be NULL): res is the ResBlock skip connection
-// (reference model.py:79,111), res2 the running MRF sum xs (model.py:161-166); out_scale = 1/num_kernels
-// on the last resblock (model.py:167).
+// (reference model.py:79,111) stored activated with slope 1/res_inv, res2 the running raw MRF sum xs
+// (model.py:161-166); out_scale = 1/num_kernels on the last resblock (model.py:167); out_slope is the
+// activation the consumer of `out` would apply (model.py:73,76,108,159,169), 1 = store raw.
 constexpr int kMaxVariants = 8;
 struct TcVariant {
   const void* w;        // packed weights of this variant (see tc_pack_weights)
@@ -92,18 +88,19 @@ struct TcArgs {
   const float* bias;
   int B, x_rows, n_q, out_rows, out_stride;
   int c_in, c_out;
-  float in_slope, out_scale, out_slope;
+  float res_inv, out_scale, out_slope;
   int nvar;
   TcVariant var[kMaxVariants];
 };
 struct TcConfig {       // tile configuration chosen for (c_in, c_out); see conv_tc.cu
-  int n, mb, ks, kbw, nst, nsl, pw;
+  int n, mb, ks, kbw, nst, nsl, nstg;
 };
 bool tc_config(int c_in, int c_out, TcConfig* cfg);
 bool tc_supported(int c_in, int c_out, int ntaps, int span);
 size_t tc_packed_weight_bytes(int c_in, int c_out, int ntaps);
 // host-side repack of fp32 [ntaps][c_in][c_out] into the kernel's smem-image weight stages (16-bit)
 void tc_pack_weights(const float* w, int ntaps, int c_in, int c_out, ActType act, void* dst_host);
+// returns cudaSuccess or an error; *msg (optional) receives a static description on failure
 cudaError_t launch_conv_tc(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out);
 
 }  // namespace hfg

@@ -191,6 +191,12 @@ class Generator:
         _lib.check(self._lib.hfg_last_launch_count(self._handle, C.byref(n)), self._handle)
         return int(n.value)
 
+    def layer_engines(self) -> Dict[str, str]:
+        """layer name -> "tc" (persistent tcgen05 kernel) | "ffma" (direct kernel) | "post"."""
+        buf = C.create_string_buffer(1 << 14)
+        _lib.check(self._lib.hfg_layer_engines(self._handle, buf, len(buf)), self._handle)
+        return dict(line.split(":") for line in buf.value.decode().strip().split("\n"))
+
     def stage_times_ms(self):
         buf = (C.c_float * 16)()
         n = C.c_int(16)

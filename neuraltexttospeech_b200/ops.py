@@ -13,10 +13,12 @@ from . import _lib
 _ACT = {"fp32": 0, "fp16": 1, "bf16": 2}
 
 
-def tapped_conv(x, w: np.ndarray, bias: np.ndarray, tap_off: Sequence[int], *, engine: str = "umma",
-                out_stride: int = 1, out_off: int = 0, in_slope: float = 1.0, res=None, acc=None,
+def tapped_conv(x, w: np.ndarray, bias: np.ndarray, tap_off: Sequence[int], *, engine: str = "tc",
+                out_stride: int = 1, out_off: int = 0, in_slope: float = 1.0, res=None, res_inv: float = 1.0,
+                res2=None, out_scale: float = 1.0, out_slope: float = 1.0, acc=None,
                 mrf_mode: int = 0, mrf_div: float = 3.0, out=None):
-    """x: torch CUDA tensor [B, rows, c_in] (float32 / float16 / bfloat16); w: fp32 [ntaps, c_in, c_out]."""
+    """x: torch CUDA tensor [B, rows, c_in] (float32 / float16 / bfloat16); w: fp32 [ntaps, c_in, c_out].
+    engine "ffma" = direct kernel, "tc" = persistent tcgen05 kernel (see include/hifigan_b200.h)."""
     import torch
     lib = _lib.load()
     act = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}[x.dtype]
@@ -30,12 +32,11 @@ def tapped_conv(x, w: np.ndarray, bias: np.ndarray, tap_off: Sequence[int], *, e
     if out is None:
         out = torch.zeros((B, rows * out_stride, c_out), dtype=x.dtype, device=x.device)
     taps = (C.c_int * ntaps)(*[int(t) for t in tap_off])
-    rc = lib.hfg_op_tapped_conv(act, {"ffma": 0, "umma": 1, "tc": 2}[engine], C.c_void_p(x.data_ptr()), B, rows, c_in,
+    ptr = lambda t: C.c_void_p(t.data_ptr()) if t is not None else None
+    rc = lib.hfg_op_tapped_conv(act, {"ffma": 0, "tc": 1}[engine], ptr(x), B, rows, c_in,
                                 w.ctypes.data_as(C.c_void_p), bias.ctypes.data_as(C.c_void_p), c_out, ntaps, taps,
-                                out_stride, out_off, float(in_slope),
-                                C.c_void_p(res.data_ptr()) if res is not None else None,
-                                C.c_void_p(acc.data_ptr()) if acc is not None else None,
-                                int(mrf_mode), float(mrf_div), C.c_void_p(out.data_ptr()),
+                                out_stride, out_off, float(in_slope), ptr(res), float(res_inv), ptr(res2),
+                                float(out_scale), float(out_slope), ptr(acc), int(mrf_mode), float(mrf_div), ptr(out),
                                 C.c_void_p(torch.cuda.current_stream(x.device).cuda_stream))
     _lib.check(rc, None, "hfg_op_tapped_conv")
     return out

@@ -39,8 +39,12 @@ SHAPES = [  # (c_in, c_out, taps, B, rows)
 ]
 
 
+def lrelu(v, s):
+    return np.where(v >= 0, v, v * np.float32(s)).astype(np.float32)
+
+
 @pytest.mark.parametrize("cin,cout,taps,B,rows", SHAPES)
-@pytest.mark.parametrize("engine,dtype", [("ffma", "float32"), ("tc", "float16"), ("tc", "bfloat16"), ("umma", "float16"), ("umma", "bfloat16"), ("ffma", "float16")])
+@pytest.mark.parametrize("engine,dtype", [("ffma", "float32"), ("tc", "float16"), ("tc", "bfloat16"), ("ffma", "float16")])
 def test_tapped_conv(cin, cout, taps, B, rows, engine, dtype):
     import torch
     from neuraltexttospeech_b200.ops import tapped_conv
@@ -50,24 +54,50 @@ def test_tapped_conv(cin, cout, taps, B, rows, engine, dtype):
     w = (rng.standard_normal((len(taps), cin, cout)) / np.sqrt(cin * len(taps))).astype(np.float32)
     bias = rng.uniform(-0.1, 0.1, cout).astype(np.float32)
     res = rng.standard_normal((B, rows, cout)).astype(np.float32)
-    xt = torch.from_numpy(x).cuda().to(tdt)
-    rt = torch.from_numpy(res).cuda().to(tdt)
-    xq, rq = xt.float().cpu().numpy(), rt.float().cpu().numpy()
-    wq = w if dtype == "float32" else torch.from_numpy(w).to(tdt).float().numpy()
-    if engine == "ffma":
-        wq = w                                            # the direct kernel keeps fp32 weights
-    ref = ref_tapped_conv(xq, wq, bias, taps, in_slope=0.1, res=rq)
-    if dtype != "float32":                                # the kernel rounds the activated input to 16 bit
-        xa = torch.from_numpy(np.where(xq >= 0, xq, xq * np.float32(0.1))).to(tdt).float().numpy()
-        if engine in ("umma", "tc"):
-            ref = ref_tapped_conv(xa, wq, bias, taps, in_slope=1.0, res=rq)
-    out = tapped_conv(xt, w, bias, taps, engine=engine, in_slope=0.1, res=rt).float().cpu().numpy()
     tol = {"float32": 2e-5, "float16": 4e-3, "bfloat16": 3e-2}[dtype]   # output rounding of O(1) values
+    if engine == "ffma":
+        xt = torch.from_numpy(x).cuda().to(tdt)
+        rt = torch.from_numpy(res).cuda().to(tdt)
+        xq, rq = xt.float().cpu().numpy(), rt.float().cpu().numpy()
+        ref = ref_tapped_conv(xq, w, bias, taps, in_slope=0.1, res=rq)       # the direct kernel keeps fp32 weights
+        out = tapped_conv(xt, w, bias, taps, engine="ffma", in_slope=0.1, res=rt).float().cpu().numpy()
+        assert np.abs(out - ref).max() <= tol
+        return
+    # tcgen05 kernel: x and res are stored already activated (slope 0.1); output stored activated with 0.3
+    xt = torch.from_numpy(lrelu(x, 0.1)).cuda().to(tdt)
+    rt = torch.from_numpy(lrelu(res, 0.1)).cuda().to(tdt)
+    xq, rq = xt.float().cpu().numpy(), rt.float().cpu().numpy()
+    wq = torch.from_numpy(w).to(tdt).float().numpy()
+    res_raw = np.where(rq >= 0, rq, rq * np.float32(10.0))
+    ref = lrelu(ref_tapped_conv(xq, wq, bias, taps, in_slope=1.0, res=res_raw), 0.3)
+    out = tapped_conv(xt, w, bias, taps, engine="tc", res=rt, res_inv=10.0, out_slope=0.3).float().cpu().numpy()
     assert np.abs(out - ref).max() <= tol
 
 
-@pytest.mark.parametrize("engine,dtype", [("ffma", "float32"), ("umma", "float16")])
-def test_transposed_phase_and_mrf_modes(engine, dtype):
+def test_tc_mrf_sum_and_scale():
+    """res2 (running MRF sum) and out_scale = 1/num_kernels of the tcgen05 epilogue (reference model.py:161-167)."""
+    import torch
+    from neuraltexttospeech_b200.ops import tapped_conv
+    rng = np.random.default_rng(9)
+    B, rows, c = 2, 333, 64
+    x = torch.from_numpy(rng.standard_normal((B, rows, c)).astype(np.float32)).cuda().half()
+    res = torch.from_numpy(rng.standard_normal((B, rows, c)).astype(np.float32)).cuda().half()
+    s2 = torch.from_numpy(rng.standard_normal((B, rows, c)).astype(np.float32)).cuda().half()
+    w = (rng.standard_normal((3, c, c)) / 14).astype(np.float32)
+    bias = rng.uniform(-0.1, 0.1, c).astype(np.float32)
+    taps = [-2, -1, 0]
+    wq = torch.from_numpy(w).half().float().numpy()
+    ref = (ref_tapped_conv(x.float().cpu().numpy(), wq, bias, taps, res=res.float().cpu().numpy()) + s2.float().cpu().numpy()) / 3
+    out = tapped_conv(x, w, bias, taps, engine="tc", res=res, res_inv=1.0, res2=s2, out_scale=1.0 / 3).float().cpu().numpy()
+    assert np.abs(out - ref).max() <= 4e-3
+    # in place on the sum buffer (how the engine accumulates xs)
+    s2b = s2.clone()
+    tapped_conv(x, w, bias, taps, engine="tc", res=res, res_inv=1.0, res2=s2b, out=s2b)
+    assert np.abs(s2b.float().cpu().numpy() - ref * 3).max() <= 8e-3
+
+
+@pytest.mark.parametrize("engine,dtype", [("ffma", "float32"), ("tc", "float16")])
+def test_transposed_phases(engine, dtype):
     import torch
     from neuraltexttospeech_b200.ops import tapped_conv
     rng = np.random.default_rng(5)
@@ -77,23 +107,31 @@ def test_transposed_phase_and_mrf_modes(engine, dtype):
     bias = rng.uniform(-0.1, 0.1, cout).astype(np.float32)
     out = torch.zeros((B, rows * u, cout), dtype=tdt, device="cuda")
     ref = np.zeros((B, rows * u, cout))
+    xq = x.float().cpu().numpy()
     for p in range(u):
         w = (rng.standard_normal((2, cin, cout)) / 12).astype(np.float32)
         taps = [-1, 0] if p == 0 else [0, 1]
-        tapped_conv(x, w, bias, taps, engine=engine, out_stride=u, out_off=p, in_slope=0.1, out=out)
+        tapped_conv(x, w, bias, taps, engine=engine, out_stride=u, out_off=p, out=out)
         wq = w if engine == "ffma" else torch.from_numpy(w).to(tdt).float().numpy()
-        xq = x.float().cpu().numpy()
-        xa = torch.from_numpy(np.where(xq >= 0, xq, xq * np.float32(0.1))).to(tdt).float().numpy()
-        ref += ref_tapped_conv(xa, wq, bias, taps, out_stride=u, out_off=p)      # other phases' rows stay 0
+        ref += ref_tapped_conv(xq, wq, bias, taps, out_stride=u, out_off=p)      # other phases' rows stay 0
     tol = 2e-5 if dtype == "float32" else 4e-3
     assert np.abs(out.float().cpu().numpy() - ref).max() <= tol
+
+
+def test_ffma_mrf_modes():
     # MRF: acc = v0; acc += v1; out = (acc + v2) / 3   (reference model.py:161-167)
+    import torch
+    from neuraltexttospeech_b200.ops import tapped_conv
+    rng = np.random.default_rng(6)
+    B, rows, cin, cout = 2, 300, 64, 32
+    x = torch.from_numpy(rng.standard_normal((B, rows, cin)).astype(np.float32)).cuda()
+    bias = rng.uniform(-0.1, 0.1, cout).astype(np.float32)
     acc = torch.zeros((B, rows, cout), dtype=torch.float32, device="cuda")
     ws = [(rng.standard_normal((3, cin, cout)) / 14).astype(np.float32) for _ in range(3)]
     taps = [-1, 0, 1]
-    tapped_conv(x, ws[0], bias, taps, engine=engine, acc=acc, mrf_mode=1)
-    tapped_conv(x, ws[1], bias, taps, engine=engine, acc=acc, mrf_mode=2)
-    fin = tapped_conv(x, ws[2], bias, taps, engine=engine, acc=acc, mrf_mode=3, mrf_div=3.0)
-    xq = x.float().cpu().numpy()
-    tot = sum(ref_tapped_conv(xq, w if engine == "ffma" else torch.from_numpy(w).to(tdt).float().numpy(), bias, taps) for w in ws) / 3
-    assert np.abs(fin.float().cpu().numpy() - tot).max() <= tol
+    tapped_conv(x, ws[0], bias, taps, engine="ffma", acc=acc, mrf_mode=1)
+    tapped_conv(x, ws[1], bias, taps, engine="ffma", acc=acc, mrf_mode=2)
+    fin = tapped_conv(x, ws[2], bias, taps, engine="ffma", acc=acc, mrf_mode=3, mrf_div=3.0, out_slope=0.3)
+    xq = x.cpu().numpy()
+    tot = sum(ref_tapped_conv(xq, w, bias, taps) for w in ws) / 3
+    assert np.abs(fin.cpu().numpy() - lrelu(tot, 0.3)).max() <= 2e-5
