@@ -102,6 +102,13 @@ __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
+// one lane of a converged warp (elect.sync): the pattern the compiler turns into a single predicated issue
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{ .reg .pred P; elect.sync _|P, 0xffffffff; selp.u32 %0, 1, 0, P; }" : "=r"(pred));
+  return pred != 0;
+}
+
 __device__ __forceinline__ void tmem_alloc(uint32_t* slot_smem, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot_smem)), "r"(ncols) : "memory");
   asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -238,12 +245,14 @@ struct TcKArgs {
 };
 
 // ------------------------------------------------------------------ the kernel
-template <typename T, int C_IN, int N, int MB, int KS, int KBW, int NST, int NSL, int NSTG>
+template <typename T, int C_IN, int N, int MB, int KS, int KBW, int TPS, int NST, int NSL, int NSTG>
 __global__ void __launch_bounds__(kTcThreads, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_res,
                const __grid_constant__ CUtensorMap tm_out, const __grid_constant__ TcKArgs ka) {
   constexpr int NKS = C_IN / KS;                  // K-slices per tile
-  constexpr int NKB = KS / KBW;                   // weight stages per (slice, tap)
+  constexpr int NKB = KS / KBW;                   // weight k-blocks per (slice, tap)
+  constexpr int BLK_BYTES = N * KBW * 2;          // one (tap, k-block) weight block; a stage holds TPS of them
+  static_assert(TPS == 1 || NKB == 1, "multi-tap stages need KBW == KS");
   constexpr int ROWB = KS * 2;                    // bytes per slab row within a slice (= swizzle width)
   constexpr int PW = N < 64 ? N : 64;             // output columns per epilogue pass
   constexpr int SROWB = PW * 2;                   // bytes per staging row (= swizzle width)
@@ -254,7 +263,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
   static_assert(C_IN % KS == 0 && KS % KBW == 0 && KBW % 16 == 0 && N % 16 == 0 && N <= 256, "tile config");
   static_assert(KS == 64 || KS == 32 || KS == 16, "K-slice = one swizzle row");
   static_assert(N % PW == 0, "pass width");
-  const TcSmemPlan pl = tc_plan(N, KS, KBW, NST, NSL, NSTG, ka.nbox * ka.box_rows);
+  const TcSmemPlan pl = tc_plan(N, KS, KBW * TPS, NST, NSL, NSTG, ka.nbox * ka.box_rows);
 
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* slab = smem;
@@ -294,97 +303,119 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
     qt = t % ka.tiles_q; b = t / ka.tiles_q;
   };
 
+  // Producer / MMA warps run their loops with ALL lanes (warp-uniform control flow keeps barrier addresses and
+  // descriptors in uniform registers) and issue the asynchronous instructions from one elected lane.
   if (warp == 0) {
     // ===================== slab producer (TMA) =====================
-    if (lane == 0) {
-      uint32_t scnt = 0;
-      const uint32_t box_bytes = (uint32_t)ka.box_rows * ROWB;
-      for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x) {
-        int b, qt, v, nt; decode(t, b, qt, v, nt);
-        const int row_base = qt * (MB * 128) + ka.min_off;
-        for (int s = 0; s < NKS; ++s, ++scnt) {
-          const int pos = scnt % NSL;
-          mbar_wait(&slice_empty[pos], ((scnt / NSL) & 1) ^ 1);
+    uint32_t scnt = 0;
+    const uint32_t box_bytes = (uint32_t)ka.box_rows * ROWB;
+    for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x) {
+      int b, qt, v, nt; decode(t, b, qt, v, nt);
+      const int row_base = qt * (MB * 128) + ka.min_off;
+      for (int s = 0; s < NKS; ++s, ++scnt) {
+        const int pos = scnt % NSL;
+        mbar_wait(&slice_empty[pos], ((scnt / NSL) & 1) ^ 1);
+        if (elect_one()) {
           mbar_expect_tx(&slice_full[pos], box_bytes * ka.nbox);
           uint8_t* dst = slab + pos * pl.slice_bytes;
           for (int bx = 0; bx < ka.nbox; ++bx)
             tma_load_3d(dst + bx * box_bytes, &tm_x, s * KS, row_base + bx * ka.box_rows, b, &slice_full[pos]);
         }
+        __syncwarp();
       }
     }
   } else if (warp == 1) {
     // ===================== weight producer =====================
-    if (lane == 0) {
-      uint32_t wcnt = 0;
-      for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x) {
-        int b, qt, v, nt; decode(t, b, qt, v, nt);
-        const int n_it = NKS * ka.var[v].ntaps * NKB;
-        const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(ka.var[v].w) + (size_t)nt * n_it * pl.stage_bytes;
-        for (int it = 0; it < n_it; ++it, ++wcnt) {
-          const int st = wcnt % NST;
-          mbar_wait(&w_empty[st], ((wcnt / NST) & 1) ^ 1);
-          mbar_expect_tx(&w_full[st], pl.stage_bytes);
-          bulk_g2s(wst + st * pl.stage_bytes, wsrc + (size_t)it * pl.stage_bytes, pl.stage_bytes, &w_full[st]);
+    uint32_t wcnt = 0;
+    for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x) {
+      int b, qt, v, nt; decode(t, b, qt, v, nt);
+      const int ntaps = ka.var[v].ntaps;
+      const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(ka.var[v].w) + (size_t)nt * (NKS * ntaps * NKB) * BLK_BYTES;
+      for (int s = 0; s < NKS; ++s) {
+        for (int j0 = 0; j0 < ntaps; j0 += TPS) {
+          const int nj = (ntaps - j0) < TPS ? (ntaps - j0) : TPS;
+          for (int kb = 0; kb < NKB; ++kb, ++wcnt) {
+            const int st = wcnt % NST;
+            const uint32_t bytes = (uint32_t)nj * BLK_BYTES;
+            mbar_wait(&w_empty[st], ((wcnt / NST) & 1) ^ 1);
+            if (elect_one()) {
+              mbar_expect_tx(&w_full[st], bytes);
+              bulk_g2s(wst + st * pl.stage_bytes, wsrc, bytes, &w_full[st]);
+            }
+            __syncwarp();
+            wsrc += bytes;
+          }
         }
       }
     }
   } else if (warp == 2) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
-      const uint32_t slab_addr = smem_u32(slab), wst_addr = smem_u32(wst);
-      uint32_t scnt = 0, wcnt = 0, tcnt = 0;
-      for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x, ++tcnt) {
-        int b, qt, v, nt; decode(t, b, qt, v, nt);
-        const TcVariant& var = ka.var[v];
-        const int abuf = tcnt % NACC;
-        mbar_wait(&acc_empty[abuf], ((tcnt / NACC) & 1) ^ 1);
+    const uint32_t slab_addr = smem_u32(slab), wst_addr = smem_u32(wst);
+    uint32_t scnt = 0, wcnt = 0, tcnt = 0;
+    for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x, ++tcnt) {
+      int b, qt, v, nt; decode(t, b, qt, v, nt);
+      const int ntaps = ka.var[v].ntaps;
+      const int abuf = tcnt % NACC;
+      mbar_wait(&acc_empty[abuf], ((tcnt / NACC) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + abuf * ACC_COLS;
+      uint32_t first = 1;
+#pragma unroll 1
+      for (int s = 0; s < NKS; ++s, ++scnt) {
+        const int pos = scnt % NSL;
+        mbar_wait(&slice_full[pos], (scnt / NSL) & 1);
         tc_fence_after();
-        const uint32_t tacc = tmem_base + abuf * ACC_COLS;
-        uint32_t first = 1;
+        const uint32_t sl = slab_addr + pos * pl.slice_bytes;
 #pragma unroll 1
-        for (int s = 0; s < NKS; ++s, ++scnt) {
-          const int pos = scnt % NSL;
-          mbar_wait(&slice_full[pos], (scnt / NSL) & 1);
-          tc_fence_after();
-          const uint32_t sl = slab_addr + pos * pl.slice_bytes;
+        for (int j0 = 0; j0 < ntaps; j0 += TPS) {
+          const int nj = (ntaps - j0) < TPS ? (ntaps - j0) : TPS;
 #pragma unroll 1
-          for (int j = 0; j < var.ntaps; ++j) {
-            const uint32_t row_off = (uint32_t)(var.tap_off[j] - ka.min_off);
-#pragma unroll 1
-            for (int kb = 0; kb < NKB; ++kb, ++wcnt) {
-              const int st = wcnt % NST;
-              mbar_wait(&w_full[st], (wcnt / NST) & 1);
-              tc_fence_after();
+          for (int kb = 0; kb < NKB; ++kb, ++wcnt) {
+            const int st = wcnt % NST;
+            mbar_wait(&w_full[st], (wcnt / NST) & 1);
+            tc_fence_after();
+            if (elect_one()) {
               const uint32_t wb = wst_addr + st * pl.stage_bytes;
+#pragma unroll 1
+              for (int jj = 0; jj < nj; ++jj) {
+                const uint32_t row_off = (uint32_t)(ka.var[v].tap_off[j0 + jj] - ka.min_off);
+                const uint64_t a0 = make_desc_sw<ROWB>(sl + row_off * ROWB + kb * KBW * 2);
+                const uint64_t b0 = make_desc(wb + jj * BLK_BYTES, N * 16, 128u);
 #pragma unroll
-              for (int mb = 0; mb < MB; ++mb) {
+                for (int mb = 0; mb < MB; ++mb) {
 #pragma unroll
-                for (int kk = 0; kk < KBW / 16; ++kk) {
-                  const uint64_t adesc = make_desc_sw<ROWB>(sl + (mb * 128 + row_off) * ROWB + (kb * KBW + kk * 16) * 2);
-                  const uint64_t bdesc = make_desc(wb + (kk * 2) * N * 16, N * 16, 128u);
-                  umma_f16(tacc + mb * N, adesc, bdesc, IDESC, (first && kk == 0) ? 0u : 1u);
+                  for (int kk = 0; kk < KBW / 16; ++kk) {
+                    // descriptor start-address field counts 16-byte units: advance with plain adds
+                    const uint64_t adesc = a0 + (uint64_t)((mb * 128 * ROWB + kk * 32) >> 4);
+                    const uint64_t bdesc = b0 + (uint64_t)((kk * 2 * N * 16) >> 4);
+                    umma_f16(tacc + mb * N, adesc, bdesc, IDESC, (first && kk == 0) ? 0u : 1u);
+                  }
                 }
+                first = 0;
               }
-              first = 0;
               umma_commit(&w_empty[st]);          // frees the weight stage when these MMAs retire
+              if (kb == NKB - 1 && j0 + TPS >= ntaps) {
+                umma_commit(&slice_empty[pos]);   // slab slice may be overwritten
+                if (s == NKS - 1) umma_commit(&acc_full[abuf]);   // accumulators of this tile complete
+              }
             }
+            first = 0;
+            __syncwarp();
           }
-          umma_commit(&slice_empty[pos]);         // slab slice may be overwritten
         }
-        umma_commit(&acc_full[abuf]);             // accumulators of this tile complete
       }
     }
   } else if (warp == 3) {
     // ===================== staging producer: residual tiles (or just buffer grants) =====================
-    if (lane == 0) {
-      uint32_t pcnt = 0;
-      for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x) {
-        int b, qt, v, nt; decode(t, b, qt, v, nt);
-        for (int mb = 0; mb < MB; ++mb) {
-          const int q0 = qt * (MB * 128) + mb * 128;
-          for (int p0 = 0; p0 < N; p0 += PW, ++pcnt) {
-            const int buf = pcnt % NSTG;
-            mbar_wait(&stg_empty[buf], ((pcnt / NSTG) & 1) ^ 1);
+    uint32_t pcnt = 0;
+    for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x) {
+      int b, qt, v, nt; decode(t, b, qt, v, nt);
+      for (int mb = 0; mb < MB; ++mb) {
+        const int q0 = qt * (MB * 128) + mb * 128;
+        for (int p0 = 0; p0 < N; p0 += PW, ++pcnt) {
+          const int buf = pcnt % NSTG;
+          mbar_wait(&stg_empty[buf], ((pcnt / NSTG) & 1) ^ 1);
+          if (elect_one()) {
             if (ka.has_res && q0 < ka.n_q) {
               mbar_expect_tx(&stg_full[buf], pl.stg_bytes);
               tma_load_4d(stg + buf * pl.stg_bytes, &tm_res, nt * N + p0, 0, q0, b, &stg_full[buf]);
@@ -392,6 +423,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
               mbar_arrive(&stg_full[buf]);
             }
           }
+          __syncwarp();
         }
       }
     }
@@ -564,7 +596,7 @@ void tc_boxes(int rows, int* box_rows, int* nbox) {
   *box_rows = best_br; *nbox = (rows + best_br - 1) / best_br;
 }
 
-template <typename T, int C_IN, int N, int MB, int KS, int KBW, int NST, int NSL, int NSTG>
+template <typename T, int C_IN, int N, int MB, int KS, int KBW, int TPS, int NST, int NSL, int NSTG>
 cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out) {
   constexpr int PW = N < 64 ? N : 64;
   TcKArgs ka{};
@@ -579,7 +611,7 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
   if (ka.span > kTcMaxSpan) return cudaErrorInvalidValue;
   if ((a.res || a.res2) && a.out_stride != 1) return cudaErrorInvalidValue;
   tc_boxes(MB * 128 + ka.span, &ka.box_rows, &ka.nbox);
-  const TcSmemPlan pl = tc_plan(N, KS, KBW, NST, NSL, NSTG, ka.nbox * ka.box_rows);
+  const TcSmemPlan pl = tc_plan(N, KS, KBW * TPS, NST, NSL, NSTG, ka.nbox * ka.box_rows);
   if ((size_t)pl.total > kTcMaxSmem) return cudaErrorInvalidConfiguration;
   ka.tiles_q = (a.n_q + MB * 128 - 1) / (MB * 128);
   ka.n_tiles = a.c_out / N;
@@ -589,7 +621,7 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
   if (!make_map4(&tm_out, act, a.out, a.c_out, a.out_stride, a.n_q, a.B, PW)) return cudaErrorNotSupported;
   if (a.res) { if (!make_map4(&tm_res, act, a.res, a.c_out, 1, a.n_q, a.B, PW)) return cudaErrorNotSupported; }
   else tm_res = tm_out;
-  auto kern = conv_tc_kernel<T, C_IN, N, MB, KS, KBW, NST, NSL, NSTG>;
+  auto kern = conv_tc_kernel<T, C_IN, N, MB, KS, KBW, TPS, NST, NSL, NSTG>;
   static int configured = 0, occ = 1;      // per instantiation
   if (pl.total > configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total);
@@ -615,22 +647,24 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
 }
 
 struct TcRow { int c_in, c_out_tile; TcConfig cfg; };
-//   c_in  n     {n,  mb, ks, kbw, nst, nsl, nstg}
-#define HFG_TC_TABLE(X)            \
-  X(512, 256, 1, 64, 16, 6, 3, 3)  \
-  X(256, 256, 2, 64, 16, 6, 3, 3)  \
-  X(128, 256, 1, 64, 16, 6, 2, 3)  \
-  X(256, 128, 2, 64, 32, 4, 3, 3)  \
-  X(128, 128, 2, 64, 32, 4, 3, 3)  \
-  X(128, 64, 4, 64, 64, 3, 2, 3)   \
-  X(64, 64, 4, 64, 64, 3, 2, 3)    \
-  X(64, 32, 4, 64, 64, 4, 2, 4)    \
-  X(32, 32, 4, 32, 32, 4, 3, 4)    \
-  X(32, 16, 4, 32, 32, 4, 3, 4)    \
-  X(16, 16, 4, 16, 16, 4, 3, 4)
+// Stage work at full tensor rate = MB * TPS * (KBW/16) * N/2 cycles: kept >= 512 so that the per-stage
+// barrier round trip of the single issuing thread is amortised.
+//   c_in  n    mb  ks kbw tps nst nsl nstg
+#define HFG_TC_TABLE(X)               \
+  X(512, 256, 1, 64, 32, 1, 4, 3, 3)  \
+  X(256, 256, 2, 64, 32, 1, 3, 3, 3)  \
+  X(128, 256, 1, 64, 32, 1, 4, 2, 3)  \
+  X(256, 128, 2, 64, 64, 1, 3, 3, 3)  \
+  X(128, 128, 2, 64, 64, 1, 3, 3, 3)  \
+  X(128, 64, 4, 64, 64, 1, 3, 2, 3)   \
+  X(64, 64, 4, 64, 64, 1, 3, 2, 3)    \
+  X(64, 32, 4, 64, 64, 2, 4, 2, 4)    \
+  X(32, 32, 4, 32, 32, 4, 4, 3, 4)    \
+  X(32, 16, 4, 32, 32, 4, 4, 3, 4)    \
+  X(16, 16, 4, 16, 16, 4, 4, 3, 4)
 
 const TcRow kTcTable[] = {
-#define X(CI, NN, MB, KS, KBW, NST, NSL, NSTG) {CI, NN, {NN, MB, KS, KBW, NST, NSL, NSTG}},
+#define X(CI, NN, MB, KS, KBW, TPS, NST, NSL, NSTG) {CI, NN, {NN, MB, KS, KBW, TPS, NST, NSL, NSTG}},
     HFG_TC_TABLE(X)
 #undef X
 };
@@ -638,7 +672,7 @@ const TcRow kTcTable[] = {
 template <typename T>
 cudaError_t launch_shape(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out) {
   const int ci = a.c_in, n = a.c_out > 256 ? 256 : a.c_out;
-#define X(CI, NN, MB, KS, KBW, NST, NSL, NSTG) if (ci == CI && n == NN) return launch_t<T, CI, NN, MB, KS, KBW, NST, NSL, NSTG>(a, act, s, grid_out);
+#define X(CI, NN, MB, KS, KBW, TPS, NST, NSL, NSTG) if (ci == CI && n == NN) return launch_t<T, CI, NN, MB, KS, KBW, TPS, NST, NSL, NSTG>(a, act, s, grid_out);
   HFG_TC_TABLE(X)
 #undef X
   return cudaErrorInvalidValue;
@@ -660,7 +694,7 @@ bool tc_supported(int c_in, int c_out, int ntaps, int span) {
   if (!tc_config(c_in, c_out, &c)) return false;
   int br, nb;
   tc_boxes(c.mb * 128 + span, &br, &nb);
-  return (size_t)tc_plan(c.n, c.ks, c.kbw, c.nst, c.nsl, c.nstg, br * nb).total <= kTcMaxSmem;
+  return (size_t)tc_plan(c.n, c.ks, c.kbw * c.tps, c.nst, c.nsl, c.nstg, br * nb).total <= kTcMaxSmem;
 }
 
 size_t tc_packed_weight_bytes(int c_in, int c_out, int ntaps) { return (size_t)ntaps * c_in * c_out * 2; }

@@ -93,7 +93,7 @@ struct TcArgs {
   TcVariant var[kMaxVariants];
 };
 struct TcConfig {       // tile configuration chosen for (c_in, c_out); see conv_tc.cu
-  int n, mb, ks, kbw, nst, nsl, nstg;
+  int n, mb, ks, kbw, tps, nst, nsl, nstg;
 };
 bool tc_config(int c_in, int c_out, TcConfig* cfg);
 bool tc_supported(int c_in, int c_out, int ntaps, int span);
