@@ -42,7 +42,8 @@ namespace hfg {
 
 namespace {
 
-constexpr int kTcThreads = 256;
+constexpr int kTcThreads = 416;       // 13 warps: 4 producers/MMA, 2 x 4 epilogue, 1 store issuer
+constexpr int kTcMaxCout = 512;
 constexpr int kTcMaxSpan = 96;       // largest max_off - min_off supported (V1: 50, V3: 72)
 constexpr size_t kTcMaxSmem = 227 * 1024;
 
@@ -225,9 +226,9 @@ __host__ __device__ inline TcSmemPlan tc_plan(int n, int ks, int kbw, int nst, i
   p.off_stg = off; off += nstg * p.stg_bytes;
   off = (off + 127) & ~127;
   p.off_w = off; off += nst * p.stage_bytes;
-  p.off_bias = off; off += n * 4;
+  p.off_bias = off; off += kTcMaxCout * 4;     // bias of every output channel of the layer
   off = (off + 15) & ~15;
-  p.off_bar = off; off += (2 * nsl + 2 * nst + 2 * nstg + 4) * 8 + 16;
+  p.off_bar = off; off += (2 * nsl + 2 * nst + 3 * nstg + 4) * 8 + 16;
   p.total = off;
   return p;
 }
@@ -276,7 +277,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
   uint64_t* w_empty = w_full + NST;
   uint64_t* stg_full = w_empty + NST;
   uint64_t* stg_empty = stg_full + NSTG;
-  uint64_t* acc_full = stg_empty + NSTG;
+  uint64_t* stg_done = stg_empty + NSTG;
+  uint64_t* acc_full = stg_done + NSTG;
   uint64_t* acc_empty = acc_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
 
@@ -285,12 +287,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
   if (tid == 0) {
     for (int s = 0; s < NSL; ++s) { mbar_init(&slice_full[s], 1); mbar_init(&slice_empty[s], 1); }
     for (int s = 0; s < NST; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
-    for (int s = 0; s < NSTG; ++s) { mbar_init(&stg_full[s], 1); mbar_init(&stg_empty[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 128); }
+    for (int s = 0; s < NSTG; ++s) { mbar_init(&stg_full[s], 1); mbar_init(&stg_empty[s], 1); mbar_init(&stg_done[s], 128); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 256); }
     fence_mbar_init();
     tma_prefetch_desc(&tm_x); tma_prefetch_desc(&tm_res); tma_prefetch_desc(&tm_out);
   }
   if (warp == 2) tmem_alloc(tmem_slot, TMEM_COLS);
+  for (int i = tid; i < ka.c_out; i += kTcThreads) bias_s[i] = ka.bias[i];
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -427,40 +430,57 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
         }
       }
     }
+  } else if (warp == 12) {
+    // ===================== store issuer: TMA tensor store of every finished staging tile =====================
+    uint32_t pcnt = 0;
+    for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x) {
+      int b, qt, v, nt; decode(t, b, qt, v, nt);
+      const int out_off = ka.var[v].out_off;
+      for (int mb = 0; mb < MB; ++mb) {
+        const int q0 = qt * (MB * 128) + mb * 128;
+        for (int p0 = 0; p0 < N; p0 += PW, ++pcnt) {
+          const int buf = pcnt % NSTG;
+          mbar_wait(&stg_done[buf], (pcnt / NSTG) & 1);
+          if (elect_one()) {
+            if (q0 < ka.n_q) {
+              tma_store_4d(&tm_out, stg + buf * pl.stg_bytes, nt * N + p0, out_off, q0, b);
+              bulk_commit();
+              bulk_wait_read<0>();                      // the store has read the tile: the buffer may be refilled
+            }
+            mbar_arrive(&stg_empty[buf]);
+          }
+          __syncwarp();
+        }
+      }
+    }
+    if (elect_one()) bulk_wait_all();                   // same lane every time (elect.sync picks the lowest)
+    __syncwarp();
   } else {
-    // ===================== epilogue warps 4-7 =====================
+    // ===================== epilogue: two groups of 4 warps (4-7, 8-11) take alternate passes =====================
+    const int grp = (warp - 4) >> 2;
     const int quarter = warp & 3;                       // TMEM lane quarter this warp may access
     const int er = quarter * 32 + lane;                 // row of the 128-row block owned by this thread
     const uint32_t lane_base = ((uint32_t)(quarter * 32)) << 16;
-    const int et = tid - 128;                           // 0..127 within the epilogue group
     constexpr int CW = PW >= 32 ? 32 : 16;
     // XOR term of the TMA swizzle for this thread's staging row (row pitch SROWB, 1024-byte aligned tile)
     const int sx = SROWB == 128 ? (er & 7) : (SROWB == 64 ? ((er >> 1) & 3) : ((er >> 2) & 1));
     uint32_t tcnt = 0, pcnt = 0;
-    int bias_nt = -1;
     for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x, ++tcnt) {
       int b, qt, v, nt; decode(t, b, qt, v, nt);
       const int n0 = nt * N;
-      if (nt != bias_nt) {                              // (re)load the bias slice; epilogue-warps-only barrier
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        for (int i = et; i < N; i += 128) bias_s[i] = ka.bias[n0 + i];
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        bias_nt = nt;
-      }
       const int abuf = tcnt % NACC;
       mbar_wait(&acc_full[abuf], (tcnt / NACC) & 1);
       tc_fence_after();
       const uint32_t tacc = tmem_base + lane_base + abuf * ACC_COLS;
-      const int out_off = ka.var[v].out_off;
 #pragma unroll 1
       for (int mb = 0; mb < MB; ++mb) {
         const int q0 = qt * (MB * 128) + mb * 128;
         const int q = q0 + er;
         const bool valid = q < ka.n_q;
-        const bool blk_valid = q0 < ka.n_q;
-        const bool has_res = ka.has_res != 0 && blk_valid;
+        const bool has_res = ka.has_res != 0 && q0 < ka.n_q;
 #pragma unroll 1
         for (int p0 = 0; p0 < N; p0 += PW, ++pcnt) {
+          if ((int)(pcnt & 1) != grp) continue;
           const int buf = pcnt % NSTG;
           uint8_t* my = stg + buf * pl.stg_bytes + er * SROWB;
           mbar_wait(&stg_full[buf], (pcnt / NSTG) & 1);   // residual tile landed / buffer granted
@@ -484,7 +504,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
             tmem_ld_wait();
             float vv[CW];
 #pragma unroll
-            for (int i = 0; i < CW; ++i) vv[i] = __uint_as_float(r[i]) + bias_s[p0 + c0 + i];
+            for (int i = 0; i < CW; ++i) vv[i] = __uint_as_float(r[i]) + bias_s[n0 + p0 + c0 + i];
             if (has_res) {
               const float ri = ka.res_inv;
 #pragma unroll
@@ -518,19 +538,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
             }
           }
           fence_proxy_async();                          // staging writes -> visible to the TMA engine
-          asm volatile("bar.sync 1, 128;" ::: "memory");
-          if (et == 0) {
-            if (blk_valid) tma_store_4d(&tm_out, stg + buf * pl.stg_bytes, n0 + p0, out_off, q0, b);
-            bulk_commit();
-            bulk_wait_read<1>();                        // the previous pass's store has read its tile
-            if (pcnt > 0) mbar_arrive(&stg_empty[(pcnt - 1) % NSTG]);
-          }
+          mbar_arrive(&stg_done[buf]);                  // hand the tile to the store warp
         }
       }
       tc_fence_before();
       mbar_arrive(&acc_empty[abuf]);                    // accumulator buffer may be overwritten
     }
-    if (et == 0) bulk_wait_all();
   }
   tc_fence_before();
   __syncthreads();
@@ -646,22 +659,23 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
   return cudaGetLastError();
 }
 
+// output channels per tile: at most 128 so that two accumulator buffers fit TMEM (epilogue overlaps the MMAs)
+inline int tc_ntile(int c_out) { return c_out > 128 ? 128 : c_out; }
+
 struct TcRow { int c_in, c_out_tile; TcConfig cfg; };
 // Stage work at full tensor rate = MB * TPS * (KBW/16) * N/2 cycles: kept >= 512 so that the per-stage
 // barrier round trip of the single issuing thread is amortised.
 //   c_in  n    mb  ks kbw tps nst nsl nstg
 #define HFG_TC_TABLE(X)               \
-  X(512, 256, 1, 64, 32, 1, 4, 3, 3)  \
-  X(256, 256, 2, 64, 32, 1, 3, 3, 3)  \
-  X(128, 256, 1, 64, 32, 1, 4, 2, 3)  \
-  X(256, 128, 2, 64, 64, 1, 3, 3, 3)  \
-  X(128, 128, 2, 64, 64, 1, 3, 3, 3)  \
-  X(128, 64, 4, 64, 64, 1, 3, 2, 3)   \
-  X(64, 64, 4, 64, 64, 1, 3, 2, 3)    \
-  X(64, 32, 4, 64, 64, 2, 4, 2, 4)    \
-  X(32, 32, 4, 32, 32, 4, 4, 3, 4)    \
-  X(32, 16, 4, 32, 32, 4, 4, 3, 4)    \
-  X(16, 16, 4, 16, 16, 4, 4, 3, 4)
+  X(512, 128, 1, 64, 64, 1, 3, 3, 4)  \
+  X(256, 128, 2, 64, 64, 1, 3, 2, 5)  \
+  X(128, 128, 2, 64, 64, 1, 3, 2, 5)  \
+  X(128, 64, 2, 64, 64, 2, 3, 2, 5)   \
+  X(64, 64, 2, 64, 64, 2, 3, 2, 5)    \
+  X(64, 32, 4, 64, 64, 2, 4, 2, 5)    \
+  X(32, 32, 4, 32, 32, 4, 4, 3, 8)    \
+  X(32, 16, 4, 32, 32, 4, 4, 3, 8)    \
+  X(16, 16, 4, 16, 16, 4, 4, 3, 8)
 
 const TcRow kTcTable[] = {
 #define X(CI, NN, MB, KS, KBW, TPS, NST, NSL, NSTG) {CI, NN, {NN, MB, KS, KBW, TPS, NST, NSL, NSTG}},
@@ -671,7 +685,7 @@ const TcRow kTcTable[] = {
 
 template <typename T>
 cudaError_t launch_shape(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out) {
-  const int ci = a.c_in, n = a.c_out > 256 ? 256 : a.c_out;
+  const int ci = a.c_in, n = tc_ntile(a.c_out);
 #define X(CI, NN, MB, KS, KBW, TPS, NST, NSL, NSTG) if (ci == CI && n == NN) return launch_t<T, CI, NN, MB, KS, KBW, TPS, NST, NSL, NSTG>(a, act, s, grid_out);
   HFG_TC_TABLE(X)
 #undef X
@@ -681,8 +695,8 @@ cudaError_t launch_shape(const TcArgs& a, ActType act, cudaStream_t s, int* grid
 }  // namespace
 
 bool tc_config(int c_in, int c_out, TcConfig* cfg) {
-  const int n = c_out > 256 ? 256 : c_out;
-  if (c_out % n) return false;
+  const int n = tc_ntile(c_out);
+  if (c_out % n || c_out > kTcMaxCout) return false;
   for (const TcRow& r : kTcTable)
     if (r.c_in == c_in && r.c_out_tile == n) { if (cfg) *cfg = r.cfg; return true; }
   return false;
