@@ -39,11 +39,13 @@ def test_sass_contains_blackwell_tensor_core_and_bulk_copy_ops():
     cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
     if not os.path.exists(cuobjdump):
         pytest.skip("cuobjdump not available")
-    sass = subprocess.run([cuobjdump, "-sass", os.path.join(ROOT, "build", "conv_umma.o")],
+    sass = subprocess.run([cuobjdump, "-sass", os.path.join(ROOT, "build", "conv_tc.o")],
                           capture_output=True, text=True).stdout
     assert "UTCHMMA" in sass          # tcgen05.mma
     assert "LDTM" in sass             # tcgen05.ld
-    assert "UBLKCP" in sass           # cp.async.bulk
+    assert "UBLKCP" in sass           # cp.async.bulk (weight stages)
+    assert "UTMALDG" in sass          # cp.async.bulk.tensor loads (TMA halo slabs)
+    assert "UTMASTG" in sass          # TMA tensor stores (epilogue)
     assert "sm_100a" in sass or "SM100" in sass.upper()
 
 
