@@ -8,6 +8,8 @@
 //  * cast_pad_kernel  : fp32 mel -> 16-bit, channel-padded, for the tensor-core conv_pre.
 //
 // Semantics restated from reference HiFiGAN_TF/model.py:71-80,106-112,155-173 (see kernels.cuh).
+#include <type_traits>
+
 #include "kernels.cuh"
 
 namespace hfg {
@@ -193,44 +195,98 @@ cudaError_t launch_conv_ffma(const ConvArgs& a, ActType act, cudaStream_t s) {
 }
 
 // ------------------------------------------------------------------ conv_post + tanh
+// Pure bandwidth kernel (C_out = 1, ~7 FLOP/B).  A block stages kPostRows + ntaps - 1 activation rows in
+// shared memory with coalesced 16-byte loads (rows outside the utterance = TF's zero padding), then each
+// thread produces kPostRows / kPostThreads output samples from the tile; a 16-byte pad per row keeps the
+// row-strided 16-byte shared loads of a quarter-warp on distinct banks (row pitch 80 B for 32 x fp16).
+constexpr int kPostThreads = 256;
+constexpr int kPostRows = 1024;
+
 template <typename T>
-__global__ void __launch_bounds__(256) conv_post_kernel(const PostArgs a) {
-  extern __shared__ float wsm[];                       // [ntaps][c_in]
-  for (int i = threadIdx.x; i < a.ntaps * a.c_in; i += blockDim.x) wsm[i] = a.w[i];
-  __syncthreads();
-  const long long total = (long long)a.B * a.rows;
-  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (gid >= total) return;
-  const int b = (int)(gid / a.rows), t = (int)(gid % a.rows);
-  const T* __restrict__ x = reinterpret_cast<const T*>(a.x) + (size_t)b * a.rows * a.c_in;
-  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-  for (int j = 0; j < a.ntaps; ++j) {
-    const int row = t + j - a.pad_left;
-    if (row < 0 || row >= a.rows) continue;
-    const T* xr = x + (size_t)row * a.c_in;
-    const float* wj = wsm + j * a.c_in;
-    for (int c = 0; c < a.c_in; c += 4) {
-      const float4 v = Act4<T>::load(xr + c);
-      s0 = fmaf(lrelu(v.x, a.in_slope), wj[c + 0], s0);
-      s1 = fmaf(lrelu(v.y, a.in_slope), wj[c + 1], s1);
-      s2 = fmaf(lrelu(v.z, a.in_slope), wj[c + 2], s2);
-      s3 = fmaf(lrelu(v.w, a.in_slope), wj[c + 3], s3);
-    }
+__global__ void __launch_bounds__(kPostThreads) conv_post_kernel(const PostArgs a) {
+  constexpr int EPC = 16 / (int)sizeof(T);             // elements per 16-byte chunk
+  extern __shared__ __align__(16) uint8_t psm[];
+  const int chunks = a.c_in / EPC;                     // 16-byte chunks per row
+  const int pitch = (chunks + 1) * 16;                 // bytes
+  const int tile_rows = kPostRows + a.ntaps - 1;
+  float* wsm = reinterpret_cast<float*>(psm + (size_t)tile_rows * pitch);   // [ntaps][c_in]
+  for (int i = threadIdx.x; i < a.ntaps * a.c_in; i += kPostThreads) wsm[i] = a.w[i];
+  const int b = blockIdx.y;
+  const int t0 = blockIdx.x * kPostRows;
+  const uint8_t* __restrict__ x = reinterpret_cast<const uint8_t*>(a.x) + (size_t)b * a.rows * a.c_in * sizeof(T);
+  const int row_bytes = chunks * 16;
+  for (int i = threadIdx.x; i < tile_rows * chunks; i += kPostThreads) {
+    const int r = i / chunks, c = i - r * chunks;
+    const int row = t0 + r - a.pad_left;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (row >= 0 && row < a.rows) v = __ldg(reinterpret_cast<const uint4*>(x + (size_t)row * row_bytes + c * 16));
+    *reinterpret_cast<uint4*>(psm + (size_t)r * pitch + c * 16) = v;
   }
-  a.out[gid] = tanhf((s0 + s1) + (s2 + s3) + a.bias);
+  __syncthreads();
+  const bool act = a.in_slope != 1.0f;
+#pragma unroll 1
+  for (int o = threadIdx.x; o < kPostRows; o += kPostThreads) {
+    const int t = t0 + o;
+    if (t >= a.rows) break;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    for (int j = 0; j < a.ntaps; ++j) {
+      const uint8_t* xr = psm + (size_t)(o + j) * pitch;
+      const float* wj = wsm + j * a.c_in;
+      for (int c = 0; c < chunks; ++c) {
+        const uint4 u = *reinterpret_cast<const uint4*>(xr + c * 16);
+        float f[EPC];
+        if constexpr (sizeof(T) == 4) {
+          f[0] = __uint_as_float(u.x); f[1] = __uint_as_float(u.y); f[2] = __uint_as_float(u.z); f[3] = __uint_as_float(u.w);
+        } else {
+          const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            float2 p;
+            if constexpr (std::is_same<T, __half>::value) p = __half22float2(*reinterpret_cast<const __half2*>(&uu[e]));
+            else p = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&uu[e]));
+            f[2 * e] = p.x; f[2 * e + 1] = p.y;
+          }
+        }
+        if (act) {
+#pragma unroll
+          for (int e = 0; e < EPC; ++e) f[e] = lrelu(f[e], a.in_slope);
+        }
+        const float* wc = wj + c * EPC;
+#pragma unroll
+        for (int e = 0; e < EPC; e += 4) {
+          const float4 w4 = *reinterpret_cast<const float4*>(wc + e);
+          s0 = fmaf(f[e + 0], w4.x, s0); s1 = fmaf(f[e + 1], w4.y, s1);
+          s2 = fmaf(f[e + 2], w4.z, s2); s3 = fmaf(f[e + 3], w4.w, s3);
+        }
+      }
+    }
+    a.out[(size_t)b * a.rows + t] = tanhf((s0 + s1) + (s2 + s3) + a.bias);
+  }
 }
 
 cudaError_t launch_conv_post(const PostArgs& a, ActType act, cudaStream_t s) {
-  if (a.c_in % 4 != 0 || a.ntaps < 1) return cudaErrorInvalidValue;
-  const long long total = (long long)a.B * a.rows;
-  if (total <= 0) return cudaSuccess;
-  const unsigned blocks = (unsigned)((total + 255) / 256);
-  const size_t smem = (size_t)a.ntaps * a.c_in * sizeof(float);
+  const int epc = act == ACT_F32 ? 4 : 8;
+  if (a.c_in % epc != 0 || a.ntaps < 1 || a.ntaps > kMaxTaps) return cudaErrorInvalidValue;
+  if (a.B <= 0 || a.rows <= 0) return cudaSuccess;
+  const dim3 grid((unsigned)((a.rows + kPostRows - 1) / kPostRows), (unsigned)a.B);
+  const size_t smem = (size_t)(kPostRows + a.ntaps - 1) * (a.c_in / epc + 1) * 16 + (size_t)a.ntaps * a.c_in * sizeof(float);
+  if (smem > 200 * 1024) return cudaErrorInvalidConfiguration;
+  cudaError_t e = cudaSuccess;
   switch (act) {
-    case ACT_F32: conv_post_kernel<float><<<blocks, 256, smem, s>>>(a); break;
-    case ACT_F16: conv_post_kernel<__half><<<blocks, 256, smem, s>>>(a); break;
-    case ACT_BF16: conv_post_kernel<__nv_bfloat16><<<blocks, 256, smem, s>>>(a); break;
+    case ACT_F32:
+      e = cudaFuncSetAttribute(conv_post_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e == cudaSuccess) conv_post_kernel<float><<<grid, kPostThreads, smem, s>>>(a);
+      break;
+    case ACT_F16:
+      e = cudaFuncSetAttribute(conv_post_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e == cudaSuccess) conv_post_kernel<__half><<<grid, kPostThreads, smem, s>>>(a);
+      break;
+    case ACT_BF16:
+      e = cudaFuncSetAttribute(conv_post_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e == cudaSuccess) conv_post_kernel<__nv_bfloat16><<<grid, kPostThreads, smem, s>>>(a);
+      break;
   }
+  if (e != cudaSuccess) return e;
   return cudaGetLastError();
 }
 

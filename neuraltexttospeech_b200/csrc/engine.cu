@@ -143,8 +143,8 @@ int validate_config(const hfg_config& c) {
   if (c.num_kernels < 1 || c.num_kernels > HFG_MAX_KERNELS) return fail(nullptr, HFG_ERR_INVALID, "num_kernels out of range: %d", c.num_kernels);
   if (c.compat != 0 && c.compat != 1) return fail(nullptr, HFG_ERR_INVALID, "compat must be 0 or 1");
   const int c0 = c.upsample_initial_channel;
-  if (c0 <= 0 || (c0 >> c.num_upsamples) < 8 || ((c0 >> c.num_upsamples) << c.num_upsamples) != c0)
-    return fail(nullptr, HFG_ERR_INVALID, "upsample_initial_channel=%d must be divisible by 2^num_upsamples with >=8 channels left", c0);
+  if (c0 <= 0 || (c0 >> c.num_upsamples) < 8 || ((c0 >> c.num_upsamples) << c.num_upsamples) != c0 || (c0 >> c.num_upsamples) % 8)
+    return fail(nullptr, HFG_ERR_INVALID, "upsample_initial_channel=%d must be divisible by 2^num_upsamples with a multiple of 8 channels left", c0);
   for (int i = 0; i < c.num_upsamples; ++i) {
     const int u = c.upsample_rates[i], k = c.upsample_kernel_sizes[i];
     if (u < 1 || k < u || (k + u - 1) / u > kMaxTaps) return fail(nullptr, HFG_ERR_INVALID, "unsupported upsample rate/kernel %d/%d", u, k);
