@@ -46,6 +46,21 @@ def peaks():
     return {"hbm_gbs": 6650.0, "tflops_burst": 1590.0, "tflops_sustained": 1400.0, "source": "fallback (B200_PROFILING.md)"}
 
 
+def ncu_traffic(stage_label, workload, mb):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed
+    `ncu --set full` capture (profiles/ncu_traffic.json); None when no capture matches this workload."""
+    path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.exists(path):
+        return None
+    try:
+        t = json.load(open(path)).get(workload, {}).get(stage_label)
+        if t and t.get("micro_batch") == mb:
+            return t["dram_bytes_per_launch"]
+    except Exception:
+        pass
+    return None
+
+
 class ClockSampler:
     """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -164,7 +179,7 @@ def main():
 
     from neuraltexttospeech_b200 import Generator, HParams
     from neuraltexttospeech_b200.synthetic import synthetic_mel, synthetic_weights
-    from neuraltexttospeech_b200.topology import boundary_bytes_per_frame, count_macs_per_frame
+    from neuraltexttospeech_b200.topology import boundary_bytes_per_frame, count_macs_per_frame, per_stage_work
 
     version, B, T = CONFIGS[args.config]
     h = HParams.builtin(version)
@@ -201,6 +216,9 @@ def main():
     for _ in range(args.warmup):
         launches_per_step = step_device()
     barrier()
+    # stage stamps (7 cudaEventRecord per forward on the launch stream) stay on during the timed region so that
+    # the dominant kernel's launch time is measured live, not in a separate pass
+    gen.set_option("stage_timing", 1)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local_rank) as clk:
         e0.record(stream)
@@ -210,6 +228,8 @@ def main():
         barrier()
     dev_ms = max_over_ranks(e0.elapsed_time(e1)) / args.steps
     clocks = clk.summary()
+    stage_ms = gen.stage_times_ms()          # per forward of `mb` utterances, averaged over the timed forwards
+    gen.set_option("stage_timing", 0)
 
     # ---------------- end-to-end through Generator.call on pinned host buffers ("e2e")
     e2e = None
@@ -230,25 +250,31 @@ def main():
                "h2d_bytes_per_step": int(mel_np.nbytes), "d2h_bytes_per_step": int(out_pin.numel() * 4),
                "ms_per_step": e2e_ms, "api": "Generator.call(numpy) -> hfg_forward_host"}
 
-    # ---------------- per-stage breakdown (separate, untimed pass)
-    stages = None
-    try:
-        gen.set_option("stage_timing", 1)
-        gen._call_device(mel_dev[:mb], out_dev[:mb])
-        torch.cuda.synchronize()
-        st = gen.stage_times_ms()
-        gen.set_option("stage_timing", 0)
-        stages = {"batch": mb, "ms": [round(x, 4) for x in st], "labels": ["conv_pre"] + [f"stage{i}" for i in range(len(st) - 2)] + ["conv_post"]}
-    except Exception as e:            # pragma: no cover
-        stages = {"error": str(e)}
-
     if rank == 0:
         pk = peaks()
+        act_b = 2 if args.precision != "fp32" else 4
         flops = 2.0 * count_macs_per_frame(h) * T * B
-        bytes_boundary = boundary_bytes_per_frame(h, 2 if args.precision != "fp32" else 4) * T * B
-        achieved = flops / (dev_ms / 1000) / 1e12
+        bytes_boundary = boundary_bytes_per_frame(h, act_b) * T * B
         tensor_bound = args.precision != "fp32"
-        peak = pk["tflops_sustained"] if tensor_bound else None
+        p_tensor, bw = pk["tflops_sustained"] * 1e12, pk["hbm_gbs"] * 1e9
+        # per-stage roofline: t_roof = max(F / P_tensor, B / BW_hbm) per forward of `mb` utterances
+        stages, t_roof_sum = [], 0.0
+        for w, ms in zip(per_stage_work(h, act_b), stage_ms):
+            f_st, b_st = 2.0 * w["macs"] * T * mb, float(w["bytes"]) * T * mb
+            t_t, t_h = f_st / p_tensor * 1e3, b_st / bw * 1e3
+            t_roof = max(t_t, t_h) if tensor_bound else t_h
+            t_roof_sum += t_roof
+            stages.append({"label": w["label"], "ms": round(ms, 4), "launches": w["launches"], "bound": "tensor" if (tensor_bound and t_t >= t_h) else "hbm",
+                           "roof_ms": round(t_roof, 4), "frac": round(t_roof / ms, 4) if ms > 0 else None,
+                           "tflops": round(f_st / (ms * 1e-3) / 1e12, 1) if ms > 0 else None,
+                           "gbs": round(b_st / (ms * 1e-3) / 1e9, 1) if ms > 0 else None})
+        # dominant kernel: the stage with the largest measured time; all of its launches are conv_tc_kernel instances
+        dom = max(range(len(stages)), key=lambda i: stages[i]["ms"])
+        dw, dst = per_stage_work(h, act_b)[dom], stages[dom]
+        dom_flops_launch = 2.0 * dw["macs"] * T * mb / dw["launches"]
+        dom_ms_launch = dst["ms"] / dw["launches"]
+        achieved = dom_flops_launch / (dom_ms_launch * 1e-3) / 1e12
+        traffic = ncu_traffic(dst["label"], args.config, mb)
         line = {
             "metric": "HiFi-GAN V1 audio-seconds/sec", "value": world * audio_s_per_step / (dev_ms / 1000), "unit": "audio-s/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms, "higher_is_better": True,
@@ -260,13 +286,17 @@ def main():
                        "l2": "per-step working set (GBs of activations) exceeds the 126 MB L2; no flush needed",
                        "sharding": "utterances sharded across ranks, no collective on the data path"},
             "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps), "clocks": clocks,
-            "roofline": {"bound": "tensor" if tensor_bound else "fp32-ffma", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                         "frac": (achieved / peak) if peak else None, "traffic": None,
-                         "peak_source": pk["source"] + " bf16 sustained (fp16 runs at the same tcgen05 rate)",
-                         "algorithmic_flops_per_step": flops, "layer_boundary_bytes_per_step": bytes_boundary,
-                         "hbm_floor_ms": bytes_boundary / (pk["hbm_gbs"] * 1e9) * 1000,
-                         "tensor_floor_ms": flops / (pk["tflops_sustained"] * 1e12) * 1000},
-            "stages": stages,
+            "roofline": {"bound": "tensor" if tensor_bound else "hbm", "achieved": achieved, "peak": pk["tflops_sustained"] if tensor_bound else None,
+                         "unit": "TFLOP/s", "frac": achieved / pk["tflops_sustained"] if tensor_bound else None, "traffic": traffic,
+                         "kernel": f"conv_tc_kernel (tcgen05 implicit GEMM), {dst['label']}: {dw['launches']} launches per forward of {mb} utterances",
+                         "flops_per_launch": dom_flops_launch, "ms_per_launch": dom_ms_launch,
+                         "timing": "CUDA events on the launch stream around the stage, inside the timed region, averaged over its forwards",
+                         "peak_source": pk["source"] + " bf16 sustained (fp16 runs at the same tcgen05 rate; kernel timed inside a long step)"},
+            "roofline_step": {"achieved_tflops": flops / (dev_ms / 1000) / 1e12, "frac_of_tensor_peak": flops / (dev_ms / 1000) / p_tensor,
+                              "per_stage_roof_ms_per_step": t_roof_sum * (B / mb), "frac_of_per_stage_roofline": t_roof_sum * (B / mb) / dev_ms,
+                              "algorithmic_flops_per_step": flops, "layer_boundary_bytes_per_step": bytes_boundary,
+                              "hbm_floor_ms": bytes_boundary / bw * 1000, "tensor_floor_ms": flops / p_tensor * 1000},
+            "stages": {"batch": mb, "rows": stages},
         }
         if not args.no_cpu_baseline:
             # CPU baseline on rank 0: BASELINE.json configs[0] (V1, batch 1, 256 frames), oracle port

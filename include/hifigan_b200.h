@@ -109,7 +109,8 @@ int hfg_layer_engines(hfg_handle h, char* buf, size_t cap);
 /* Kernels launched by the last hfg_forward / hfg_forward_host on this handle. */
 int hfg_last_launch_count(hfg_handle h, long long* out);
 
-/* Per-stage device time of the last forward when option "stage_timing" is 1:
+/* Per-stage device time (CUDA events on the forward's stream) while option "stage_timing" is 1, averaged over
+ * the forwards run since the previous call (the 128 most recent at most), then reset:
  * out[0]=conv_pre, out[1+i]=stage i (ups[i] + its resblocks), out[1+n]=conv_post. Returns count via n. */
 int hfg_stage_times_ms(hfg_handle h, float* out, int* n);
 

@@ -47,6 +47,7 @@ struct Layer {
 };
 
 thread_local std::string g_create_error;
+constexpr int kTimingSlots = 128;    // forwards whose stage stamps are kept between two hfg_stage_times_ms calls
 
 }  // namespace
 
@@ -62,8 +63,9 @@ struct hfg_ctx {
   std::string err;
   long long launches = 0;
   bool stage_timing = false;
-  std::vector<cudaEvent_t> events;
-  std::vector<float> stage_ms;
+  std::vector<cudaEvent_t> events;   // kTimingSlots forwards x marks_per_fwd stamps (ring)
+  int marks_per_fwd = 0;
+  long long timed_forwards = 0;      // forwards stamped since the last hfg_stage_times_ms
   int n_stage_marks = 0;
   // host-buffer path
   int micro_batch = 16;
@@ -312,7 +314,10 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
   const float kSlope = 0.1f;                                    // LRELU_SLOPE, reference model.py:14
   const float kFinalSlope = c.compat == 0 ? 0.3f : 0.01f;       // keras LeakyReLU() default, model.py:152
   int mark = 0;
-  auto stamp = [&]() { if (h->stage_timing && mark < (int)h->events.size()) cudaEventRecord(h->events[mark++], s); };
+  const int slot = (int)(h->timed_forwards % kTimingSlots);
+  auto stamp = [&]() {
+    if (h->stage_timing && mark < h->marks_per_fwd) cudaEventRecord(h->events[(size_t)slot * h->marks_per_fwd + mark++], s);
+  };
   auto layer = [&](const std::string& name) -> const Layer& { return h->layers[h->index[name]]; };
   stamp();
 
@@ -382,6 +387,7 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
   if (e != cudaSuccess) return fail(h, HFG_ERR_CUDA, "conv_post launch failed: %s", cudaGetErrorString(e));
   stamp();
   h->n_stage_marks = mark;
+  if (h->stage_timing) h->timed_forwards++;
   return HFG_OK;
 }
 
@@ -519,7 +525,8 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
   for (const Layer& L : h->layers)
     if (!L.transposed && L.name != "conv_pre" && L.name != "conv_post") { if (L.use_tc) h->need_sum = true; else h->need_acc = true; }
   if (h->events.empty()) {
-    h->events.resize(c.num_upsamples + 3);
+    h->marks_per_fwd = c.num_upsamples + 3;
+    h->events.resize((size_t)h->marks_per_fwd * kTimingSlots);
     for (auto& ev : h->events) CUDA_TRY(h, cudaEventCreate(&ev));
   }
   h->finalized = true;
@@ -606,7 +613,7 @@ int hfg_set_option(hfg_handle h, const char* key, long long value) {
   if (!h || !key) return HFG_ERR_INVALID;
   const std::string k(key);
   if (k == "micro_batch") { if (value < 0) return fail(h, HFG_ERR_INVALID, "micro_batch must be >= 0"); h->micro_batch = (int)value; return HFG_OK; }
-  if (k == "stage_timing") { h->stage_timing = value != 0; return HFG_OK; }
+  if (k == "stage_timing") { h->stage_timing = value != 0; h->timed_forwards = 0; return HFG_OK; }
   if (k == "force_ffma") { h->force_ffma = value != 0; h->finalized = false; return HFG_OK; }
   return fail(h, HFG_ERR_INVALID, "unknown option '%s'", key);
 }
@@ -630,12 +637,23 @@ int hfg_last_launch_count(hfg_handle h, long long* out) {
 
 int hfg_stage_times_ms(hfg_handle h, float* out, int* n) {
   if (!h || !out || !n) return HFG_ERR_INVALID;
-  if (!h->stage_timing || h->n_stage_marks < 2) return fail(h, HFG_ERR_STATE, "stage timing not enabled or no forward ran");
-  CUDA_TRY(h, cudaEventSynchronize(h->events[h->n_stage_marks - 1]));
+  if (!h->stage_timing || h->n_stage_marks < 2 || h->timed_forwards < 1) return fail(h, HFG_ERR_STATE, "stage timing not enabled or no forward ran");
   const int cnt = h->n_stage_marks - 1;
   if (*n < cnt) return fail(h, HFG_ERR_INVALID, "need room for %d floats", cnt);
-  for (int i = 0; i < cnt; ++i) CUDA_TRY(h, cudaEventElapsedTime(&out[i], h->events[i], h->events[i + 1]));
+  // average over the forwards stamped since the last call (at most the kTimingSlots most recent ones)
+  const long long nf = h->timed_forwards < kTimingSlots ? h->timed_forwards : kTimingSlots;
+  for (int i = 0; i < cnt; ++i) out[i] = 0.f;
+  for (long long f = 0; f < nf; ++f) {
+    const size_t base = (size_t)((h->timed_forwards - 1 - f) % kTimingSlots) * h->marks_per_fwd;
+    CUDA_TRY(h, cudaEventSynchronize(h->events[base + cnt]));
+    for (int i = 0; i < cnt; ++i) {
+      float ms = 0.f;
+      CUDA_TRY(h, cudaEventElapsedTime(&ms, h->events[base + i], h->events[base + i + 1]));
+      out[i] += ms / (float)nf;
+    }
+  }
   *n = cnt;
+  h->timed_forwards = 0;
   return HFG_OK;
 }
 

@@ -114,3 +114,27 @@ def boundary_bytes_per_frame(h, act_bytes: int = 2) -> int:
             res = L.c_out if (".convs2." in L.name or ".convs." in L.name) else 0
             total += act_bytes * rate * (L.c_in + L.c_out + res)
     return total
+
+
+def per_stage_work(h, act_bytes: int = 2):
+    """Per mel frame, per measurement stage of hfg_stage_times_ms: [conv_pre, stage 0.., conv_post] ->
+    list of dicts {label, macs, bytes, launches} (FLOP = 2*MAC, layer-boundary bytes).
+    `launches` counts weight-bearing layers (one kernel launch each on the tcgen05 path)."""
+    out = []
+    rate = 1
+    cur = None
+    for L in enumerate_layers(h):
+        if L.name == "conv_pre" or L.name == "conv_post" or L.kind == "convT":
+            label = L.name if L.kind == "conv" else f"stage{L.name.split('.')[1]}"
+            cur = {"label": label, "macs": 0, "bytes": 0, "launches": 0}
+            out.append(cur)
+        if L.kind == "convT":
+            cur["macs"] += rate * L.kernel * L.c_in * L.c_out
+            cur["bytes"] += act_bytes * (rate * L.c_in + rate * L.stride * L.c_out)
+            rate *= L.stride
+        else:
+            res = L.c_out if (".convs2." in L.name or ".convs." in L.name) else 0
+            cur["macs"] += rate * L.kernel * L.c_in * L.c_out
+            cur["bytes"] += act_bytes * rate * (L.c_in + L.c_out + res)
+        cur["launches"] += 1
+    return out
