@@ -54,8 +54,8 @@ def ncu_traffic(stage_label, workload, mb):
         return None
     try:
         t = json.load(open(path)).get(workload, {}).get(stage_label)
-        if t and t.get("micro_batch") == mb:
-            return t["dram_bytes_per_launch"]
+        if t:      # the capture's launches process `micro_batch` utterances; traffic is linear in the utterance count
+            return t["dram_bytes_per_launch"] * mb / t["micro_batch"]
     except Exception:
         pass
     return None
@@ -154,7 +154,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="v1_b64x10s", choices=sorted(CONFIGS))
     ap.add_argument("--precision", default="fp16", choices=["fp32", "fp16", "bf16"])
-    ap.add_argument("--micro-batch", type=int, default=16)
+    ap.add_argument("--micro-batch", type=int, default=32)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()

@@ -99,7 +99,7 @@ int hfg_forward(hfg_handle h, const float* mel_dev, int B, int T, float* audio_d
  * asynchronous; pageable memory works too. */
 int hfg_forward_host(hfg_handle h, const float* mel_host, int B, int T, float* audio_host);
 
-/* Utterances per micro-batch used by hfg_forward_host (default 16); 0 = whole batch. */
+/* Utterances per micro-batch used by hfg_forward_host (default 32); 0 = whole batch. */
 int hfg_set_option(hfg_handle h, const char* key, long long value);
 
 /* Which kernel family each layer was bound to by hfg_finalize_weights: lines "<layer>:<tc|ffma|post>\n"

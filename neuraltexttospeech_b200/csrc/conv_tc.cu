@@ -32,6 +32,7 @@
 // buffering where 2*MB*N <= 512 columns, NSTG-deep staging ring).
 #include <cuda.h>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <type_traits>
 #include <vector>
@@ -157,6 +158,42 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* tm, const void* 
   asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
                ::"l"(tm), "r"(smem_u32(src_smem)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
 }
+// ---- cta_group::2 (CTA pair) forms: loads of either CTA signal the LEADER's mbarrier (cluster address `bar_cl`)
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t saddr, uint32_t rank) {
+  uint32_t r; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank)); return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cl) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cl) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d_2cta(void* dst_smem, const CUtensorMap* tm, int c0, int c1, int c2, uint32_t bar_cl) {
+  asm volatile("cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+               ::"r"(smem_u32(dst_smem)), "l"(tm), "r"(c0), "r"(c1), "r"(c2), "r"(bar_cl) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_2cta(void* dst_smem, const CUtensorMap* tm, int c0, int c1, uint32_t bar_cl) {
+  asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+               ::"r"(smem_u32(dst_smem)), "l"(tm), "r"(c0), "r"(c1), "r"(bar_cl) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc2(uint32_t* slot_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot_smem)), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_f16_2cta(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p; }"
+               ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrives on the barrier at the same smem offset in BOTH CTAs of the pair when the MMAs issued so far retire
+__device__ __forceinline__ void umma_commit_2cta(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(tm) : "memory");
 }
@@ -177,8 +214,8 @@ __device__ __forceinline__ uint64_t make_desc_sw(uint32_t saddr) {
   return (uint64_t)((saddr & 0x3FFFF) >> 4) | (1ull << 16) | ((uint64_t)((8 * ROWB) >> 4) << 32) | (1ull << 46) | (LT << 61);
 }
 // instruction descriptor, kind::f16 (cute::UMMA::InstrDescriptor): D=f32, A/B = f16 or bf16, both K-major, M=128
-__host__ __device__ constexpr uint32_t make_idesc(int n, bool bf16) {
-  return (1u << 4) | ((bf16 ? 1u : 0u) << 7) | ((bf16 ? 1u : 0u) << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+__host__ __device__ constexpr uint32_t make_idesc(int n, bool bf16, int m = 128) {
+  return (1u << 4) | ((bf16 ? 1u : 0u) << 7) | ((bf16 ? 1u : 0u) << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
 template <typename T> struct H2;
@@ -214,12 +251,12 @@ struct TcSmemPlan {
   int total;
 };
 
-__host__ __device__ inline TcSmemPlan tc_plan(int n, int ks, int kbw, int nst, int nsl, int nstg, int slice_rows) {
+__host__ __device__ inline TcSmemPlan tc_plan(int n, int ks, int kbw, int nst, int nsl, int nstg, int slice_rows, int cg = 1) {
   TcSmemPlan p;
   const int pw = n < 64 ? n : 64;
   p.slice_rows = slice_rows;
   p.slice_bytes = slice_rows * ks * 2;            // multiple of the swizzle atom (slice_rows % 8 == 0)
-  p.stage_bytes = n * kbw * 2;
+  p.stage_bytes = (n / cg) * kbw * 2;     // a CTA of a pair stages half of the weight rows
   p.stg_bytes = 128 * pw * 2;
   int off = nsl * p.slice_bytes;
   off = (off + 1023) & ~1023;
@@ -242,17 +279,25 @@ struct TcKArgs {
   TcVariant var[kMaxVariants];
   int min_off, span;
   int box_rows, nbox;   // slab slice = nbox TMA boxes of box_rows rows
-  int tiles_q, n_tiles, total_tiles;
+  int tiles_q, n_tiles, total_tiles;   // CG == 2: tiles_q / total_tiles count PAIR tiles of 2*MB*128 rows
+  const void* w_base;                  // CG == 2: base of the layer's packed weights (tm_w), 256-byte rows
+  int resident;                        // every tile uses the same weights and they fit the NST stages: load them once
 };
 
 // ------------------------------------------------------------------ the kernel
-template <typename T, int C_IN, int N, int MB, int KS, int KBW, int TPS, int NST, int NSL, int NSTG>
+// CG == 2: the kernel runs as CTA pairs (cluster of 2, cta_group::2): the pair computes 2*MB*128 rows with M=256
+// MMAs issued by the leader (rank 0); each CTA stages its own rows of A and only HALF of the weight rows (B), which
+// cuts the shared-memory operand reads per MMA from 4+N*32 to 4+N*16 bytes per N/2 cycles and halves weight staging.
+template <typename T, int C_IN, int N, int MB, int KS, int KBW, int TPS, int NST, int NSL, int NSTG, int CG>
 __global__ void __launch_bounds__(kTcThreads, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_res,
-               const __grid_constant__ CUtensorMap tm_out, const __grid_constant__ TcKArgs ka) {
+               const __grid_constant__ CUtensorMap tm_out, const __grid_constant__ CUtensorMap tm_w,
+               const __grid_constant__ TcKArgs ka) {
+  static_assert(CG == 1 || CG == 2, "cta group");
+  constexpr int NB = N / CG;                      // weight rows (B operand) staged by this CTA
   constexpr int NKS = C_IN / KS;                  // K-slices per tile
   constexpr int NKB = KS / KBW;                   // weight k-blocks per (slice, tap)
-  constexpr int BLK_BYTES = N * KBW * 2;          // one (tap, k-block) weight block; a stage holds TPS of them
+  constexpr int BLK_BYTES = NB * KBW * 2;         // this CTA's part of one (tap, k-block) weight block; a stage holds TPS
   static_assert(TPS == 1 || NKB == 1, "multi-tap stages need KBW == KS");
   constexpr int ROWB = KS * 2;                    // bytes per slab row within a slice (= swizzle width)
   constexpr int PW = N < 64 ? N : 64;             // output columns per epilogue pass
@@ -260,11 +305,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
   constexpr int NACC = (2 * MB * N <= 512) ? 2 : 1;
   constexpr int ACC_COLS = MB * N;
   constexpr uint32_t TMEM_COLS = tc_tmem_cols(NACC * ACC_COLS);
-  constexpr uint32_t IDESC = make_idesc(N, std::is_same<T, __nv_bfloat16>::value);
-  static_assert(C_IN % KS == 0 && KS % KBW == 0 && KBW % 16 == 0 && N % 16 == 0 && N <= 256, "tile config");
+  constexpr uint32_t IDESC = make_idesc(N, std::is_same<T, __nv_bfloat16>::value, 128 * CG);
+  static_assert(C_IN % KS == 0 && KS % KBW == 0 && KBW % 16 == 0 && N % 16 == 0 && N <= 256 && NB % 8 == 0, "tile config");
+  static_assert(CG == 1 || BLK_BYTES % 256 == 0, "pair weight blocks are whole 256-byte rows of tm_w");
   static_assert(KS == 64 || KS == 32 || KS == 16, "K-slice = one swizzle row");
   static_assert(N % PW == 0, "pass width");
-  const TcSmemPlan pl = tc_plan(N, KS, KBW * TPS, NST, NSL, NSTG, ka.nbox * ka.box_rows);
+  const TcSmemPlan pl = tc_plan(N, KS, KBW * TPS, NST, NSL, NSTG, ka.nbox * ka.box_rows, CG);
 
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* slab = smem;
@@ -283,19 +329,22 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;       // 0 = leader of the pair
+  const int tile0 = blockIdx.x / CG, tile_step = gridDim.x / CG;
 
   if (tid == 0) {
     for (int s = 0; s < NSL; ++s) { mbar_init(&slice_full[s], 1); mbar_init(&slice_empty[s], 1); }
     for (int s = 0; s < NST; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
-    for (int s = 0; s < NSTG; ++s) { mbar_init(&stg_full[s], 1); mbar_init(&stg_empty[s], 1); mbar_init(&stg_done[s], 128); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 256); }
+    for (int s = 0; s < NSTG; ++s) { mbar_init(&stg_full[s], 1); mbar_init(&stg_empty[s], 1); mbar_init(&stg_done[s], 4); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 8 * CG); }
     fence_mbar_init();
     tma_prefetch_desc(&tm_x); tma_prefetch_desc(&tm_res); tma_prefetch_desc(&tm_out);
+    if (CG == 2) tma_prefetch_desc(&tm_w);
   }
-  if (warp == 2) tmem_alloc(tmem_slot, TMEM_COLS);
+  if (warp == 2) { if (CG == 2) tmem_alloc2(tmem_slot, TMEM_COLS); else tmem_alloc(tmem_slot, TMEM_COLS); }
   for (int i = tid; i < ka.c_out; i += kTcThreads) bias_s[i] = ka.bias[i];
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all(); else __syncthreads();   // pair: the peer's barriers are initialised before any remote signal
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -304,6 +353,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
     nt = t % ka.n_tiles; t /= ka.n_tiles;
     v = t % ka.nvar; t /= ka.nvar;
     qt = t % ka.tiles_q; b = t / ka.tiles_q;
+    if (CG == 2) qt = qt * 2 + (int)rank;           // the pair's 2*MB*128 rows: leader takes the first half
   };
 
   // Producer / MMA warps run their loops with ALL lanes (warp-uniform control flow keeps barrier addresses and
@@ -312,17 +362,25 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
     // ===================== slab producer (TMA) =====================
     uint32_t scnt = 0;
     const uint32_t box_bytes = (uint32_t)ka.box_rows * ROWB;
-    for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x) {
+    for (int t = tile0; t < ka.total_tiles; t += tile_step) {
       int b, qt, v, nt; decode(t, b, qt, v, nt);
       const int row_base = qt * (MB * 128) + ka.min_off;
       for (int s = 0; s < NKS; ++s, ++scnt) {
         const int pos = scnt % NSL;
         mbar_wait(&slice_empty[pos], ((scnt / NSL) & 1) ^ 1);
         if (elect_one()) {
-          mbar_expect_tx(&slice_full[pos], box_bytes * ka.nbox);
           uint8_t* dst = slab + pos * pl.slice_bytes;
-          for (int bx = 0; bx < ka.nbox; ++bx)
-            tma_load_3d(dst + bx * box_bytes, &tm_x, s * KS, row_base + bx * ka.box_rows, b, &slice_full[pos]);
+          if (CG == 1) {
+            mbar_expect_tx(&slice_full[pos], box_bytes * ka.nbox);
+            for (int bx = 0; bx < ka.nbox; ++bx)
+              tma_load_3d(dst + bx * box_bytes, &tm_x, s * KS, row_base + bx * ka.box_rows, b, &slice_full[pos]);
+          } else {
+            // both CTAs' slabs complete on the leader's barrier (the leader's MMAs read both)
+            if (rank == 0) mbar_expect_tx(&slice_full[pos], 2 * box_bytes * ka.nbox);
+            const uint32_t bar_cl = mapa_u32(smem_u32(&slice_full[pos]), 0);
+            for (int bx = 0; bx < ka.nbox; ++bx)
+              tma_load_3d_2cta(dst + bx * box_bytes, &tm_x, s * KS, row_base + bx * ka.box_rows, b, bar_cl);
+          }
         }
         __syncwarp();
       }
@@ -330,10 +388,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
   } else if (warp == 1) {
     // ===================== weight producer =====================
     uint32_t wcnt = 0;
-    for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x) {
+    for (int t = tile0; t < ka.total_tiles; t += tile_step) {
       int b, qt, v, nt; decode(t, b, qt, v, nt);
       const int ntaps = ka.var[v].ntaps;
       const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(ka.var[v].w) + (size_t)nt * (NKS * ntaps * NKB) * BLK_BYTES;
+      // pair: block hb of the variant lives at 256-byte row (var_row + (2*hb + rank) * BLK_BYTES/256) of tm_w
+      int wrow = CG == 2 ? (int)((reinterpret_cast<const uint8_t*>(ka.var[v].w) - reinterpret_cast<const uint8_t*>(ka.w_base)) >> 8) +
+                               (2 * nt * (NKS * ntaps * NKB) + (int)rank) * (BLK_BYTES >> 8) : 0;
       for (int s = 0; s < NKS; ++s) {
         for (int j0 = 0; j0 < ntaps; j0 += TPS) {
           const int nj = (ntaps - j0) < TPS ? (ntaps - j0) : TPS;
@@ -342,20 +403,30 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
             const uint32_t bytes = (uint32_t)nj * BLK_BYTES;
             mbar_wait(&w_empty[st], ((wcnt / NST) & 1) ^ 1);
             if (elect_one()) {
-              mbar_expect_tx(&w_full[st], bytes);
-              bulk_g2s(wst + st * pl.stage_bytes, wsrc, bytes, &w_full[st]);
+              if (CG == 1) {
+                mbar_expect_tx(&w_full[st], bytes);
+                bulk_g2s(wst + st * pl.stage_bytes, wsrc, bytes, &w_full[st]);
+              } else {
+                if (rank == 0) mbar_expect_tx(&w_full[st], 2 * bytes);
+                const uint32_t bar_cl = mapa_u32(smem_u32(&w_full[st]), 0);
+                for (int jj = 0; jj < nj; ++jj)        // NKB == 1 when TPS > 1: consecutive taps are consecutive blocks
+                  tma_load_2d_2cta(wst + st * pl.stage_bytes + jj * BLK_BYTES, &tm_w, 0, wrow + 2 * jj * (BLK_BYTES >> 8), bar_cl);
+              }
             }
             __syncwarp();
             wsrc += bytes;
+            wrow += 2 * nj * (BLK_BYTES >> 8);
           }
         }
       }
+      if (ka.resident) break;                         // the stages stay in shared memory for every later tile
     }
   } else if (warp == 2) {
-    // ===================== MMA issuer =====================
+    // ===================== MMA issuer (pair: leader CTA only) =====================
+    if (rank == 0) {
     const uint32_t slab_addr = smem_u32(slab), wst_addr = smem_u32(wst);
     uint32_t scnt = 0, wcnt = 0, tcnt = 0;
-    for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x, ++tcnt) {
+    for (int t = tile0; t < ka.total_tiles; t += tile_step, ++tcnt) {
       int b, qt, v, nt; decode(t, b, qt, v, nt);
       const int ntaps = ka.var[v].ntaps;
       const int abuf = tcnt % NACC;
@@ -363,6 +434,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
       tc_fence_after();
       const uint32_t tacc = tmem_base + abuf * ACC_COLS;
       uint32_t first = 1;
+      if (ka.resident) wcnt = 0;
 #pragma unroll 1
       for (int s = 0; s < NKS; ++s, ++scnt) {
         const int pos = scnt % NSL;
@@ -374,32 +446,35 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
           const int nj = (ntaps - j0) < TPS ? (ntaps - j0) : TPS;
 #pragma unroll 1
           for (int kb = 0; kb < NKB; ++kb, ++wcnt) {
-            const int st = wcnt % NST;
-            mbar_wait(&w_full[st], (wcnt / NST) & 1);
+            const int st = wcnt % NST;                // resident: wcnt restarts per tile, stage = position in the tile
+            if (!ka.resident || tcnt == 0) mbar_wait(&w_full[st], (wcnt / NST) & 1);
             tc_fence_after();
             if (elect_one()) {
               const uint32_t wb = wst_addr + st * pl.stage_bytes;
-#pragma unroll 1
-              for (int jj = 0; jj < nj; ++jj) {
+#pragma unroll
+              for (int jj = 0; jj < TPS; ++jj) {
+                if (jj >= nj) break;
                 const uint32_t row_off = (uint32_t)(ka.var[v].tap_off[j0 + jj] - ka.min_off);
                 const uint64_t a0 = make_desc_sw<ROWB>(sl + row_off * ROWB + kb * KBW * 2);
-                const uint64_t b0 = make_desc(wb + jj * BLK_BYTES, N * 16, 128u);
+                const uint64_t b0 = make_desc(wb + jj * BLK_BYTES, NB * 16, 128u);
 #pragma unroll
                 for (int mb = 0; mb < MB; ++mb) {
 #pragma unroll
                   for (int kk = 0; kk < KBW / 16; ++kk) {
                     // descriptor start-address field counts 16-byte units: advance with plain adds
                     const uint64_t adesc = a0 + (uint64_t)((mb * 128 * ROWB + kk * 32) >> 4);
-                    const uint64_t bdesc = b0 + (uint64_t)((kk * 2 * N * 16) >> 4);
-                    umma_f16(tacc + mb * N, adesc, bdesc, IDESC, (first && kk == 0) ? 0u : 1u);
+                    const uint64_t bdesc = b0 + (uint64_t)((kk * 2 * NB * 16) >> 4);
+                    if (CG == 2) umma_f16_2cta(tacc + mb * N, adesc, bdesc, IDESC, (first && kk == 0) ? 0u : 1u);
+                    else umma_f16(tacc + mb * N, adesc, bdesc, IDESC, (first && kk == 0) ? 0u : 1u);
                   }
                 }
                 first = 0;
               }
-              umma_commit(&w_empty[st]);          // frees the weight stage when these MMAs retire
+              // pair: the commits arrive on the same barrier of BOTH CTAs
+              if (!ka.resident) { if (CG == 2) umma_commit_2cta(&w_empty[st]); else umma_commit(&w_empty[st]); }   // frees the weight stage
               if (kb == NKB - 1 && j0 + TPS >= ntaps) {
-                umma_commit(&slice_empty[pos]);   // slab slice may be overwritten
-                if (s == NKS - 1) umma_commit(&acc_full[abuf]);   // accumulators of this tile complete
+                if (CG == 2) umma_commit_2cta(&slice_empty[pos]); else umma_commit(&slice_empty[pos]);   // slab slice may be overwritten
+                if (s == NKS - 1) { if (CG == 2) umma_commit_2cta(&acc_full[abuf]); else umma_commit(&acc_full[abuf]); }   // tile complete
               }
             }
             first = 0;
@@ -408,10 +483,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
         }
       }
     }
+    }
   } else if (warp == 3) {
     // ===================== staging producer: residual tiles (or just buffer grants) =====================
     uint32_t pcnt = 0;
-    for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x) {
+    for (int t = tile0; t < ka.total_tiles; t += tile_step) {
       int b, qt, v, nt; decode(t, b, qt, v, nt);
       for (int mb = 0; mb < MB; ++mb) {
         const int q0 = qt * (MB * 128) + mb * 128;
@@ -433,7 +509,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
   } else if (warp == 12) {
     // ===================== store issuer: TMA tensor store of every finished staging tile =====================
     uint32_t pcnt = 0;
-    for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x) {
+    for (int t = tile0; t < ka.total_tiles; t += tile_step) {
       int b, qt, v, nt; decode(t, b, qt, v, nt);
       const int out_off = ka.var[v].out_off;
       for (int mb = 0; mb < MB; ++mb) {
@@ -465,7 +541,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
     // XOR term of the TMA swizzle for this thread's staging row (row pitch SROWB, 1024-byte aligned tile)
     const int sx = SROWB == 128 ? (er & 7) : (SROWB == 64 ? ((er >> 1) & 3) : ((er >> 2) & 1));
     uint32_t tcnt = 0, pcnt = 0;
-    for (int t = blockIdx.x; t < ka.total_tiles; t += gridDim.x, ++tcnt) {
+    for (int t = tile0; t < ka.total_tiles; t += tile_step, ++tcnt) {
       int b, qt, v, nt; decode(t, b, qt, v, nt);
       const int n0 = nt * N;
       const int abuf = tcnt % NACC;
@@ -538,16 +614,24 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
             }
           }
           fence_proxy_async();                          // staging writes -> visible to the TMA engine
-          mbar_arrive(&stg_done[buf]);                  // hand the tile to the store warp
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&stg_done[buf]);   // one arrival per warp: hand the tile to the store warp
         }
       }
       tc_fence_before();
-      mbar_arrive(&acc_empty[abuf]);                    // accumulator buffer may be overwritten
+      __syncwarp();
+      if (lane == 0) {                                  // one arrival per warp: accumulator buffer may be overwritten
+        if (CG == 2) mbar_arrive_cluster(mapa_u32(smem_u32(&acc_empty[abuf]), 0));   // the leader's MMA warp waits for both CTAs
+        else mbar_arrive(&acc_empty[abuf]);
+      }
     }
   }
   tc_fence_before();
-  __syncthreads();
-  if (warp == 2) { __syncwarp(); tc_fence_after(); tmem_dealloc(tmem_base, TMEM_COLS); }
+  if (CG == 2) cluster_sync_all(); else __syncthreads();   // pair: nobody exits while the peer may still signal its barriers
+  if (warp == 2) {
+    __syncwarp(); tc_fence_after();
+    if (CG == 2) tmem_dealloc2(tmem_base, TMEM_COLS); else tmem_dealloc(tmem_base, TMEM_COLS);
+  }
 }
 
 // ------------------------------------------------------------------ host side
@@ -609,7 +693,19 @@ void tc_boxes(int rows, int* box_rows, int* nbox) {
   *box_rows = best_br; *nbox = (rows + best_br - 1) / best_br;
 }
 
-template <typename T, int C_IN, int N, int MB, int KS, int KBW, int TPS, int NST, int NSL, int NSTG>
+// rank-2 map over a layer's packed weights viewed as 256-byte rows; box = one CTA's part of a weight block
+bool make_map_w(CUtensorMap* m, const void* base, size_t bytes, int box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return false;
+  cuuint64_t gdim[2] = {128, (cuuint64_t)(bytes / 256)};
+  cuuint64_t gstr[1] = {256};
+  cuuint32_t box[2] = {128, (cuuint32_t)box_rows};
+  cuuint32_t est[2] = {1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, const_cast<void*>(base), gdim, gstr, box, est, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <typename T, int C_IN, int N, int MB, int KS, int KBW, int TPS, int NST, int NSL, int NSTG, int CG>
 cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out) {
   constexpr int PW = N < 64 ? N : 64;
   TcKArgs ka{};
@@ -624,17 +720,29 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
   if (ka.span > kTcMaxSpan) return cudaErrorInvalidValue;
   if ((a.res || a.res2) && a.out_stride != 1) return cudaErrorInvalidValue;
   tc_boxes(MB * 128 + ka.span, &ka.box_rows, &ka.nbox);
-  const TcSmemPlan pl = tc_plan(N, KS, KBW * TPS, NST, NSL, NSTG, ka.nbox * ka.box_rows);
+  const TcSmemPlan pl = tc_plan(N, KS, KBW * TPS, NST, NSL, NSTG, ka.nbox * ka.box_rows, CG);
   if ((size_t)pl.total > kTcMaxSmem) return cudaErrorInvalidConfiguration;
-  ka.tiles_q = (a.n_q + MB * 128 - 1) / (MB * 128);
+  ka.tiles_q = (a.n_q + CG * MB * 128 - 1) / (CG * MB * 128);
+  ka.w_base = a.w_base;
+  {
+    int max_taps = 0;
+    for (int v = 0; v < a.nvar; ++v) max_taps = a.var[v].ntaps > max_taps ? a.var[v].ntaps : max_taps;
+    const int stages = (C_IN / KS) * ((max_taps + TPS - 1) / TPS) * (KS / KBW);
+    ka.resident = (a.nvar == 1 && a.c_out == N && stages <= NST) ? 1 : 0;
+  }
   ka.n_tiles = a.c_out / N;
   ka.total_tiles = a.B * ka.tiles_q * a.nvar * ka.n_tiles;
-  CUtensorMap tm_x, tm_res, tm_out;
+  CUtensorMap tm_x, tm_res, tm_out, tm_w;
+  if (CG == 2) {
+    if (!a.w_base || a.w_bytes % 256 || (uintptr_t)a.w_base % 256) return cudaErrorInvalidValue;
+    if (!make_map_w(&tm_w, a.w_base, a.w_bytes, (N / CG) * KBW * 2 / 256)) return cudaErrorNotSupported;
+  }
   if (!make_map3(&tm_x, act, a.x, C_IN, a.x_rows, a.B, KS, ka.box_rows)) return cudaErrorNotSupported;
   if (!make_map4(&tm_out, act, a.out, a.c_out, a.out_stride, a.n_q, a.B, PW)) return cudaErrorNotSupported;
   if (a.res) { if (!make_map4(&tm_res, act, a.res, a.c_out, 1, a.n_q, a.B, PW)) return cudaErrorNotSupported; }
   else tm_res = tm_out;
-  auto kern = conv_tc_kernel<T, C_IN, N, MB, KS, KBW, TPS, NST, NSL, NSTG>;
+  if (CG == 1) tm_w = tm_out;
+  auto kern = conv_tc_kernel<T, C_IN, N, MB, KS, KBW, TPS, NST, NSL, NSTG, CG>;
   static int configured = 0, occ = 1;      // per instantiation
   if (pl.total > configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total);
@@ -653,40 +761,74 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
     if (occ < 1) occ = 1;
   }
   int grid = g_num_sms * occ;
-  if (grid > ka.total_tiles) grid = ka.total_tiles;
+  if (CG == 1) {
+    if (grid > ka.total_tiles) grid = ka.total_tiles;
+    if (grid_out) *grid_out = grid;
+    kern<<<grid, kTcThreads, pl.total, s>>>(tm_x, tm_res, tm_out, tm_w, ka);
+    return cudaGetLastError();
+  }
+  // CTA pairs: cluster of 2 (same TPC), one pair per pair-tile stride
+  int pairs = g_num_sms / 2;
+  if (pairs > ka.total_tiles) pairs = ka.total_tiles;
+  grid = 2 * pairs;
   if (grid_out) *grid_out = grid;
-  kern<<<grid, kTcThreads, pl.total, s>>>(tm_x, tm_res, tm_out, ka);
-  return cudaGetLastError();
+  cudaLaunchConfig_t lc{};
+  lc.gridDim = dim3(grid); lc.blockDim = dim3(kTcThreads); lc.dynamicSmemBytes = pl.total; lc.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  lc.attrs = at; lc.numAttrs = 1;
+  return cudaLaunchKernelEx(&lc, kern, tm_x, tm_res, tm_out, tm_w, ka);
 }
 
 // output channels per tile: at most 128 so that two accumulator buffers fit TMEM (epilogue overlaps the MMAs)
 inline int tc_ntile(int c_out) { return c_out > 128 ? 128 : c_out; }
 
 struct TcRow { int c_in, c_out_tile; TcConfig cfg; };
-// Stage work at full tensor rate = MB * TPS * (KBW/16) * N/2 cycles: kept >= 512 so that the per-stage
-// barrier round trip of the single issuing thread is amortised.
-//   c_in  n    mb  ks kbw tps nst nsl nstg
-#define HFG_TC_TABLE(X)               \
-  X(512, 128, 1, 64, 64, 1, 3, 3, 4)  \
-  X(256, 128, 2, 64, 64, 1, 3, 2, 5)  \
-  X(128, 128, 2, 64, 64, 1, 3, 2, 5)  \
-  X(128, 64, 2, 64, 64, 2, 3, 2, 5)   \
-  X(64, 64, 2, 64, 64, 2, 3, 2, 5)    \
-  X(64, 32, 4, 64, 64, 2, 4, 2, 5)    \
-  X(32, 32, 4, 32, 32, 4, 4, 3, 8)    \
-  X(32, 16, 4, 32, 32, 4, 4, 3, 8)    \
-  X(16, 16, 4, 16, 16, 4, 4, 3, 8)
+// Stage work at full tensor rate = MB * TPS * (KBW/16) * N/2 cycles (x2 rows for a pair): kept >= 512 so that the
+// per-stage barrier round trip of the single issuing thread is amortised.  Rows are tried in order; the first row
+// matching (c_in, n) that fits shared memory and is not masked by the debug knob HFG_TC_SKIP (bit i = skip row i) is
+// the layer's config.  Measured on B200 (V1, 32 x 10 s): pairs win for N >= 64 (stage0 -12 %, stage1 -14 %, stage2 -3 %)
+// and lose for the 32-channel layers (stage3 +20 %: tiles too short to hide the cross-CTA barrier round trips).
+//   c_in  n    mb  ks kbw tps nst nsl nstg cg     (cg 2 = CTA pairs, cta_group::2)
+#define HFG_TC_TABLE(X)                  \
+  X(512, 128, 1, 64, 64, 1, 8, 3, 4, 2)  \
+  X(256, 128, 2, 64, 64, 1, 6, 2, 5, 2)  \
+  X(128, 128, 2, 64, 64, 1, 6, 2, 5, 2)  \
+  X(128, 64, 2, 64, 64, 2, 6, 2, 5, 2)   \
+  X(64, 64, 2, 64, 64, 2, 6, 2, 5, 2)    \
+  X(512, 128, 1, 64, 64, 1, 3, 3, 4, 1)  \
+  X(256, 128, 2, 64, 64, 1, 3, 2, 5, 1)  \
+  X(128, 128, 2, 64, 64, 1, 3, 2, 5, 1)  \
+  X(128, 64, 2, 64, 64, 2, 3, 2, 5, 1)   \
+  X(64, 64, 2, 64, 64, 2, 6, 2, 3, 1)    \
+  X(64, 32, 4, 64, 64, 2, 4, 2, 5, 1)    \
+  X(32, 32, 4, 32, 32, 4, 4, 3, 8, 1)    \
+  X(32, 16, 4, 32, 32, 4, 4, 3, 8, 1)    \
+  X(16, 16, 4, 16, 16, 4, 4, 3, 8, 1)
 
 const TcRow kTcTable[] = {
-#define X(CI, NN, MB, KS, KBW, TPS, NST, NSL, NSTG) {CI, NN, {NN, MB, KS, KBW, TPS, NST, NSL, NSTG}},
+#define X(CI, NN, MB, KS, KBW, TPS, NST, NSL, NSTG, CG) {CI, NN, {NN, MB, KS, KBW, TPS, NST, NSL, NSTG, CG}},
     HFG_TC_TABLE(X)
 #undef X
 };
 
+unsigned tc_skip_mask() {
+  static int init = 0; static unsigned mask = 0;
+  if (!init) { const char* e = getenv("HFG_TC_SKIP"); mask = e ? (unsigned)strtoul(e, nullptr, 0) : 0u; init = 1; }
+  return mask;
+}
+
 template <typename T>
 cudaError_t launch_shape(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out) {
   const int ci = a.c_in, n = tc_ntile(a.c_out);
-#define X(CI, NN, MB, KS, KBW, TPS, NST, NSL, NSTG) if (ci == CI && n == NN) return launch_t<T, CI, NN, MB, KS, KBW, TPS, NST, NSL, NSTG>(a, act, s, grid_out);
+  TcConfig c;
+  int mn = a.var[0].tap_off[0], mx = mn;
+  for (int v = 0; v < a.nvar; ++v)
+    for (int j = 0; j < a.var[v].ntaps; ++j) { mn = a.var[v].tap_off[j] < mn ? a.var[v].tap_off[j] : mn; mx = a.var[v].tap_off[j] > mx ? a.var[v].tap_off[j] : mx; }
+  if (!tc_config(a.c_in, a.c_out, mx - mn, &c)) return cudaErrorInvalidValue;
+#define X(CI, NN, MB, KS, KBW, TPS, NST, NSL, NSTG, CG) \
+  if (ci == CI && n == NN && c.cg == CG && c.nst == NST && c.nstg == NSTG) return launch_t<T, CI, NN, MB, KS, KBW, TPS, NST, NSL, NSTG, CG>(a, act, s, grid_out);
   HFG_TC_TABLE(X)
 #undef X
   return cudaErrorInvalidValue;
@@ -694,45 +836,56 @@ cudaError_t launch_shape(const TcArgs& a, ActType act, cudaStream_t s, int* grid
 
 }  // namespace
 
-bool tc_config(int c_in, int c_out, TcConfig* cfg) {
+// first unmasked row for (c_in, n) whose shared-memory plan fits a layer of this tap span (max_off - min_off over all variants)
+bool tc_config(int c_in, int c_out, int span, TcConfig* cfg) {
   const int n = tc_ntile(c_out);
-  if (c_out % n || c_out > kTcMaxCout) return false;
-  for (const TcRow& r : kTcTable)
-    if (r.c_in == c_in && r.c_out_tile == n) { if (cfg) *cfg = r.cfg; return true; }
+  if (c_out % n || c_out > kTcMaxCout || span < 0 || span > kTcMaxSpan) return false;
+  const unsigned skip = tc_skip_mask();
+  int i = 0;
+  for (const TcRow& r : kTcTable) {
+    if (r.c_in == c_in && r.c_out_tile == n && !((skip >> i) & 1u)) {
+      const TcConfig& c = r.cfg;
+      int br, nb;
+      tc_boxes(c.mb * 128 + span, &br, &nb);
+      if ((size_t)tc_plan(c.n, c.ks, c.kbw * c.tps, c.nst, c.nsl, c.nstg, br * nb, c.cg).total <= kTcMaxSmem) {
+        if (cfg) *cfg = c;
+        return true;
+      }
+    }
+    ++i;
+  }
   return false;
 }
 
 bool tc_supported(int c_in, int c_out, int ntaps, int span) {
-  if (ntaps < 1 || ntaps > kMaxTaps || span < 0 || span > kTcMaxSpan) return false;
-  TcConfig c;
-  if (!tc_config(c_in, c_out, &c)) return false;
-  int br, nb;
-  tc_boxes(c.mb * 128 + span, &br, &nb);
-  return (size_t)tc_plan(c.n, c.ks, c.kbw * c.tps, c.nst, c.nsl, c.nstg, br * nb).total <= kTcMaxSmem;
+  if (ntaps < 1 || ntaps > kMaxTaps) return false;
+  return tc_config(c_in, c_out, span, nullptr);
 }
 
 size_t tc_packed_weight_bytes(int c_in, int c_out, int ntaps) { return (size_t)ntaps * c_in * c_out * 2; }
 
-// fp32 [ntaps][c_in][c_out] -> [n-tile][K-slice][tap][k-block] stages of [KBW/8 chunks][N rows][8 x 16-bit]
-void tc_pack_weights(const float* w, int ntaps, int c_in, int c_out, ActType act, void* dst_host) {
+// fp32 [ntaps][c_in][c_out] -> [n-tile][K-slice][tap][k-block][CTA of the pair] blocks of [KBW/8 chunks][N/cg rows][8 x 16-bit]
+void tc_pack_weights(const float* w, int ntaps, int c_in, int c_out, int span, ActType act, void* dst_host) {
   TcConfig c;
-  if (!tc_config(c_in, c_out, &c)) return;
+  if (!tc_config(c_in, c_out, span, &c)) return;
   uint16_t* dst = reinterpret_cast<uint16_t*>(dst_host);
+  const int nb = c.n / c.cg;
   size_t o = 0;
   for (int nt = 0; nt < c_out / c.n; ++nt)
     for (int s = 0; s < c_in / c.ks; ++s)
       for (int j = 0; j < ntaps; ++j)
         for (int kb = 0; kb < c.ks / c.kbw; ++kb)
-          for (int chunk = 0; chunk < c.kbw / 8; ++chunk)
-            for (int row = 0; row < c.n; ++row)
-              for (int e = 0; e < 8; ++e) {
-                const int ci = s * c.ks + kb * c.kbw + chunk * 8 + e, co = nt * c.n + row;
-                const float f = w[((size_t)j * c_in + ci) * c_out + co];
-                uint16_t bits;
-                if (act == ACT_BF16) { __nv_bfloat16 h = __float2bfloat16_rn(f); memcpy(&bits, &h, 2); }
-                else { __half h = __float2half_rn(f); memcpy(&bits, &h, 2); }
-                dst[o++] = bits;
-              }
+          for (int r = 0; r < c.cg; ++r)
+            for (int chunk = 0; chunk < c.kbw / 8; ++chunk)
+              for (int row = 0; row < nb; ++row)
+                for (int e = 0; e < 8; ++e) {
+                  const int ci = s * c.ks + kb * c.kbw + chunk * 8 + e, co = nt * c.n + r * nb + row;
+                  const float f = w[((size_t)j * c_in + ci) * c_out + co];
+                  uint16_t bits;
+                  if (act == ACT_BF16) { __nv_bfloat16 h = __float2bfloat16_rn(f); memcpy(&bits, &h, 2); }
+                  else { __half h = __float2half_rn(f); memcpy(&bits, &h, 2); }
+                  dst[o++] = bits;
+                }
 }
 
 cudaError_t launch_conv_tc(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out) {

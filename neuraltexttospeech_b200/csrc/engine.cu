@@ -43,7 +43,7 @@ struct Layer {
   float* d_bias = nullptr;
   void* d_wpk = nullptr;
   bool use_tc = false;      // persistent tcgen05 kernel (conv_tc.cu): one launch per layer, phases = variants
-  std::vector<size_t> tc_off;   // byte offset of each phase's packed weights in d_wpk
+  size_t wpk_bytes = 0;     // size of d_wpk (multiple of 256)
 };
 
 thread_local std::string g_create_error;
@@ -68,7 +68,7 @@ struct hfg_ctx {
   long long timed_forwards = 0;      // forwards stamped since the last hfg_stage_times_ms
   int n_stage_marks = 0;
   // host-buffer path
-  int micro_batch = 16;
+  int micro_batch = 32;
   cudaStream_t stream = nullptr;
   void* ws = nullptr; size_t ws_bytes = 0;
   float* d_mel = nullptr; size_t d_mel_bytes = 0;
@@ -247,6 +247,7 @@ struct Runner {
     a.c_in = L.cin_pad; a.c_out = L.cout;
     a.res_inv = res_inv; a.out_scale = out_scale; a.out_slope = out_slope;
     a.nvar = (int)L.phases.size();
+    a.w_base = L.d_wpk; a.w_bytes = L.wpk_bytes;
     for (int p = 0; p < a.nvar; ++p) {
       const Phase& ph = L.phases[p];
       a.var[p].w = (const char*)L.d_wpk + ph.wpk_off;
@@ -477,13 +478,12 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
       }
     }
     // tensor-core eligibility (engine option "force_ffma" keeps everything on the direct kernel)
-    int max_taps = 0, max_span = 0;
+    int max_taps = 0, mn = L.phases[0].tap_off[0], mx = mn;     // span over ALL phases: they share one halo slab
     for (const Phase& ph : L.phases) {
       max_taps = ph.ntaps > max_taps ? ph.ntaps : max_taps;
-      int mn = ph.tap_off[0], mx = ph.tap_off[0];
-      for (int j = 1; j < ph.ntaps; ++j) { mn = std::min(mn, ph.tap_off[j]); mx = std::max(mx, ph.tap_off[j]); }
-      max_span = std::max(max_span, mx - mn);
+      for (int j = 0; j < ph.ntaps; ++j) { mn = std::min(mn, ph.tap_off[j]); mx = std::max(mx, ph.tap_off[j]); }
     }
+    const int max_span = mx - mn;
     int cin_mma = L.cin;
     if (L.name == "conv_pre") cin_mma = (int)align_up((size_t)L.cin, 64);
     L.use_tc = !is_post && h->act != ACT_F32 && !h->force_ffma && (int)L.phases.size() <= kMaxVariants &&
@@ -509,7 +509,8 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
       size_t total = 0;
       for (Phase& ph : L.phases) { ph.wpk_off = total; total += align_up(tc_packed_weight_bytes(L.cin_pad, L.cout, ph.ntaps), 256); }
       std::vector<char> pk(total);
-      for (Phase& ph : L.phases) tc_pack_weights(&w32[ph.w32_off], ph.ntaps, L.cin_pad, L.cout, h->act, pk.data() + ph.wpk_off);
+      for (Phase& ph : L.phases) tc_pack_weights(&w32[ph.w32_off], ph.ntaps, L.cin_pad, L.cout, max_span, h->act, pk.data() + ph.wpk_off);
+      L.wpk_bytes = total;
       CUDA_TRY(h, cudaMalloc(&L.d_wpk, total));
       CUDA_TRY(h, cudaMemcpy(L.d_wpk, pk.data(), total, cudaMemcpyHostToDevice));
     } else {
@@ -683,9 +684,9 @@ int hfg_op_tapped_conv(int act, int engine, const void* x_dev, int B, int x_rows
       return fail(nullptr, HFG_ERR_UNSUPPORTED, "tcgen05 kernel does not cover c_in=%d c_out=%d ntaps=%d span=%d act=%d in_slope=%g mrf_mode=%d",
                   c_in, c_out, ntaps, mx - mn, act, in_slope, mrf_mode);
     }
-    const size_t nb = tc_packed_weight_bytes(c_in, c_out, ntaps);
+    const size_t nb = align_up(tc_packed_weight_bytes(c_in, c_out, ntaps), 256);
     std::vector<char> pk(nb);
-    tc_pack_weights(w_host, ntaps, c_in, c_out, (ActType)act, pk.data());
+    tc_pack_weights(w_host, ntaps, c_in, c_out, mx - mn, (ActType)act, pk.data());
     CUDA_TRY(nullptr, cudaMalloc(&d_w, nb));
     CUDA_TRY(nullptr, cudaMemcpy(d_w, pk.data(), nb, cudaMemcpyHostToDevice));
     TcArgs t{};
@@ -693,6 +694,7 @@ int hfg_op_tapped_conv(int act, int engine, const void* x_dev, int B, int x_rows
     t.B = B; t.x_rows = x_rows; t.n_q = x_rows; t.out_rows = x_rows * out_stride; t.out_stride = out_stride;
     t.c_in = c_in; t.c_out = c_out; t.res_inv = res_inv; t.out_scale = out_scale; t.out_slope = out_slope;
     t.nvar = 1; t.var[0].w = d_w; t.var[0].ntaps = ntaps; t.var[0].out_off = out_off;
+    t.w_base = d_w; t.w_bytes = nb;
     for (int j = 0; j < ntaps; ++j) t.var[0].tap_off[j] = tap_off[j];
     e = launch_conv_tc(t, (ActType)act, s, nullptr);
   } else {

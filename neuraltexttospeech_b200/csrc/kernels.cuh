@@ -91,15 +91,17 @@ struct TcArgs {
   float res_inv, out_scale, out_slope;
   int nvar;
   TcVariant var[kMaxVariants];
+  const void* w_base;   // allocation holding every variant's packed weights (256-byte aligned; the CTA-pair
+  size_t w_bytes;       // configurations read it through one TMA map), and its size (multiple of 256)
 };
 struct TcConfig {       // tile configuration chosen for (c_in, c_out); see conv_tc.cu
-  int n, mb, ks, kbw, tps, nst, nsl, nstg;
+  int n, mb, ks, kbw, tps, nst, nsl, nstg, cg;   // cg = 2: CTA pairs (cta_group::2)
 };
-bool tc_config(int c_in, int c_out, TcConfig* cfg);
+bool tc_config(int c_in, int c_out, int span, TcConfig* cfg);   // span = max_off - min_off over ALL variants of the layer
 bool tc_supported(int c_in, int c_out, int ntaps, int span);
 size_t tc_packed_weight_bytes(int c_in, int c_out, int ntaps);
 // host-side repack of fp32 [ntaps][c_in][c_out] into the kernel's smem-image weight stages (16-bit)
-void tc_pack_weights(const float* w, int ntaps, int c_in, int c_out, ActType act, void* dst_host);
+void tc_pack_weights(const float* w, int ntaps, int c_in, int c_out, int span, ActType act, void* dst_host);
 // returns cudaSuccess or an error; *msg (optional) receives a static description on failure
 cudaError_t launch_conv_tc(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out);
 
