@@ -282,6 +282,7 @@ struct TcKArgs {
   int tiles_q, n_tiles, total_tiles;   // CG == 2: tiles_q / total_tiles count PAIR tiles of 2*MB*128 rows
   const void* w_base;                  // CG == 2: base of the layer's packed weights (tm_w), 256-byte rows
   int resident;                        // every tile uses the same weights and they fit the NST stages: load them once
+  float* post_out;                     // conv_post mode: audio[b, q] = tanh(channel 0) written as fp32, no 16-bit output tile
 };
 
 // ------------------------------------------------------------------ the kernel
@@ -518,7 +519,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
           const int buf = pcnt % NSTG;
           mbar_wait(&stg_done[buf], (pcnt / NSTG) & 1);
           if (elect_one()) {
-            if (q0 < ka.n_q) {
+            if (q0 < ka.n_q && ka.post_out == nullptr) {
               tma_store_4d(&tm_out, stg + buf * pl.stg_bytes, nt * N + p0, out_off, q0, b);
               bulk_commit();
               bulk_wait_read<0>();                      // the store has read the tile: the buffer may be refilled
@@ -601,6 +602,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
                 f = H2<T>::up(rr2[i].z); vv[i * 8 + 4] += f.x; vv[i * 8 + 5] += f.y;
                 f = H2<T>::up(rr2[i].w); vv[i * 8 + 6] += f.x; vv[i * 8 + 7] += f.y;
               }
+            }
+            if (ka.post_out != nullptr) {               // conv_post + tanh (reference model.py:170-171): C_out = 1 lives in column 0
+              if (valid && p0 + c0 == 0 && n0 == 0) ka.post_out[(size_t)b * ka.n_q + q] = tanhf(vv[0]);
+              continue;
             }
             const float osc = ka.out_scale, osl = ka.out_slope;
 #pragma unroll
@@ -724,6 +729,8 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
   if ((size_t)pl.total > kTcMaxSmem) return cudaErrorInvalidConfiguration;
   ka.tiles_q = (a.n_q + CG * MB * 128 - 1) / (CG * MB * 128);
   ka.w_base = a.w_base;
+  ka.post_out = a.post_out;
+  if (a.post_out && (a.out_stride != 1 || a.res || a.res2)) return cudaErrorInvalidValue;
   {
     int max_taps = 0;
     for (int v = 0; v < a.nvar; ++v) max_taps = a.var[v].ntaps > max_taps ? a.var[v].ntaps : max_taps;

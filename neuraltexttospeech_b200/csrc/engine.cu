@@ -36,6 +36,7 @@ struct Layer {
   bool transposed = false;
   int k = 0, dil = 1, stride = 1, cin = 0, cout = 0;
   int cin_pad = 0;        // channel count the kernels see (conv_pre pads num_mels up for the MMA path)
+  int cout_k = 0;         // output channels the kernels see (conv_post on the tcgen05 path pads 1 -> 16)
   std::vector<float> v, g, b;
   bool has_v = false, has_g = false, has_b = false;
   std::vector<Phase> phases;
@@ -238,13 +239,13 @@ struct Runner {
   // persistent tcgen05 kernel: the whole layer (all phases of a transposed conv) in one launch; x is
   // stored already activated (conv_tc.cu), res is stored activated with slope 1/res_inv
   void conv_tc(const Layer& L, const void* x, int x_rows, void* out, const void* res, float res_inv,
-               const void* res2, float out_scale, float out_slope) {
+               const void* res2, float out_scale, float out_slope, float* post_out = nullptr) {
     if (status != cudaSuccess) return;
     const int u = L.transposed ? L.stride : 1;
     TcArgs a{};
     a.x = x; a.out = out; a.res = res; a.res2 = res2; a.bias = L.d_bias;
     a.B = B; a.x_rows = x_rows; a.n_q = x_rows; a.out_rows = x_rows * u; a.out_stride = u;
-    a.c_in = L.cin_pad; a.c_out = L.cout;
+    a.c_in = L.cin_pad; a.c_out = L.cout_k; a.post_out = post_out;
     a.res_inv = res_inv; a.out_scale = out_scale; a.out_slope = out_slope;
     a.nvar = (int)L.phases.size();
     a.w_base = L.d_wpk; a.w_bytes = L.wpk_bytes;
@@ -379,6 +380,14 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
 
   // leakyReLU(0.3) -> conv_post -> tanh (model.py:169-171)
   const Layer& post = layer("conv_post");
+  if (post.use_tc) {            // x is stored activated with the final slope (see hfg_finalize_weights); w.T is free scratch here
+    r.conv_tc(post, x, L, w.T, nullptr, 1.0f, nullptr, 1.0f, 1.0f, audio_dev);
+    if (r.status != cudaSuccess) return fail(h, HFG_ERR_CUDA, "conv_post launch failed: %s", cudaGetErrorString(r.status));
+    stamp();
+    h->n_stage_marks = mark;
+    if (h->stage_timing) h->timed_forwards++;
+    return HFG_OK;
+  }
   PostArgs pa{};
   pa.x = x; pa.w = post.d_w32; pa.out = audio_dev; pa.B = B; pa.rows = L; pa.c_in = post.cin; pa.ntaps = post.k;
   pa.pad_left = (post.k - 1) / 2; pa.in_slope = x_preact ? 1.0f : kFinalSlope;
@@ -486,14 +495,19 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
     const int max_span = mx - mn;
     int cin_mma = L.cin;
     if (L.name == "conv_pre") cin_mma = (int)align_up((size_t)L.cin, 64);
-    L.use_tc = !is_post && h->act != ACT_F32 && !h->force_ffma && (int)L.phases.size() <= kMaxVariants &&
-               tc_supported(cin_mma, L.cout, max_taps, max_span);
+    // conv_post (C_out = 1) rides the tcgen05 kernel as a 16-column tile when its input is stored pre-activated,
+    // i.e. when the last stage's resblocks run on the tcgen05 kernel too (layers are finalised in call order)
+    L.cout_k = L.cout;
+    if (is_post && h->layers[h->layers.size() - 2].use_tc) L.cout_k = 16;
+    L.use_tc = (!is_post || L.cout_k == 16) && h->act != ACT_F32 && !h->force_ffma && (int)L.phases.size() <= kMaxVariants &&
+               tc_supported(cin_mma, L.cout_k, max_taps, max_span);
+    if (!L.use_tc) L.cout_k = L.cout;
     if (L.use_tc) L.cin_pad = cin_mma;
     // fp32 weights per phase, [ntaps][cin_pad][cout]
     std::vector<float> w32;
     for (Phase& ph : L.phases) {
       ph.w32_off = w32.size();
-      w32.resize(w32.size() + (size_t)ph.ntaps * L.cin_pad * L.cout, 0.f);
+      w32.resize(w32.size() + (size_t)ph.ntaps * L.cin_pad * L.cout_k, 0.f);
     }
     for (size_t p = 0; p < L.phases.size(); ++p) {
       Phase& ph = L.phases[p];
@@ -502,14 +516,14 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
         if (!L.transposed) j = t;
         else { const int u = L.stride, P = (L.k - u) / 2; j = ((int)p + P) % u + t * u; }
         for (int ci = 0; ci < L.cin; ++ci)
-          memcpy(&w32[ph.w32_off + ((size_t)t * L.cin_pad + ci) * L.cout], &w[((size_t)j * L.cin + ci) * L.cout], sizeof(float) * L.cout);
+          memcpy(&w32[ph.w32_off + ((size_t)t * L.cin_pad + ci) * L.cout_k], &w[((size_t)j * L.cin + ci) * L.cout], sizeof(float) * L.cout);
       }
     }
     if (L.use_tc) {
       size_t total = 0;
-      for (Phase& ph : L.phases) { ph.wpk_off = total; total += align_up(tc_packed_weight_bytes(L.cin_pad, L.cout, ph.ntaps), 256); }
+      for (Phase& ph : L.phases) { ph.wpk_off = total; total += align_up(tc_packed_weight_bytes(L.cin_pad, L.cout_k, ph.ntaps), 256); }
       std::vector<char> pk(total);
-      for (Phase& ph : L.phases) tc_pack_weights(&w32[ph.w32_off], ph.ntaps, L.cin_pad, L.cout, max_span, h->act, pk.data() + ph.wpk_off);
+      for (Phase& ph : L.phases) tc_pack_weights(&w32[ph.w32_off], ph.ntaps, L.cin_pad, L.cout_k, max_span, h->act, pk.data() + ph.wpk_off);
       L.wpk_bytes = total;
       CUDA_TRY(h, cudaMalloc(&L.d_wpk, total));
       CUDA_TRY(h, cudaMemcpy(L.d_wpk, pk.data(), total, cudaMemcpyHostToDevice));
@@ -517,7 +531,7 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
       CUDA_TRY(h, cudaMalloc((void**)&L.d_w32, w32.size() * sizeof(float)));
       CUDA_TRY(h, cudaMemcpy(L.d_w32, w32.data(), w32.size() * sizeof(float), cudaMemcpyHostToDevice));
     }
-    std::vector<float> bias(align_up((size_t)L.cout, 4), 0.f);
+    std::vector<float> bias(align_up((size_t)L.cout_k, 4), 0.f);
     memcpy(bias.data(), L.b.data(), sizeof(float) * L.cout);
     CUDA_TRY(h, cudaMalloc((void**)&L.d_bias, bias.size() * sizeof(float)));
     CUDA_TRY(h, cudaMemcpy(L.d_bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
@@ -624,7 +638,7 @@ int hfg_layer_engines(hfg_handle h, char* buf, size_t cap) {
   if (!h->finalized) return fail(h, HFG_ERR_STATE, "hfg_layer_engines: weights not finalised");
   std::string out;
   for (const Layer& L : h->layers)
-    out += L.name + ":" + (L.name == "conv_post" ? "post" : (L.use_tc ? "tc" : "ffma")) + "\n";
+    out += L.name + ":" + (L.use_tc ? "tc" : (L.name == "conv_post" ? "post" : "ffma")) + "\n";
   if (out.size() + 1 > cap) return fail(h, HFG_ERR_NOMEM, "need %zu bytes", out.size() + 1);
   memcpy(buf, out.c_str(), out.size() + 1);
   return HFG_OK;

@@ -91,6 +91,8 @@ struct TcArgs {
   float res_inv, out_scale, out_slope;
   int nvar;
   TcVariant var[kMaxVariants];
+  float* post_out;      // conv_post mode (may be NULL): fp32 [B, n_q] = tanh(output channel 0); `out` is then only a scratch
+                        // buffer of >= B*n_q*c_out 16-bit elements for the (unused) output tensor map
   const void* w_base;   // allocation holding every variant's packed weights (256-byte aligned; the CTA-pair
   size_t w_bytes;       // configurations read it through one TMA map), and its size (multiple of 256)
 };

@@ -160,9 +160,9 @@ def test_weight_errors():
 
 @pytest.mark.parametrize("v", "13")
 def test_tensor_core_path_covers_every_conv(v, gens):
-    # V1 / V3 in 16-bit mode: every conv but conv_post runs on the tcgen05 kernel (no silent direct-kernel fallback)
+    # V1 / V3 in 16-bit mode: every conv, conv_post included (as a 16-column tile with a tanh/fp32 epilogue), runs on
+    # the tcgen05 kernel (no silent direct-kernel fallback)
     eng = gens(v, "fp16").layer_engines()
-    assert eng.pop("conv_post") == "post"
     assert set(eng.values()) == {"tc"}, {k: e for k, e in eng.items() if e != "tc"}
     eng32 = gens(v, "fp32").layer_engines()
-    assert "tc" not in set(eng32.values())
+    assert "tc" not in set(eng32.values()) and eng32["conv_post"] == "post"
