@@ -105,8 +105,8 @@ def cpu_port_audio_s_per_s(version, B, T, repeats, threads=None):
     from neuraltexttospeech_b200.hparams import HParams
     from neuraltexttospeech_b200.synthetic import synthetic_mel, synthetic_weights
     from oracle import hifigan_oracle as O
-    if threads:
-        torch.set_num_threads(threads)
+    # all the host threads this process may use (torchrun exports OMP_NUM_THREADS=1; override it at run time)
+    torch.set_num_threads(threads or len(os.sched_getaffinity(0)))
     h = HParams.builtin(version)
     w = synthetic_weights(h, "A")
     mel = synthetic_mel(B, T, h.num_mels)
@@ -298,7 +298,7 @@ def main():
                               "hbm_floor_ms": bytes_boundary / bw * 1000, "tensor_floor_ms": flops / p_tensor * 1000},
             "stages": {"batch": mb, "rows": stages},
         }
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:
             # CPU baseline on rank 0: BASELINE.json configs[0] (V1, batch 1, 256 frames), oracle port
             best, mean, threads, ts = cpu_port_audio_s_per_s("1", 1, 256, 5)
             line["cpu_baseline"] = {"value": best, "unit": "audio-s/s", "cores": threads, "kind": "port",
