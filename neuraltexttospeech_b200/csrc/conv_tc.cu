@@ -282,7 +282,8 @@ struct TcKArgs {
   int tiles_q, n_tiles, total_tiles;   // CG == 2: tiles_q / total_tiles count PAIR tiles of 2*MB*128 rows
   const void* w_base;                  // CG == 2: base of the layer's packed weights (tm_w), 256-byte rows
   int resident;                        // every tile uses the same weights and they fit the NST stages: load them once
-  float* post_out;                     // conv_post mode: audio[b, q] = tanh(channel 0) written as fp32, no 16-bit output tile
+  float* post_out;                     // conv_post mode: audio[b, q*post_f + s] = tanh(channel s) written as fp32, no 16-bit tile
+  int post_f;
 };
 
 // ------------------------------------------------------------------ the kernel
@@ -604,7 +605,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
               }
             }
             if (ka.post_out != nullptr) {               // conv_post + tanh (reference model.py:170-171): C_out = 1 lives in column 0
-              if (valid && p0 + c0 == 0 && n0 == 0) ka.post_out[(size_t)b * ka.n_q + q] = tanhf(vv[0]);
+              if (valid && p0 + c0 == 0 && n0 == 0) {
+                float* op = ka.post_out + ((size_t)b * ka.n_q + q) * ka.post_f;
+                if (ka.post_f == 1) op[0] = tanhf(vv[0]);
+                else if (ka.post_f == 2) *reinterpret_cast<float2*>(op) = make_float2(tanhf(vv[0]), tanhf(vv[1]));
+                else {
+#pragma unroll
+                  for (int i = 0; i < 16; ++i) if (i < ka.post_f) op[i] = tanhf(vv[i]);
+                }
+              }
               continue;
             }
             const float osc = ka.out_scale, osl = ka.out_slope;
@@ -729,7 +738,8 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
   if ((size_t)pl.total > kTcMaxSmem) return cudaErrorInvalidConfiguration;
   ka.tiles_q = (a.n_q + CG * MB * 128 - 1) / (CG * MB * 128);
   ka.w_base = a.w_base;
-  ka.post_out = a.post_out;
+  ka.post_out = a.post_out; ka.post_f = a.post_f;
+  if (a.post_out && (a.post_f < 1 || a.post_f > 16)) return cudaErrorInvalidValue;
   if (a.post_out && (a.out_stride != 1 || a.res || a.res2)) return cudaErrorInvalidValue;
   {
     int max_taps = 0;

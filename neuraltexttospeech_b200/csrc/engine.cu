@@ -37,6 +37,12 @@ struct Layer {
   int k = 0, dil = 1, stride = 1, cin = 0, cout = 0;
   int cin_pad = 0;        // channel count the kernels see (conv_pre pads num_mels up for the MMA path)
   int cout_k = 0;         // output channels the kernels see (conv_post on the tcgen05 path pads 1 -> 16)
+  int in_rate = 1, out_rate = 1;   // rows per mel frame of the input / output tensor
+  // Time folding (tcgen05 path, channel counts below the 16-wide MMA tile, e.g. V2's 8-channel stage): a [L, C] tensor
+  // is bit-identical to [L/f, C*f]; a conv over it is a conv over the folded rows with block-Toeplitz weights.
+  int fold_in = 1, fold_out = 1;
+  int u_k = 1;            // output stride in kernel-view rows (stride * fold_in / fold_out)
+  int post_f = 0;         // conv_post on the tcgen05 path: samples per kernel-view row
   std::vector<float> v, g, b;
   bool has_v = false, has_g = false, has_b = false;
   std::vector<Phase> phases;
@@ -108,9 +114,12 @@ int conv_pad_left(int k, int d, int compat, bool* ok) {
 
 void build_layers(hfg_ctx* h) {
   const hfg_config& c = h->cfg;
+  int rate = 1;
   auto add = [&](const std::string& name, bool tr, int k, int d, int s, int cin, int cout) {
     Layer L; L.name = name; L.transposed = tr; L.k = k; L.dil = d; L.stride = s; L.cin = cin; L.cout = cout;
     L.cin_pad = cin;
+    L.in_rate = rate; L.out_rate = rate * (tr ? s : 1);
+    rate = L.out_rate;
     h->index[name] = (int)h->layers.size();
     h->layers.push_back(std::move(L));
   };
@@ -187,6 +196,61 @@ std::vector<float> fold_weight_norm(const Layer& L) {
   return w;
 }
 
+// Kernel-visible form of a layer: phases ("variants") of taps over kernel-view rows.
+//   unfolded:  out[q*u + p] = sum_{(o, j) in taps_p} x[q + o] . W_j            (conv: u = 1; transposed conv: polyphase)
+//   conv folded by f (input and output [L, C] viewed as [L/f, C*f], row r = Q*f + s):
+//       out'[Q, (s, co)] = sum_O sum_(s', ci) x'[Q + O, (s', ci)] . W'_O,  O = floor((s + o)/f), s' = (s + o) mod f
+//   transposed conv whose OUTPUT is folded by f (f | u): kernel-view stride u/f, variant p' holds phases p'*f + s as channel blocks
+//   conv_post on the tcgen05 path: C_out = 1 -> column s of a 16-column tile holds sample Q*f + s
+struct KView {
+  int cin_k = 0, cout_k = 0, u_k = 1, post_f = 0;
+  std::vector<std::vector<int>> off;                        // [phase][tap] kernel-view row offset
+  std::vector<std::vector<std::vector<float>>> w;           // [phase][tap] -> [cin_k][cout_k]
+  int max_taps() const { size_t m = 0; for (auto& o : off) m = std::max(m, o.size()); return (int)m; }
+  int span() const {                                        // over ALL phases: they share one halo slab
+    int mn = off[0][0], mx = mn;
+    for (auto& o : off) for (int v : o) { mn = std::min(mn, v); mx = std::max(mx, v); }
+    return mx - mn;
+  }
+};
+
+inline int floordiv(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
+
+KView build_view(const Layer& L, const std::vector<float>& w, int pad_left, int fi, int fo, bool post_tc) {
+  KView V;
+  const int u = L.transposed ? L.stride : 1, cin = L.cin, cout = L.cout;
+  V.cin_k = cin * fi; V.cout_k = post_tc ? 16 : cout * fo; V.post_f = post_tc ? fo : 0;
+  std::vector<std::vector<std::pair<int, int>>> ut(u);      // unfolded (row offset, kernel index j) per phase
+  if (!L.transposed) {
+    for (int j = 0; j < L.k; ++j) ut[0].push_back({j * L.dil - pad_left, j});
+  } else {
+    const int P = (L.k - u) / 2;
+    for (int p = 0; p < u; ++p)
+      for (int j = (p + P) % u; j < L.k; j += u) ut[p].push_back({(p + P - j) / u, j});   // exact: (p+P-j) % u == 0
+  }
+  V.u_k = L.transposed ? u / fo : 1;
+  const int nph = L.transposed ? V.u_k : 1;
+  for (int pp = 0; pp < nph; ++pp) {
+    std::map<int, std::vector<float>> acc;
+    const int f = L.transposed ? fo : fi;                  // conv: fi == fo (conv_post: fo == fi, one output sample per s)
+    for (int sidx = 0; sidx < f; ++sidx) {
+      const auto& taps = ut[L.transposed ? pp * fo + sidx : 0];
+      for (const auto& tj : taps) {
+        const int O = L.transposed ? tj.first : floordiv(sidx + tj.first, f);
+        const int sp = L.transposed ? 0 : sidx + tj.first - O * f;
+        std::vector<float>& m = acc[O];
+        if (m.empty()) m.assign((size_t)V.cin_k * V.cout_k, 0.f);
+        for (int ci = 0; ci < cin; ++ci)
+          for (int co = 0; co < cout; ++co)
+            m[(size_t)(sp * cin + ci) * V.cout_k + (post_tc ? sidx : sidx * cout + co)] += w[((size_t)tj.second * cin + ci) * cout + co];
+      }
+    }
+    V.off.emplace_back(); V.w.emplace_back();
+    for (auto& kv : acc) { V.off.back().push_back(kv.first); V.w.back().push_back(std::move(kv.second)); }
+  }
+  return V;
+}
+
 void free_layer_device(Layer& L) {
   if (L.d_w32) cudaFree(L.d_w32);
   if (L.d_bias) cudaFree(L.d_bias);
@@ -241,11 +305,11 @@ struct Runner {
   void conv_tc(const Layer& L, const void* x, int x_rows, void* out, const void* res, float res_inv,
                const void* res2, float out_scale, float out_slope, float* post_out = nullptr) {
     if (status != cudaSuccess) return;
-    const int u = L.transposed ? L.stride : 1;
+    const int u = L.u_k, rows = x_rows / L.fold_in;      // kernel-view rows (time folding, see Layer)
     TcArgs a{};
     a.x = x; a.out = out; a.res = res; a.res2 = res2; a.bias = L.d_bias;
-    a.B = B; a.x_rows = x_rows; a.n_q = x_rows; a.out_rows = x_rows * u; a.out_stride = u;
-    a.c_in = L.cin_pad; a.c_out = L.cout_k; a.post_out = post_out;
+    a.B = B; a.x_rows = rows; a.n_q = rows; a.out_rows = rows * u; a.out_stride = u;
+    a.c_in = L.cin_pad; a.c_out = L.cout_k; a.post_out = post_out; a.post_f = L.post_f;
     a.res_inv = res_inv; a.out_scale = out_scale; a.out_slope = out_slope;
     a.nvar = (int)L.phases.size();
     a.w_base = L.d_wpk; a.w_bytes = L.wpk_bytes;
@@ -466,64 +530,52 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
   h->precision = precision;
   h->act = precision == HFG_PRECISION_FP32 ? ACT_F32 : (precision == HFG_PRECISION_FP16 ? ACT_F16 : ACT_BF16);
   const hfg_config& c = h->cfg;
-  for (Layer& L : h->layers) {
+  for (size_t li = 0; li < h->layers.size(); ++li) {
+    Layer& L = h->layers[li];
     free_layer_device(L);
     const std::vector<float> w = fold_weight_norm(L);   // canonical [k][cin][cout]
-    const bool is_post = (L.name == "conv_post");
-    // phases and tap tables
-    L.phases.clear();
-    L.cin_pad = L.cin;
-    if (!L.transposed) {
-      bool ok; Phase ph; ph.ntaps = L.k;
-      const int pl = (L.name == "conv_pre" || is_post) ? (L.dil * (L.k - 1)) / 2 : conv_pad_left(L.k, L.dil, c.compat, &ok);
-      for (int j = 0; j < L.k; ++j) ph.tap_off[j] = j * L.dil - pl;
-      L.phases.push_back(ph);
-    } else {
-      const int u = L.stride, P = (L.k - u) / 2;
-      for (int p = 0; p < u; ++p) {
-        Phase ph;
-        for (int j = (p + P) % u; j < L.k; j += u) ph.tap_off[ph.ntaps++] = (p + P - j) / u;   // exact: (p+P-j) % u == 0
-        L.phases.push_back(ph);
-      }
-    }
-    // tensor-core eligibility (engine option "force_ffma" keeps everything on the direct kernel)
-    int max_taps = 0, mn = L.phases[0].tap_off[0], mx = mn;     // span over ALL phases: they share one halo slab
-    for (const Phase& ph : L.phases) {
-      max_taps = ph.ntaps > max_taps ? ph.ntaps : max_taps;
-      for (int j = 0; j < ph.ntaps; ++j) { mn = std::min(mn, ph.tap_off[j]); mx = std::max(mx, ph.tap_off[j]); }
-    }
-    const int max_span = mx - mn;
-    int cin_mma = L.cin;
-    if (L.name == "conv_pre") cin_mma = (int)align_up((size_t)L.cin, 64);
-    // conv_post (C_out = 1) rides the tcgen05 kernel as a 16-column tile when its input is stored pre-activated,
+    const bool is_post = (L.name == "conv_post"), is_pre = (L.name == "conv_pre");
+    bool ok;
+    const int pl = (is_pre || is_post) ? (L.dil * (L.k - 1)) / 2 : (L.transposed ? 0 : conv_pad_left(L.k, L.dil, c.compat, &ok));
+    const bool tc_mode = h->act != ACT_F32 && !h->force_ffma;
+    // fold factor of a [rows, C] tensor on the tcgen05 path: C*f = 16 when C < 16 and the row count is divisible
+    auto fold_of = [&](int C, int rate) { return (tc_mode && C < 16 && 16 % C == 0 && rate % (16 / C) == 0) ? 16 / C : 1; };
+    // conv_post rides the tcgen05 kernel (16-column tile, tanh/fp32 epilogue) when its input is stored pre-activated,
     // i.e. when the last stage's resblocks run on the tcgen05 kernel too (layers are finalised in call order)
-    L.cout_k = L.cout;
-    if (is_post && h->layers[h->layers.size() - 2].use_tc) L.cout_k = 16;
-    L.use_tc = (!is_post || L.cout_k == 16) && h->act != ACT_F32 && !h->force_ffma && (int)L.phases.size() <= kMaxVariants &&
-               tc_supported(cin_mma, L.cout_k, max_taps, max_span);
-    if (!L.use_tc) L.cout_k = L.cout;
-    if (L.use_tc) L.cin_pad = cin_mma;
-    // fp32 weights per phase, [ntaps][cin_pad][cout]
-    std::vector<float> w32;
-    for (Phase& ph : L.phases) {
-      ph.w32_off = w32.size();
-      w32.resize(w32.size() + (size_t)ph.ntaps * L.cin_pad * L.cout_k, 0.f);
+    const bool post_tc = is_post && tc_mode && li > 0 && h->layers[li - 1].use_tc;
+    KView V;
+    L.use_tc = false;
+    if (tc_mode && (!is_post || post_tc)) {
+      int fi = fold_of(L.cin, L.in_rate), fo = is_post ? fi : fold_of(L.cout, L.out_rate);
+      if (L.transposed ? (fi != 1 || L.stride % fo != 0) : (!is_post && fi != fo)) fi = fo = 1;
+      V = build_view(L, w, pl, fi, fo, post_tc);
+      const int cin_mma = is_pre ? (int)align_up((size_t)V.cin_k, 64) : V.cin_k;
+      L.use_tc = (int)V.off.size() <= kMaxVariants && V.max_taps() <= kMaxTaps && tc_supported(cin_mma, V.cout_k, V.max_taps(), V.span());
+      if (L.use_tc) { L.cin_pad = cin_mma; L.fold_in = fi; L.fold_out = fo; }
     }
-    for (size_t p = 0; p < L.phases.size(); ++p) {
-      Phase& ph = L.phases[p];
+    if (!L.use_tc) {                                     // direct kernels: unfolded view
+      V = build_view(L, w, pl, 1, 1, false);
+      L.cin_pad = L.cin; L.fold_in = L.fold_out = 1;
+    }
+    L.cout_k = V.cout_k; L.u_k = V.u_k; L.post_f = V.post_f;
+    L.phases.clear();
+    std::vector<float> w32;                              // per phase [ntaps][cin_pad][cout_k]
+    for (size_t p = 0; p < V.off.size(); ++p) {
+      Phase ph; ph.ntaps = (int)V.off[p].size(); ph.w32_off = w32.size();
+      w32.resize(w32.size() + (size_t)ph.ntaps * L.cin_pad * L.cout_k, 0.f);
       for (int t = 0; t < ph.ntaps; ++t) {
-        int j;
-        if (!L.transposed) j = t;
-        else { const int u = L.stride, P = (L.k - u) / 2; j = ((int)p + P) % u + t * u; }
-        for (int ci = 0; ci < L.cin; ++ci)
-          memcpy(&w32[ph.w32_off + ((size_t)t * L.cin_pad + ci) * L.cout_k], &w[((size_t)j * L.cin + ci) * L.cout], sizeof(float) * L.cout);
+        ph.tap_off[t] = V.off[p][t];
+        for (int ci = 0; ci < V.cin_k; ++ci)
+          memcpy(&w32[ph.w32_off + ((size_t)t * L.cin_pad + ci) * L.cout_k], &V.w[p][t][(size_t)ci * L.cout_k], sizeof(float) * L.cout_k);
       }
+      L.phases.push_back(ph);
     }
     if (L.use_tc) {
+      const int span = V.span();
       size_t total = 0;
       for (Phase& ph : L.phases) { ph.wpk_off = total; total += align_up(tc_packed_weight_bytes(L.cin_pad, L.cout_k, ph.ntaps), 256); }
       std::vector<char> pk(total);
-      for (Phase& ph : L.phases) tc_pack_weights(&w32[ph.w32_off], ph.ntaps, L.cin_pad, L.cout_k, max_span, h->act, pk.data() + ph.wpk_off);
+      for (Phase& ph : L.phases) tc_pack_weights(&w32[ph.w32_off], ph.ntaps, L.cin_pad, L.cout_k, span, h->act, pk.data() + ph.wpk_off);
       L.wpk_bytes = total;
       CUDA_TRY(h, cudaMalloc(&L.d_wpk, total));
       CUDA_TRY(h, cudaMemcpy(L.d_wpk, pk.data(), total, cudaMemcpyHostToDevice));
@@ -532,7 +584,8 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
       CUDA_TRY(h, cudaMemcpy(L.d_w32, w32.data(), w32.size() * sizeof(float), cudaMemcpyHostToDevice));
     }
     std::vector<float> bias(align_up((size_t)L.cout_k, 4), 0.f);
-    memcpy(bias.data(), L.b.data(), sizeof(float) * L.cout);
+    if (L.post_f > 0) { for (int sidx = 0; sidx < L.post_f; ++sidx) bias[sidx] = L.b[0]; }
+    else { for (int sidx = 0; sidx < L.fold_out; ++sidx) memcpy(&bias[(size_t)sidx * L.cout], L.b.data(), sizeof(float) * L.cout); }
     CUDA_TRY(h, cudaMalloc((void**)&L.d_bias, bias.size() * sizeof(float)));
     CUDA_TRY(h, cudaMemcpy(L.d_bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
   }

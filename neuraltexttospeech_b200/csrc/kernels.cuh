@@ -7,7 +7,7 @@
 
 namespace hfg {
 
-constexpr int kMaxTaps = 16;
+constexpr int kMaxTaps = 24;      // a k=11 dilated conv folded by 2 has 17 kernel-view taps
 
 enum ActType : int { ACT_F32 = 0, ACT_F16 = 1, ACT_BF16 = 2 };
 
@@ -91,7 +91,8 @@ struct TcArgs {
   float res_inv, out_scale, out_slope;
   int nvar;
   TcVariant var[kMaxVariants];
-  float* post_out;      // conv_post mode (may be NULL): fp32 [B, n_q] = tanh(output channel 0); `out` is then only a scratch
+  int post_f;           // conv_post mode: samples per row (time folding): audio[b, q*post_f + s] = tanh(output channel s)
+  float* post_out;      // conv_post mode (may be NULL): fp32 [B, n_q*post_f]; `out` is then only a scratch
                         // buffer of >= B*n_q*c_out 16-bit elements for the (unused) output tensor map
   const void* w_base;   // allocation holding every variant's packed weights (256-byte aligned; the CTA-pair
   size_t w_bytes;       // configurations read it through one TMA map), and its size (multiple of 256)

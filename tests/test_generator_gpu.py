@@ -158,10 +158,10 @@ def test_weight_errors():
     g.close()
 
 
-@pytest.mark.parametrize("v", "13")
+@pytest.mark.parametrize("v", "123")
 def test_tensor_core_path_covers_every_conv(v, gens):
-    # V1 / V3 in 16-bit mode: every conv, conv_post included (as a 16-column tile with a tanh/fp32 epilogue), runs on
-    # the tcgen05 kernel (no silent direct-kernel fallback)
+    # 16-bit mode: every conv, conv_post included (as a 16-column tile with a tanh/fp32 epilogue), runs on the tcgen05
+    # kernel (no silent direct-kernel fallback); V2's 8-channel stage gets there by time folding ([L,8] == [L/2,16])
     eng = gens(v, "fp16").layer_engines()
     assert set(eng.values()) == {"tc"}, {k: e for k, e in eng.items() if e != "tc"}
     eng32 = gens(v, "fp32").layer_engines()

@@ -6,7 +6,7 @@ for cfg in v3_b64x10s v2_b256x10s v1_b1x256; do
 import json
 try:
     d=json.load(open("gpurun_out/cfg_$cfg.json"))
-    print("$cfg value %.0f e2e %.0f ms %.2f frac_stage_roof %.3f"%(d["value"], d["e2e"]["value"], d["ms_per_step"], d["roofline_step"]["frac_of_per_stage_roofline"]))
+    print("$cfg value %.0f e2e %.0f ms %.2f frac_stage_roof %.3f"%(d["value"], (d["e2e"] or {"value":0})["value"], d["ms_per_step"], d["roofline_step"]["frac_of_per_stage_roofline"]))
     for r in d["stages"]["rows"]: print("   ", r)
 except Exception as e:
     print("$cfg failed", e, open("gpurun_out/cfg_$cfg.err").read()[-800:])
