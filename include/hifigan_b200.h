@@ -99,6 +99,14 @@ int hfg_forward(hfg_handle h, const float* mel_dev, int B, int T, float* audio_d
  * asynchronous; pageable memory works too. */
 int hfg_forward_host(hfg_handle h, const float* mel_host, int B, int T, float* audio_host);
 
+/* 16-bit PCM output, fused into the conv_post epilogue: sample = (int16)trunc(clamp(audio, -1, 1)
+ * * 32768), +1.0 saturating to 32767 -- the step the reference intends after the vocoder
+ * (Grad-TTS_TF/inference.py:89; FastSpeech2_TF/FastSpeech2/utils/model.py:82-85).  pcm: [B, T*prod(rates)] int16.
+ * Halves the device->host bytes of the host variant. */
+int hfg_forward_pcm16(hfg_handle h, const float* mel_dev, int B, int T, int16_t* pcm_dev,
+                      void* workspace_dev, size_t workspace_bytes, void* stream);
+int hfg_forward_host_pcm16(hfg_handle h, const float* mel_host, int B, int T, int16_t* pcm_host);
+
 /* Utterances per micro-batch used by hfg_forward_host (default 32); 0 = whole batch. */
 int hfg_set_option(hfg_handle h, const char* key, long long value);
 

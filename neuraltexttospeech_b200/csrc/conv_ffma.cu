@@ -260,7 +260,9 @@ __global__ void __launch_bounds__(kPostThreads) conv_post_kernel(const PostArgs 
         }
       }
     }
-    a.out[(size_t)b * a.rows + t] = tanhf((s0 + s1) + (s2 + s3) + a.bias);
+    const float y = tanhf((s0 + s1) + (s2 + s3) + a.bias);
+    if (a.out_pcm) a.out_pcm[(size_t)b * a.rows + t] = pcm16_of(y);
+    else a.out[(size_t)b * a.rows + t] = y;
   }
 }
 

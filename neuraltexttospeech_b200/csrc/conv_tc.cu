@@ -284,6 +284,7 @@ struct TcKArgs {
   int resident;                        // every tile uses the same weights and they fit the NST stages: load them once
   float* post_out;                     // conv_post mode: audio[b, q*post_f + s] = tanh(channel s) written as fp32, no 16-bit tile
   int post_f;
+  int16_t* post_pcm;                   // conv_post mode: 16-bit PCM output instead of post_out (pcm16_of)
 };
 
 // ------------------------------------------------------------------ the kernel
@@ -520,7 +521,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
           const int buf = pcnt % NSTG;
           mbar_wait(&stg_done[buf], (pcnt / NSTG) & 1);
           if (elect_one()) {
-            if (q0 < ka.n_q && ka.post_out == nullptr) {
+            if (q0 < ka.n_q && ka.post_out == nullptr && ka.post_pcm == nullptr) {
               tma_store_4d(&tm_out, stg + buf * pl.stg_bytes, nt * N + p0, out_off, q0, b);
               bulk_commit();
               bulk_wait_read<0>();                      // the store has read the tile: the buffer may be refilled
@@ -604,8 +605,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
                 f = H2<T>::up(rr2[i].w); vv[i * 8 + 6] += f.x; vv[i * 8 + 7] += f.y;
               }
             }
-            if (ka.post_out != nullptr) {               // conv_post + tanh (reference model.py:170-171): C_out = 1 lives in column 0
-              if (valid && p0 + c0 == 0 && n0 == 0) {
+            if (ka.post_out != nullptr || ka.post_pcm != nullptr) {   // conv_post + tanh (reference model.py:170-171): C_out = 1 lives in column 0
+              if (valid && p0 + c0 == 0 && n0 == 0 && ka.post_pcm != nullptr) {
+                int16_t* op = ka.post_pcm + ((size_t)b * ka.n_q + q) * ka.post_f;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) if (i < ka.post_f) op[i] = pcm16_of(tanhf(vv[i]));
+              } else if (valid && p0 + c0 == 0 && n0 == 0) {
                 float* op = ka.post_out + ((size_t)b * ka.n_q + q) * ka.post_f;
                 if (ka.post_f == 1) op[0] = tanhf(vv[0]);
                 else if (ka.post_f == 2) *reinterpret_cast<float2*>(op) = make_float2(tanhf(vv[0]), tanhf(vv[1]));
@@ -738,9 +743,10 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
   if ((size_t)pl.total > kTcMaxSmem) return cudaErrorInvalidConfiguration;
   ka.tiles_q = (a.n_q + CG * MB * 128 - 1) / (CG * MB * 128);
   ka.w_base = a.w_base;
-  ka.post_out = a.post_out; ka.post_f = a.post_f;
-  if (a.post_out && (a.post_f < 1 || a.post_f > 16)) return cudaErrorInvalidValue;
-  if (a.post_out && (a.out_stride != 1 || a.res || a.res2)) return cudaErrorInvalidValue;
+  ka.post_out = a.post_out; ka.post_f = a.post_f; ka.post_pcm = a.post_pcm;
+  const bool post_mode = a.post_out || a.post_pcm;
+  if (post_mode && (a.post_f < 1 || a.post_f > 16)) return cudaErrorInvalidValue;
+  if (post_mode && (a.out_stride != 1 || a.res || a.res2)) return cudaErrorInvalidValue;
   {
     int max_taps = 0;
     for (int v = 0; v < a.nvar; ++v) max_taps = a.var[v].ntaps > max_taps ? a.var[v].ntaps : max_taps;

@@ -79,7 +79,7 @@ struct hfg_ctx {
   cudaStream_t stream = nullptr;
   void* ws = nullptr; size_t ws_bytes = 0;
   float* d_mel = nullptr; size_t d_mel_bytes = 0;
-  float* d_audio = nullptr; size_t d_audio_bytes = 0;
+  void* d_audio = nullptr; size_t d_audio_bytes = 0;   // fp32 audio or 16-bit PCM
   bool force_ffma = false;
   bool need_acc = true, need_sum = false;
 };
@@ -303,13 +303,13 @@ struct Runner {
   // persistent tcgen05 kernel: the whole layer (all phases of a transposed conv) in one launch; x is
   // stored already activated (conv_tc.cu), res is stored activated with slope 1/res_inv
   void conv_tc(const Layer& L, const void* x, int x_rows, void* out, const void* res, float res_inv,
-               const void* res2, float out_scale, float out_slope, float* post_out = nullptr) {
+               const void* res2, float out_scale, float out_slope, float* post_out = nullptr, int16_t* post_pcm = nullptr) {
     if (status != cudaSuccess) return;
     const int u = L.u_k, rows = x_rows / L.fold_in;      // kernel-view rows (time folding, see Layer)
     TcArgs a{};
     a.x = x; a.out = out; a.res = res; a.res2 = res2; a.bias = L.d_bias;
     a.B = B; a.x_rows = rows; a.n_q = rows; a.out_rows = rows * u; a.out_stride = u;
-    a.c_in = L.cin_pad; a.c_out = L.cout_k; a.post_out = post_out; a.post_f = L.post_f;
+    a.c_in = L.cin_pad; a.c_out = L.cout_k; a.post_out = post_out; a.post_pcm = post_pcm; a.post_f = L.post_f;
     a.res_inv = res_inv; a.out_scale = out_scale; a.out_slope = out_slope;
     a.nvar = (int)L.phases.size();
     a.w_base = L.d_wpk; a.w_bytes = L.wpk_bytes;
@@ -372,7 +372,8 @@ struct Runner {
   float slope_of_res = 1.0f;   // slope the residual tensor of the current stage was stored with (1 = raw)
 };
 
-int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev, char* ws, cudaStream_t s) {
+// audio_dev (fp32) or pcm_dev (16-bit PCM, see pcm16_of in kernels.cuh): exactly one is non-NULL
+int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev, int16_t* pcm_dev, char* ws, cudaStream_t s) {
   const hfg_config& c = h->cfg;
   Workspace w;
   workspace_layout(h, B, T, ws, &w);
@@ -445,7 +446,7 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
   // leakyReLU(0.3) -> conv_post -> tanh (model.py:169-171)
   const Layer& post = layer("conv_post");
   if (post.use_tc) {            // x is stored activated with the final slope (see hfg_finalize_weights); w.T is free scratch here
-    r.conv_tc(post, x, L, w.T, nullptr, 1.0f, nullptr, 1.0f, 1.0f, audio_dev);
+    r.conv_tc(post, x, L, w.T, nullptr, 1.0f, nullptr, 1.0f, 1.0f, audio_dev, pcm_dev);
     if (r.status != cudaSuccess) return fail(h, HFG_ERR_CUDA, "conv_post launch failed: %s", cudaGetErrorString(r.status));
     stamp();
     h->n_stage_marks = mark;
@@ -453,7 +454,7 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
     return HFG_OK;
   }
   PostArgs pa{};
-  pa.x = x; pa.w = post.d_w32; pa.out = audio_dev; pa.B = B; pa.rows = L; pa.c_in = post.cin; pa.ntaps = post.k;
+  pa.x = x; pa.w = post.d_w32; pa.out = audio_dev; pa.out_pcm = pcm_dev; pa.B = B; pa.rows = L; pa.c_in = post.cin; pa.ntaps = post.k;
   pa.pad_left = (post.k - 1) / 2; pa.in_slope = x_preact ? 1.0f : kFinalSlope;
   pa.bias = post.b.empty() ? 0.f : post.b[0];
   cudaError_t e = launch_conv_post(pa, h->act, s);
@@ -615,30 +616,42 @@ int hfg_workspace_bytes(hfg_handle h, int B, int T, size_t* out) {
   return HFG_OK;
 }
 
-int hfg_forward(hfg_handle h, const float* mel_dev, int B, int T, float* audio_dev, void* workspace_dev,
-                size_t workspace_bytes, void* stream) {
+static int forward_device(hfg_handle h, const float* mel_dev, int B, int T, float* audio_dev, int16_t* pcm_dev,
+                          void* workspace_dev, size_t workspace_bytes, void* stream, const char* fn) {
   if (!h) return HFG_ERR_INVALID;
-  if (!h->finalized) return fail(h, HFG_ERR_STATE, "hfg_forward: weights not finalised");
+  if (!h->finalized) return fail(h, HFG_ERR_STATE, "%s: weights not finalised", fn);
   if (B < 0 || T < 0) return fail(h, HFG_ERR_INVALID, "negative batch or frame count");
   h->launches = 0;
   if (B == 0 || T == 0) return HFG_OK;                 // empty batch / empty utterances: nothing to synthesise
-  if (!mel_dev || !audio_dev || !workspace_dev) return fail(h, HFG_ERR_INVALID, "hfg_forward: null device pointer");
-  if ((uintptr_t)mel_dev % 16 || (uintptr_t)audio_dev % 4) return fail(h, HFG_ERR_INVALID, "mel must be 16-byte aligned");
+  if (!mel_dev || (!audio_dev && !pcm_dev) || !workspace_dev) return fail(h, HFG_ERR_INVALID, "%s: null device pointer", fn);
+  if ((uintptr_t)mel_dev % 16 || (uintptr_t)audio_dev % 4 || (uintptr_t)pcm_dev % 2)
+    return fail(h, HFG_ERR_INVALID, "mel must be 16-byte aligned, the output naturally aligned");
   char* ws = (char*)align_up((size_t)(uintptr_t)workspace_dev, 256);
   const size_t need = workspace_layout(h, B, T, nullptr, nullptr);
   if ((size_t)(ws - (char*)workspace_dev) + need > workspace_bytes)
     return fail(h, HFG_ERR_NOMEM, "workspace too small: need %zu bytes, got %zu", need + 256, workspace_bytes);
   CUDA_TRY(h, cudaSetDevice(h->device));
-  return run_forward(h, mel_dev, B, T, audio_dev, ws, (cudaStream_t)stream);
+  return run_forward(h, mel_dev, B, T, audio_dev, pcm_dev, ws, (cudaStream_t)stream);
 }
 
-int hfg_forward_host(hfg_handle h, const float* mel_host, int B, int T, float* audio_host) {
+int hfg_forward(hfg_handle h, const float* mel_dev, int B, int T, float* audio_dev, void* workspace_dev,
+                size_t workspace_bytes, void* stream) {
+  return forward_device(h, mel_dev, B, T, audio_dev, nullptr, workspace_dev, workspace_bytes, stream, "hfg_forward");
+}
+
+int hfg_forward_pcm16(hfg_handle h, const float* mel_dev, int B, int T, int16_t* pcm_dev, void* workspace_dev,
+                      size_t workspace_bytes, void* stream) {
+  return forward_device(h, mel_dev, B, T, nullptr, pcm_dev, workspace_dev, workspace_bytes, stream, "hfg_forward_pcm16");
+}
+
+// host-buffer forward; `sample_bytes` = 4 (fp32 audio) or 2 (16-bit PCM)
+static int forward_host(hfg_handle h, const float* mel_host, int B, int T, void* out_host, int sample_bytes, const char* fn) {
   if (!h) return HFG_ERR_INVALID;
-  if (!h->finalized) return fail(h, HFG_ERR_STATE, "hfg_forward_host: weights not finalised");
+  if (!h->finalized) return fail(h, HFG_ERR_STATE, "%s: weights not finalised", fn);
   if (B < 0 || T < 0) return fail(h, HFG_ERR_INVALID, "negative batch or frame count");
   h->launches = 0;
   if (B == 0 || T == 0) return HFG_OK;
-  if (!mel_host || !audio_host) return fail(h, HFG_ERR_INVALID, "hfg_forward_host: null host pointer");
+  if (!mel_host || !out_host) return fail(h, HFG_ERR_INVALID, "%s: null host pointer", fn);
   CUDA_TRY(h, cudaSetDevice(h->device));
   if (!h->stream) CUDA_TRY(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   const int mb = (h->micro_batch <= 0 || h->micro_batch > B) ? B : h->micro_batch;
@@ -656,25 +669,35 @@ int hfg_forward_host(hfg_handle h, const float* mel_host, int B, int T, float* a
     CUDA_TRY(h, cudaMalloc((void**)&h->d_mel, (size_t)B * mel_elems * 4));
     h->d_mel_bytes = (size_t)B * mel_elems * 4;
   }
-  if ((size_t)B * aud_elems * 4 > h->d_audio_bytes) {
+  if ((size_t)B * aud_elems * sample_bytes > h->d_audio_bytes) {
     if (h->d_audio) cudaFree(h->d_audio);
     h->d_audio = nullptr; h->d_audio_bytes = 0;
-    CUDA_TRY(h, cudaMalloc((void**)&h->d_audio, (size_t)B * aud_elems * 4));
-    h->d_audio_bytes = (size_t)B * aud_elems * 4;
+    CUDA_TRY(h, cudaMalloc((void**)&h->d_audio, (size_t)B * aud_elems * sample_bytes));
+    h->d_audio_bytes = (size_t)B * aud_elems * sample_bytes;
   }
   long long launches = 0;
   CUDA_TRY(h, cudaMemcpyAsync(h->d_mel, mel_host, (size_t)B * mel_elems * 4, cudaMemcpyHostToDevice, h->stream));
   for (int b0 = 0; b0 < B; b0 += mb) {
     const int nb = (B - b0 < mb) ? B - b0 : mb;
-    int rc = run_forward(h, h->d_mel + (size_t)b0 * mel_elems, nb, T, h->d_audio + (size_t)b0 * aud_elems, (char*)h->ws, h->stream);
+    char* dev_out = (char*)h->d_audio + (size_t)b0 * aud_elems * sample_bytes;
+    int rc = run_forward(h, h->d_mel + (size_t)b0 * mel_elems, nb, T, sample_bytes == 4 ? (float*)dev_out : nullptr,
+                         sample_bytes == 2 ? (int16_t*)dev_out : nullptr, (char*)h->ws, h->stream);
     launches += h->launches; h->launches = 0;
     if (rc) return rc;
-    CUDA_TRY(h, cudaMemcpyAsync(audio_host + (size_t)b0 * aud_elems, h->d_audio + (size_t)b0 * aud_elems,
-                                (size_t)nb * aud_elems * 4, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(h, cudaMemcpyAsync((char*)out_host + (size_t)b0 * aud_elems * sample_bytes, dev_out,
+                                (size_t)nb * aud_elems * sample_bytes, cudaMemcpyDeviceToHost, h->stream));
   }
   h->launches = launches;
   CUDA_TRY(h, cudaStreamSynchronize(h->stream));
   return HFG_OK;
+}
+
+int hfg_forward_host(hfg_handle h, const float* mel_host, int B, int T, float* audio_host) {
+  return forward_host(h, mel_host, B, T, audio_host, 4, "hfg_forward_host");
+}
+
+int hfg_forward_host_pcm16(hfg_handle h, const float* mel_host, int B, int T, int16_t* pcm_host) {
+  return forward_host(h, mel_host, B, T, pcm_host, 2, "hfg_forward_host_pcm16");
 }
 
 int hfg_set_option(hfg_handle h, const char* key, long long value) {

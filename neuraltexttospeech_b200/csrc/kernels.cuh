@@ -53,9 +53,20 @@ struct PostArgs {
   const float* w;       // fp32 [ntaps][c_in]
   float bias;
   float* out;           // fp32 [B, rows]
+  int16_t* out_pcm;     // when non-NULL: 16-bit PCM [B, rows] instead of `out` (see pcm16_of)
   int B, rows, c_in, ntaps, pad_left;
   float in_slope;
 };
+
+// fp32 waveform sample -> 16-bit PCM, fused into the conv_post epilogue: the step the reference intends after the
+// vocoder, `(audio.clamp(-1, 1) * 32768).astype(int16)` (Grad-TTS_TF/inference.py:89, same pattern in
+// FastSpeech2_TF/FastSpeech2/utils/model.py:82-85): clamp, scale, truncate toward zero; +1.0 saturates to 32767
+// (the numpy cast would wrap it to -32768).
+__host__ __device__ inline int16_t pcm16_of(float v) {
+  v = v < -1.f ? -1.f : (v > 1.f ? 1.f : v);
+  const int i = (int)(v * 32768.f);
+  return (int16_t)(i > 32767 ? 32767 : i);
+}
 
 // fp32 / generic direct kernels (conv_ffma.cu)
 cudaError_t launch_conv_ffma(const ConvArgs& a, ActType act, cudaStream_t s);
@@ -94,6 +105,7 @@ struct TcArgs {
   int post_f;           // conv_post mode: samples per row (time folding): audio[b, q*post_f + s] = tanh(output channel s)
   float* post_out;      // conv_post mode (may be NULL): fp32 [B, n_q*post_f]; `out` is then only a scratch
                         // buffer of >= B*n_q*c_out 16-bit elements for the (unused) output tensor map
+  int16_t* post_pcm;    // conv_post mode, when non-NULL: 16-bit PCM [B, n_q*post_f] instead of post_out
   const void* w_base;   // allocation holding every variant's packed weights (256-byte aligned; the CTA-pair
   size_t w_bytes;       // configurations read it through one TMA map), and its size (multiple of 256)
 };

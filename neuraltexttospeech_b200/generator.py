@@ -153,6 +153,50 @@ class Generator:
                                               out.ctypes.data_as(C.c_void_p)), self._handle, "hfg_forward_host")
         return out
 
+    # ------------------------------------------------------------------ 16-bit PCM output
+    def synthesize_pcm16(self, x):
+        """mel [B, T, num_mels] fp32 -> int16 PCM [B, T*prod(rates)]: `(audio.clamp(-1, 1) * 32768).astype(int16)`
+        (the step the reference intends after the vocoder, Grad-TTS_TF/inference.py:89), fused into the conv_post
+        epilogue on the GPU; +1.0 saturates to 32767.  numpy in -> numpy out, torch CUDA in -> torch CUDA out."""
+        if not self._weights_loaded:
+            raise RuntimeError("weights not loaded: call load_weights() or init_random() first")
+        if torch is not None and isinstance(x, torch.Tensor) and x.is_cuda:
+            mel = x.float().contiguous()
+            self._check_shape(mel.shape)
+            if mel.device.index != self.device:
+                raise ValueError(f"mel is on cuda:{mel.device.index}, generator on cuda:{self.device}")
+            B, T = int(mel.shape[0]), int(mel.shape[1])
+            out = torch.empty((B, T * self._total_up), dtype=torch.int16, device=mel.device)
+            if B == 0 or T == 0:
+                return out
+            ws = self._workspace(B, T, mel.device)
+            stream = torch.cuda.current_stream(mel.device).cuda_stream
+            _lib.check(self._lib.hfg_forward_pcm16(self._handle, C.c_void_p(mel.data_ptr()), B, T, C.c_void_p(out.data_ptr()),
+                                                   C.c_void_p(ws.data_ptr()), ws.numel(), C.c_void_p(stream)),
+                       self._handle, "hfg_forward_pcm16")
+            return out
+        as_torch = torch is not None and isinstance(x, torch.Tensor)
+        mel = x.detach().numpy() if as_torch else np.asarray(x)
+        self._check_shape(mel.shape)
+        mel = np.ascontiguousarray(mel, dtype=np.float32)
+        B, T = int(mel.shape[0]), int(mel.shape[1])
+        out = np.empty((B, T * self._total_up), dtype=np.int16)
+        _lib.check(self._lib.hfg_forward_host_pcm16(self._handle, mel.ctypes.data_as(C.c_void_p), B, T,
+                                                    out.ctypes.data_as(C.c_void_p)), self._handle, "hfg_forward_host_pcm16")
+        return torch.from_numpy(out) if as_torch else out
+
+    def forward_host_pcm16_ptr(self, mel_ptr: int, B: int, T: int, pcm_ptr: int) -> None:
+        """Raw host-pointer entry of the PCM path (pinned buffers)."""
+        _lib.check(self._lib.hfg_forward_host_pcm16(self._handle, C.c_void_p(mel_ptr), B, T, C.c_void_p(pcm_ptr)),
+                   self._handle, "hfg_forward_host_pcm16")
+
+    def _workspace(self, B: int, T: int, device):
+        need = self.workspace_bytes(B, T)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = None
+            self._ws = torch.empty(need, dtype=torch.uint8, device=device)
+        return self._ws
+
     def forward_host_ptr(self, mel_ptr: int, B: int, T: int, audio_ptr: int) -> None:
         """Raw host-pointer entry (pinned buffers from hfg_host_alloc / torch pin_memory)."""
         _lib.check(self._lib.hfg_forward_host(self._handle, C.c_void_p(mel_ptr), B, T, C.c_void_p(audio_ptr)),
@@ -175,10 +219,7 @@ class Generator:
             out = torch.empty((B, T * self._total_up, 1), dtype=torch.float32, device=mel.device)
         if B == 0 or T == 0:
             return out
-        need = self.workspace_bytes(B, T)
-        if self._ws is None or self._ws.numel() < need:
-            self._ws = None
-            self._ws = torch.empty(need, dtype=torch.uint8, device=mel.device)
+        self._workspace(B, T, mel.device)
         stream = torch.cuda.current_stream(mel.device).cuda_stream
         _lib.check(self._lib.hfg_forward(self._handle, C.c_void_p(mel.data_ptr()), B, T, C.c_void_p(out.data_ptr()),
                                          C.c_void_p(self._ws.data_ptr()), self._ws.numel(), C.c_void_p(stream)),
