@@ -151,6 +151,36 @@ int hfg_version(void);
 
 void hfg_destroy(hfg_handle h);
 
+/* ---------------------------------------------------------------------------------------------------------
+ * Mel front-end: the step BEFORE the generator, `STFT.mel_spectrogram`
+ * (reference HiFiGAN_TF/common/audio_processing_tf.py:41-104; callers data.py:142,210, gan.py:48-52,147):
+ * tf.signal.stft (periodic Hann, no centre padding) -> power -> HTK mel filterbank -> log(clip(., 1e-5)).
+ * The output layout is the generator's input layout. */
+typedef struct {                 /* mirrors STFT.__init__ (audio_processing_tf.py:47-58) */
+  int32_t fft_length;            /* filter_length (1024); 256, 1024 or 4096                          */
+  int32_t frame_length;          /* 1024; <= fft_length (frames are zero-padded at the end)          */
+  int32_t frame_step;            /* 256                                                              */
+  int32_t n_mel_channels;        /* 80                                                               */
+  int32_t sampling_rate;         /* 22050                                                            */
+  float mel_fmin, mel_fmax;      /* 0, 8000                                                          */
+} hfg_mel_config;
+
+typedef struct hfg_mel_ctx* hfg_mel_handle;
+
+int hfg_mel_create(const hfg_mel_config* cfg, int device, hfg_mel_handle* out);
+
+/* Frames of an n_samples utterance: 1 + (n_samples - frame_length) / frame_step, 0 if shorter than one frame. */
+int hfg_mel_num_frames(hfg_mel_handle h, long long n_samples, int* out);
+
+/* wav_dev: device fp32 [B, n_samples]; mel_dev: device fp32 [B, T, n_mel_channels]; asynchronous on `stream`. */
+int hfg_mel_forward(hfg_mel_handle h, const float* wav_dev, int B, long long n_samples, float* mel_dev, void* stream);
+
+/* Same with HOST buffers (H2D, kernel, D2H, synchronise). */
+int hfg_mel_forward_host(hfg_mel_handle h, const float* wav_host, int B, long long n_samples, float* mel_host);
+
+const char* hfg_mel_last_error(hfg_mel_handle h);
+void hfg_mel_destroy(hfg_mel_handle h);
+
 #ifdef __cplusplus
 }
 #endif

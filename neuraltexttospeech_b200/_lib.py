@@ -34,6 +34,18 @@ class HfgConfig(C.Structure):
     ]
 
 
+class HfgMelConfig(C.Structure):
+    _fields_ = [
+        ("fft_length", C.c_int32),
+        ("frame_length", C.c_int32),
+        ("frame_step", C.c_int32),
+        ("n_mel_channels", C.c_int32),
+        ("sampling_rate", C.c_int32),
+        ("mel_fmin", C.c_float),
+        ("mel_fmax", C.c_float),
+    ]
+
+
 # every symbol include/hifigan_b200.h declares: name -> (restype, argtypes)
 SIGNATURES = {
     "hfg_version": (C.c_int, []),
@@ -57,6 +69,12 @@ SIGNATURES = {
     "hfg_host_free": (C.c_int, [C.c_void_p]),
     "hfg_last_error": (C.c_char_p, [C.c_void_p]),
     "hfg_destroy": (None, [C.c_void_p]),
+    "hfg_mel_create": (C.c_int, [C.POINTER(HfgMelConfig), C.c_int, C.POINTER(C.c_void_p)]),
+    "hfg_mel_num_frames": (C.c_int, [C.c_void_p, C.c_longlong, C.POINTER(C.c_int)]),
+    "hfg_mel_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_longlong, C.c_void_p, C.c_void_p]),
+    "hfg_mel_forward_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_longlong, C.c_void_p]),
+    "hfg_mel_last_error": (C.c_char_p, [C.c_void_p]),
+    "hfg_mel_destroy": (None, [C.c_void_p]),
 }
 
 _lib = None
@@ -85,10 +103,14 @@ def last_error(handle=None) -> str:
     return msg.decode() if msg else ""
 
 
-def check(rc: int, handle=None, what: str = ""):
+def check(rc: int, handle=None, what: str = "", mel: bool = False):
     if rc == 0:
         return
-    msg = last_error(handle) or f"error {rc}"
+    if mel:
+        m = load().hfg_mel_last_error(handle)
+        msg = (m.decode() if m else "") or f"error {rc}"
+    else:
+        msg = last_error(handle) or f"error {rc}"
     if what:
         msg = f"{what}: {msg}"
     if rc in (HFG_ERR_INVALID, HFG_ERR_UNSUPPORTED):

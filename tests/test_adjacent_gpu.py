@@ -48,3 +48,70 @@ def test_pcm16_saturates_and_device_path_matches_host_path():
     assert (dev.cpu().numpy() == host).all()
     assert g.synthesize_pcm16(np.zeros((0, 8, 80), np.float32)).shape == (0, 8 * 256)
     g.close()
+
+
+def _speechlike(B, N, seed=0):
+    rng = np.random.default_rng(seed)
+    t = np.arange(N)[None, :] / 22050.0
+    f0 = rng.uniform(90, 250, size=(B, 1))
+    x = sum(rng.uniform(0.02, 0.3, size=(B, 1)) * np.sin(2 * np.pi * f0 * h * t + rng.uniform(0, 6.28, size=(B, 1))) for h in range(1, 30))
+    x = x / np.abs(x).max() * 0.8 + 0.01 * rng.standard_normal((B, N))
+    return x.astype(np.float32)
+
+
+@pytest.mark.parametrize("B,N", [(1, 1024), (3, 1024 + 256 * 6), (2, 22050), (1, 1024 + 255)])
+def test_mel_frontend_matches_oracle(B, N):
+    from neuraltexttospeech_b200 import STFT
+    wav = _speechlike(B, N)
+    fe = STFT()
+    mel = fe.mel_spectrogram(wav)
+    ref = A.mel_spectrogram(wav.astype(np.float64))
+    if B == 1:
+        ref = ref[0]
+    assert mel.shape == ref.shape and mel.dtype == np.float32
+    # fp32 FFT vs the fp64 oracle, compared in the log domain the generator consumes
+    assert np.abs(mel - ref).max() <= 2e-3
+    assert np.abs(mel - ref).mean() <= 2e-5
+    fe.close()
+
+
+def test_mel_frontend_edge_cases_and_device_path():
+    import torch
+    from neuraltexttospeech_b200 import STFT
+    fe = STFT()
+    assert fe.mel_spectrogram(np.zeros(1000, np.float32)).shape == (0, 80)          # shorter than one frame
+    assert fe.mel_spectrogram(np.zeros((0, 4096), np.float32)).shape == (0, 13, 80)  # empty batch
+    sil = fe.mel_spectrogram(np.zeros(4096, np.float32))
+    assert np.allclose(sil, np.log(1e-5))                                           # silence sits on the 1e-5 floor
+    wav = _speechlike(2, 8192, seed=3)
+    host = fe.mel_spectrogram(wav)
+    dev = fe.mel_spectrogram(torch.from_numpy(wav).cuda())
+    assert dev.is_cuda and (dev.cpu().numpy() == host).all()
+    with pytest.raises(ValueError):
+        STFT(filter_length=1000)
+    # other supported FFT sizes, frame shorter than the FFT (zero-padded at the end like tf.signal.stft)
+    for nfft, fl, st in ((256, 200, 64), (4096, 4096, 1024)):
+        f2 = STFT(filter_length=nfft, frame_length=fl, frame_step=st)
+        m = f2.mel_spectrogram(wav)
+        r = A.mel_spectrogram(wav.astype(np.float64), frame_length=fl, frame_step=st, fft_length=nfft)
+        assert m.shape == r.shape and np.abs(m - r).max() <= 2e-3
+        f2.close()
+    fe.close()
+
+
+def test_wav_to_mel_to_wav_round_trip_runs_on_device():
+    """Front-end output feeds the generator directly (same layout); PCM comes back as int16."""
+    import torch
+    from neuraltexttospeech_b200 import STFT
+    h = HParams.builtin("3")
+    g = Generator(h, precision="fp16").load_weights(synthetic_weights(h, "A"))
+    fe = STFT()
+    wav = torch.from_numpy(_speechlike(2, 1024 + 256 * 15)).cuda()
+    mel = fe.mel_spectrogram(wav)
+    assert mel.shape == (2, 16, 80)
+    audio = g(mel)
+    pcm = g.synthesize_pcm16(mel)
+    assert audio.shape == (2, 16 * 256, 1) and pcm.shape == (2, 16 * 256)
+    ref = O.generator_forward(h, synthetic_weights(h, "A"), mel.cpu().numpy(), "torch32")
+    assert np.abs(audio.cpu().numpy() - ref).max() <= 2e-3
+    g.close(); fe.close()
