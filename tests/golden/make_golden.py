@@ -36,8 +36,8 @@ from oracle import hifigan_oracle as O                          # noqa: E402
 REF = "/root/reference"
 
 
-def _upstream_generator(h):
-    """Build the vendored upstream torch generator with weight norm removed."""
+def _upstream_generator(h, keep_weight_norm=False):
+    """Build the vendored upstream torch generator (weight norm removed unless keep_weight_norm)."""
     import torch
     if h.resblock == "1":
         sys.path.insert(0, os.path.join(REF, "FastSpeech2_TF/FastSpeech2"))
@@ -74,7 +74,8 @@ def _upstream_generator(h):
             for rb in group:                 # but never assigns it; give it the module constant
                 if not hasattr(rb, "lrelu_slope"):
                     rb.lrelu_slope = mod.LRELU_SLOPE
-    gen.remove_weight_norm()
+    if not keep_weight_norm:
+        gen.remove_weight_norm()
     return gen.eval()
 
 
