@@ -157,6 +157,7 @@ def main():
     ap.add_argument("--micro-batch", type=int, default=32)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-adjacent", action="store_true", help="skip the PCM16 / mel front-end side measurements")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -233,6 +234,7 @@ def main():
 
     # ---------------- end-to-end through Generator.call on pinned host buffers ("e2e")
     e2e = None
+    adjacent = {}
     if not args.no_e2e:
         mel_pin = torch.from_numpy(mel_np).pin_memory()
         out_pin = torch.empty((B, L, 1), dtype=torch.float32).pin_memory()
@@ -249,6 +251,41 @@ def main():
         e2e = {"value": world * audio_s_per_step / (e2e_ms / 1000), "unit": "audio-s/s",
                "h2d_bytes_per_step": int(mel_np.nbytes), "d2h_bytes_per_step": int(out_pin.numel() * 4),
                "ms_per_step": e2e_ms, "api": "Generator.call(numpy) -> hfg_forward_host"}
+        # same call with the 16-bit PCM epilogue: half the D2H bytes
+        pcm_pin = torch.empty((B, L), dtype=torch.int16).pin_memory()
+        for _ in range(2):
+            gen.forward_host_pcm16_ptr(mel_pin.data_ptr(), B, T, pcm_pin.data_ptr())
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            gen.forward_host_pcm16_ptr(mel_pin.data_ptr(), B, T, pcm_pin.data_ptr())
+        barrier()
+        pcm_ms = max_over_ranks((time.perf_counter() - t0) * 1000) / args.steps
+        adjacent["e2e_pcm16"] = {"value": world * audio_s_per_step / (pcm_ms / 1000), "unit": "audio-s/s", "ms_per_step": pcm_ms,
+                                 "h2d_bytes_per_step": int(mel_np.nbytes), "d2h_bytes_per_step": int(pcm_pin.numel() * 2),
+                                 "api": "Generator.synthesize_pcm16 -> hfg_forward_host_pcm16"}
+    # mel front-end kernel on the waveforms this step produced: HBM-bound, bytes = wav in + mel out
+    if not args.no_adjacent:
+        from neuraltexttospeech_b200 import STFT
+        fe = STFT(device=local_rank)
+        wav = out_dev.view(B, L)
+        Tm = fe.num_frames(L)
+        for _ in range(3):
+            fe.mel_spectrogram(wav)
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        f0.record(stream)
+        for _ in range(10):
+            fe.mel_spectrogram(wav)
+        f1.record(stream)
+        torch.cuda.synchronize()
+        fe_ms = f0.elapsed_time(f1) / 10
+        fe_bytes = B * L * 4 + B * Tm * 80 * 4
+        adjacent["mel_frontend"] = {"ms": fe_ms, "utterances": B, "frames": Tm, "audio_s_per_s": audio_s_per_step / (fe_ms / 1000),
+                                    "bound": "hbm", "achieved_gbs": fe_bytes / (fe_ms * 1e-3) / 1e9, "peak_gbs": peaks()["hbm_gbs"],
+                                    "frac": fe_bytes / (fe_ms * 1e-3) / 1e9 / peaks()["hbm_gbs"],
+                                    "note": "wav [B, L] fp32 resident in HBM (one step's output, L2-sized per utterance) -> log-mel [B, T, 80]"}
+        fe.close()
 
     if rank == 0:
         pk = peaks()
@@ -297,6 +334,7 @@ def main():
                               "algorithmic_flops_per_step": flops, "layer_boundary_bytes_per_step": bytes_boundary,
                               "hbm_floor_ms": bytes_boundary / bw * 1000, "tensor_floor_ms": flops / p_tensor * 1000},
             "stages": {"batch": mb, "rows": stages},
+            "adjacent": adjacent,
         }
         if not args.no_cpu_baseline and world == 1:
             # CPU baseline on rank 0: BASELINE.json configs[0] (V1, batch 1, 256 frames), oracle port

@@ -167,8 +167,12 @@ __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
+// Remote arrive on the leader's barrier.  Default semantics (.release.cta): what travels through this barrier is the
+// completion of tcgen05.ld (ordered by tcgen05.fence::before_thread_sync), not generic-proxy data, so no cluster-scope
+// release is needed -- `.release.cluster` compiled to MEMBAR.ALL.GPU + ERRBAR per warp per tile, which was 20 % of all
+// stall samples and the per-tile critical path of the C <= 64 pair layers (profiles/r1j).
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cl) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cl) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar_cl) : "memory");
 }
 __device__ __forceinline__ void tma_load_3d_2cta(void* dst_smem, const CUtensorMap* tm, int c0, int c1, int c2, uint32_t bar_cl) {
   asm volatile("cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
@@ -285,6 +289,7 @@ struct TcKArgs {
   float* post_out;                     // conv_post mode: audio[b, q*post_f + s] = tanh(channel s) written as fp32, no 16-bit tile
   int post_f;
   int16_t* post_pcm;                   // conv_post mode: 16-bit PCM output instead of post_out (pcm16_of)
+  int nsl, nstg;                       // ring depths actually used (>= the table's NSL / NSTG when shared memory allows)
 };
 
 // ------------------------------------------------------------------ the kernel
@@ -313,7 +318,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
   static_assert(CG == 1 || BLK_BYTES % 256 == 0, "pair weight blocks are whole 256-byte rows of tm_w");
   static_assert(KS == 64 || KS == 32 || KS == 16, "K-slice = one swizzle row");
   static_assert(N % PW == 0, "pass width");
-  const TcSmemPlan pl = tc_plan(N, KS, KBW * TPS, NST, NSL, NSTG, ka.nbox * ka.box_rows, CG);
+  const int nsl = ka.nsl, nstg = ka.nstg;          // runtime ring depths (the template values are the table defaults)
+  const TcSmemPlan pl = tc_plan(N, KS, KBW * TPS, NST, nsl, nstg, ka.nbox * ka.box_rows, CG);
 
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* slab = smem;
@@ -321,13 +327,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
   uint8_t* wst = smem + pl.off_w;
   float* bias_s = reinterpret_cast<float*>(smem + pl.off_bias);
   uint64_t* slice_full = reinterpret_cast<uint64_t*>(smem + pl.off_bar);
-  uint64_t* slice_empty = slice_full + NSL;
-  uint64_t* w_full = slice_empty + NSL;
+  uint64_t* slice_empty = slice_full + nsl;
+  uint64_t* w_full = slice_empty + nsl;
   uint64_t* w_empty = w_full + NST;
   uint64_t* stg_full = w_empty + NST;
-  uint64_t* stg_empty = stg_full + NSTG;
-  uint64_t* stg_done = stg_empty + NSTG;
-  uint64_t* acc_full = stg_done + NSTG;
+  uint64_t* stg_empty = stg_full + nstg;
+  uint64_t* stg_done = stg_empty + nstg;
+  uint64_t* acc_full = stg_done + nstg;
   uint64_t* acc_empty = acc_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
 
@@ -336,9 +342,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
   const int tile0 = blockIdx.x / CG, tile_step = gridDim.x / CG;
 
   if (tid == 0) {
-    for (int s = 0; s < NSL; ++s) { mbar_init(&slice_full[s], 1); mbar_init(&slice_empty[s], 1); }
+    for (int s = 0; s < nsl; ++s) { mbar_init(&slice_full[s], 1); mbar_init(&slice_empty[s], 1); }
     for (int s = 0; s < NST; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
-    for (int s = 0; s < NSTG; ++s) { mbar_init(&stg_full[s], 1); mbar_init(&stg_empty[s], 1); mbar_init(&stg_done[s], 4); }
+    for (int s = 0; s < nstg; ++s) { mbar_init(&stg_full[s], 1); mbar_init(&stg_empty[s], 1); mbar_init(&stg_done[s], 4); }
     for (int s = 0; s < 2; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 8 * CG); }
     fence_mbar_init();
     tma_prefetch_desc(&tm_x); tma_prefetch_desc(&tm_res); tma_prefetch_desc(&tm_out);
@@ -369,8 +375,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
       int b, qt, v, nt; decode(t, b, qt, v, nt);
       const int row_base = qt * (MB * 128) + ka.min_off;
       for (int s = 0; s < NKS; ++s, ++scnt) {
-        const int pos = scnt % NSL;
-        mbar_wait(&slice_empty[pos], ((scnt / NSL) & 1) ^ 1);
+        const int pos = scnt % (uint32_t)nsl;
+        mbar_wait(&slice_empty[pos], ((scnt / (uint32_t)nsl) & 1) ^ 1);
         if (elect_one()) {
           uint8_t* dst = slab + pos * pl.slice_bytes;
           if (CG == 1) {
@@ -440,8 +446,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
       if (ka.resident) wcnt = 0;
 #pragma unroll 1
       for (int s = 0; s < NKS; ++s, ++scnt) {
-        const int pos = scnt % NSL;
-        mbar_wait(&slice_full[pos], (scnt / NSL) & 1);
+        const int pos = scnt % (uint32_t)nsl;
+        mbar_wait(&slice_full[pos], (scnt / (uint32_t)nsl) & 1);
         tc_fence_after();
         const uint32_t sl = slab_addr + pos * pl.slice_bytes;
 #pragma unroll 1
@@ -495,8 +501,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
       for (int mb = 0; mb < MB; ++mb) {
         const int q0 = qt * (MB * 128) + mb * 128;
         for (int p0 = 0; p0 < N; p0 += PW, ++pcnt) {
-          const int buf = pcnt % NSTG;
-          mbar_wait(&stg_empty[buf], ((pcnt / NSTG) & 1) ^ 1);
+          const int buf = pcnt % (uint32_t)nstg;
+          mbar_wait(&stg_empty[buf], ((pcnt / (uint32_t)nstg) & 1) ^ 1);
           if (elect_one()) {
             if (ka.has_res && q0 < ka.n_q) {
               mbar_expect_tx(&stg_full[buf], pl.stg_bytes);
@@ -518,8 +524,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
       for (int mb = 0; mb < MB; ++mb) {
         const int q0 = qt * (MB * 128) + mb * 128;
         for (int p0 = 0; p0 < N; p0 += PW, ++pcnt) {
-          const int buf = pcnt % NSTG;
-          mbar_wait(&stg_done[buf], (pcnt / NSTG) & 1);
+          const int buf = pcnt % (uint32_t)nstg;
+          mbar_wait(&stg_done[buf], (pcnt / (uint32_t)nstg) & 1);
           if (elect_one()) {
             if (q0 < ka.n_q && ka.post_out == nullptr && ka.post_pcm == nullptr) {
               tma_store_4d(&tm_out, stg + buf * pl.stg_bytes, nt * N + p0, out_off, q0, b);
@@ -560,9 +566,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
 #pragma unroll 1
         for (int p0 = 0; p0 < N; p0 += PW, ++pcnt) {
           if ((int)(pcnt & 1) != grp) continue;
-          const int buf = pcnt % NSTG;
+          const int buf = pcnt % (uint32_t)nstg;
           uint8_t* my = stg + buf * pl.stg_bytes + er * SROWB;
-          mbar_wait(&stg_full[buf], (pcnt / NSTG) & 1);   // residual tile landed / buffer granted
+          mbar_wait(&stg_full[buf], (pcnt / (uint32_t)nstg) & 1);   // residual tile landed / buffer granted
 #pragma unroll
           for (int c0 = 0; c0 < PW; c0 += CW) {
             uint32_t r[32];
@@ -704,7 +710,8 @@ bool make_map4(CUtensorMap* m, ActType act, const void* base, int C, int u, int 
 // slab slice = nbox boxes of box_rows rows covering MB*128 + span rows with little waste
 void tc_boxes(int rows, int* box_rows, int* nbox) {
   int best_br = 256, best_pad = 1 << 30;
-  for (int br = 256; br >= 8; br >>= 1) {            // fewest padded rows with at most 24 boxes; ties -> larger box
+  static const int min_br = []() { const char* e = getenv("HFG_TC_MINBOX"); const int v = e ? atoi(e) : 8; return v < 8 ? 8 : v; }();
+  for (int br = 256; br >= min_br; br >>= 1) {       // fewest padded rows with at most 24 boxes; ties -> larger box
     const int nb = (rows + br - 1) / br;
     if (nb > 24) break;
     if (nb * br < best_pad) { best_pad = nb * br; best_br = br; }
@@ -724,6 +731,27 @@ bool make_map_w(CUtensorMap* m, const void* base, size_t bytes, int box_rows) {
             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+int tc_env_int(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
+
+// Ring depths of a launch.  The table's (NSL, NSTG) always fit.  Layers whose weights stay resident in shared memory
+// (C <= 64: the HBM-bound layers) have per-tile MMA time far below the latency of one slab load, so with the table's
+// two slab slots only ONE load is in flight per SM while the other slot is consumed: their depth is raised as far as
+// shared memory allows (Little's law: ~80 KB in flight per SM saturate HBM), trading staging slots above 3 for slab slots.
+void tc_ring_depths(int n, int ks, int kbw_tps, int nst, int nsl0, int nstg0, int slice_rows, int cg, bool resident, int* nsl, int* nstg) {
+  *nsl = nsl0; *nstg = nstg0;
+  static const int want_nsl = tc_env_int("HFG_TC_NSL", 4), min_nstg = tc_env_int("HFG_TC_NSTG_MIN", 3);
+  if (!resident || want_nsl <= nsl0) return;
+  auto fits = [&](int a, int b) { return (size_t)tc_plan(n, ks, kbw_tps, nst, a, b, slice_rows, cg).total <= kTcMaxSmem; };
+  int a = nsl0, b = nstg0;
+  while (a < want_nsl) {
+    if (fits(a + 1, b)) { ++a; continue; }
+    if (b > min_nstg) { --b; continue; }
+    break;
+  }
+  while (!fits(a, b) && a > nsl0) --a;        // (cannot happen: every accepted step fits)
+  if (fits(a, b)) { *nsl = a; *nstg = b; }
+}
+
 template <typename T, int C_IN, int N, int MB, int KS, int KBW, int TPS, int NST, int NSL, int NSTG, int CG>
 cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out) {
   constexpr int PW = N < 64 ? N : 64;
@@ -739,7 +767,14 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
   if (ka.span > kTcMaxSpan) return cudaErrorInvalidValue;
   if ((a.res || a.res2) && a.out_stride != 1) return cudaErrorInvalidValue;
   tc_boxes(MB * 128 + ka.span, &ka.box_rows, &ka.nbox);
-  const TcSmemPlan pl = tc_plan(N, KS, KBW * TPS, NST, NSL, NSTG, ka.nbox * ka.box_rows, CG);
+  {
+    int max_taps = 0;
+    for (int v = 0; v < a.nvar; ++v) max_taps = a.var[v].ntaps > max_taps ? a.var[v].ntaps : max_taps;
+    const int stages = (C_IN / KS) * ((max_taps + TPS - 1) / TPS) * (KS / KBW);
+    ka.resident = (a.nvar == 1 && a.c_out == N && stages <= NST) ? 1 : 0;
+  }
+  tc_ring_depths(N, KS, KBW * TPS, NST, NSL, NSTG, ka.nbox * ka.box_rows, CG, ka.resident != 0, &ka.nsl, &ka.nstg);
+  const TcSmemPlan pl = tc_plan(N, KS, KBW * TPS, NST, ka.nsl, ka.nstg, ka.nbox * ka.box_rows, CG);
   if ((size_t)pl.total > kTcMaxSmem) return cudaErrorInvalidConfiguration;
   ka.tiles_q = (a.n_q + CG * MB * 128 - 1) / (CG * MB * 128);
   ka.w_base = a.w_base;
@@ -747,12 +782,6 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
   const bool post_mode = a.post_out || a.post_pcm;
   if (post_mode && (a.post_f < 1 || a.post_f > 16)) return cudaErrorInvalidValue;
   if (post_mode && (a.out_stride != 1 || a.res || a.res2)) return cudaErrorInvalidValue;
-  {
-    int max_taps = 0;
-    for (int v = 0; v < a.nvar; ++v) max_taps = a.var[v].ntaps > max_taps ? a.var[v].ntaps : max_taps;
-    const int stages = (C_IN / KS) * ((max_taps + TPS - 1) / TPS) * (KS / KBW);
-    ka.resident = (a.nvar == 1 && a.c_out == N && stages <= NST) ? 1 : 0;
-  }
   ka.n_tiles = a.c_out / N;
   ka.total_tiles = a.B * ka.tiles_q * a.nvar * ka.n_tiles;
   CUtensorMap tm_x, tm_res, tm_out, tm_w;

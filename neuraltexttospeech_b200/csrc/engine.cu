@@ -77,6 +77,8 @@ struct hfg_ctx {
   // host-buffer path
   int micro_batch = 32;
   cudaStream_t stream = nullptr;
+  cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;   // host path: copies overlap the forward of the neighbouring micro-batch
+  std::vector<cudaEvent_t> copy_events;                      // 2 per micro-batch (mel landed, audio ready)
   void* ws = nullptr; size_t ws_bytes = 0;
   float* d_mel = nullptr; size_t d_mel_bytes = 0;
   void* d_audio = nullptr; size_t d_audio_bytes = 0;   // fp32 audio or 16-bit PCM
@@ -675,19 +677,38 @@ static int forward_host(hfg_handle h, const float* mel_host, int B, int T, void*
     CUDA_TRY(h, cudaMalloc((void**)&h->d_audio, (size_t)B * aud_elems * sample_bytes));
     h->d_audio_bytes = (size_t)B * aud_elems * sample_bytes;
   }
+  // Three streams: the mels of micro-batch i+1 go up and the waveforms of micro-batch i-1 come down while micro-batch i
+  // computes; only the first H2D and the last D2H are exposed.
+  if (!h->h2d_stream) CUDA_TRY(h, cudaStreamCreateWithFlags(&h->h2d_stream, cudaStreamNonBlocking));
+  if (!h->d2h_stream) CUDA_TRY(h, cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking));
+  const int n_mb = (B + mb - 1) / mb;
+  while ((int)h->copy_events.size() < 2 * n_mb) {
+    cudaEvent_t ev;
+    CUDA_TRY(h, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    h->copy_events.push_back(ev);
+  }
   long long launches = 0;
-  CUDA_TRY(h, cudaMemcpyAsync(h->d_mel, mel_host, (size_t)B * mel_elems * 4, cudaMemcpyHostToDevice, h->stream));
-  for (int b0 = 0; b0 < B; b0 += mb) {
+  for (int i = 0, b0 = 0; b0 < B; b0 += mb, ++i) {
+    const int nb = (B - b0 < mb) ? B - b0 : mb;
+    CUDA_TRY(h, cudaMemcpyAsync(h->d_mel + (size_t)b0 * mel_elems, mel_host + (size_t)b0 * mel_elems, (size_t)nb * mel_elems * 4,
+                                cudaMemcpyHostToDevice, h->h2d_stream));
+    CUDA_TRY(h, cudaEventRecord(h->copy_events[2 * i], h->h2d_stream));
+  }
+  for (int i = 0, b0 = 0; b0 < B; b0 += mb, ++i) {
     const int nb = (B - b0 < mb) ? B - b0 : mb;
     char* dev_out = (char*)h->d_audio + (size_t)b0 * aud_elems * sample_bytes;
+    CUDA_TRY(h, cudaStreamWaitEvent(h->stream, h->copy_events[2 * i], 0));
     int rc = run_forward(h, h->d_mel + (size_t)b0 * mel_elems, nb, T, sample_bytes == 4 ? (float*)dev_out : nullptr,
                          sample_bytes == 2 ? (int16_t*)dev_out : nullptr, (char*)h->ws, h->stream);
     launches += h->launches; h->launches = 0;
-    if (rc) return rc;
+    if (rc) { cudaStreamSynchronize(h->h2d_stream); cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->d2h_stream); return rc; }
+    CUDA_TRY(h, cudaEventRecord(h->copy_events[2 * i + 1], h->stream));
+    CUDA_TRY(h, cudaStreamWaitEvent(h->d2h_stream, h->copy_events[2 * i + 1], 0));
     CUDA_TRY(h, cudaMemcpyAsync((char*)out_host + (size_t)b0 * aud_elems * sample_bytes, dev_out,
-                                (size_t)nb * aud_elems * sample_bytes, cudaMemcpyDeviceToHost, h->stream));
+                                (size_t)nb * aud_elems * sample_bytes, cudaMemcpyDeviceToHost, h->d2h_stream));
   }
   h->launches = launches;
+  CUDA_TRY(h, cudaStreamSynchronize(h->d2h_stream));
   CUDA_TRY(h, cudaStreamSynchronize(h->stream));
   return HFG_OK;
 }
@@ -830,6 +851,9 @@ void hfg_destroy(hfg_handle h) {
   if (h->d_mel) cudaFree(h->d_mel);
   if (h->d_audio) cudaFree(h->d_audio);
   if (h->stream) cudaStreamDestroy(h->stream);
+  if (h->h2d_stream) cudaStreamDestroy(h->h2d_stream);
+  if (h->d2h_stream) cudaStreamDestroy(h->d2h_stream);
+  for (auto& ev : h->copy_events) cudaEventDestroy(ev);
   delete h;
 }
 
