@@ -154,7 +154,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="v1_b64x10s", choices=sorted(CONFIGS))
     ap.add_argument("--precision", default="fp16", choices=["fp32", "fp16", "bf16"])
-    ap.add_argument("--micro-batch", type=int, default=32)
+    ap.add_argument("--micro-batch", type=int, default=0, help="utterances per forward; 0 = the library's own rule")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-adjacent", action="store_true", help="skip the PCM16 / mel front-end side measurements")
@@ -204,7 +204,8 @@ def main():
     # ---------------- device-resident measurement ("value")
     mel_dev = torch.from_numpy(mel_np).cuda()
     out_dev = torch.empty((B, L, 1), dtype=torch.float32, device="cuda")
-    mb = max(1, min(args.micro_batch, B))    # utterances per forward call: keeps the workspace modest
+    # utterances per forward call (hfg_auto_micro_batch: one activation buffer <= 1 GiB)
+    mb = max(1, min(args.micro_batch, B)) if args.micro_batch > 0 else gen.auto_micro_batch(B, T)
     stream = torch.cuda.current_stream()
 
     def step_device():
@@ -239,7 +240,8 @@ def main():
         mel_pin = torch.from_numpy(mel_np).pin_memory()
         out_pin = torch.empty((B, L, 1), dtype=torch.float32).pin_memory()
         mel_h, out_h = mel_pin.numpy(), out_pin.numpy()
-        gen.set_option("micro_batch", mb)
+        gen.set_option("micro_batch", args.micro_batch if args.micro_batch > 0 else 0)   # 0: two micro-batches, copies overlap compute
+        mb_host = args.micro_batch if args.micro_batch > 0 else gen.auto_micro_batch(B, T, host_path=True)
         for _ in range(2):
             gen._call_host(mel_h, out_h)
         barrier()
@@ -250,7 +252,7 @@ def main():
         e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1000) / args.steps
         e2e = {"value": world * audio_s_per_step / (e2e_ms / 1000), "unit": "audio-s/s",
                "h2d_bytes_per_step": int(mel_np.nbytes), "d2h_bytes_per_step": int(out_pin.numel() * 4),
-               "ms_per_step": e2e_ms, "api": "Generator.call(numpy) -> hfg_forward_host"}
+               "ms_per_step": e2e_ms, "micro_batch": mb_host, "api": "Generator.call(numpy) -> hfg_forward_host"}
         # same call with the 16-bit PCM epilogue: half the D2H bytes
         pcm_pin = torch.empty((B, L), dtype=torch.int16).pin_memory()
         for _ in range(2):

@@ -107,12 +107,21 @@ int hfg_forward_pcm16(hfg_handle h, const float* mel_dev, int B, int T, int16_t*
                       void* workspace_dev, size_t workspace_bytes, void* stream);
 int hfg_forward_host_pcm16(hfg_handle h, const float* mel_host, int B, int T, int16_t* pcm_host);
 
-/* Utterances per micro-batch used by hfg_forward_host (default 32); 0 = whole batch. */
+/* Options: "micro_batch" = utterances per forward of hfg_forward_host (0 = auto, the default: hfg_auto_micro_batch);
+ * "stage_timing" 0/1; "force_ffma" 0/1 and "auto_fold" 0/1 (both need a new hfg_finalize_weights). */
 int hfg_set_option(hfg_handle h, const char* key, long long value);
 
 /* Which kernel family each layer was bound to by hfg_finalize_weights: lines "<layer>:<tc|ffma|post>\n"
  * (tc = persistent tcgen05 kernel, ffma = direct fp32-accumulate kernel, post = conv_post+tanh kernel). */
 int hfg_layer_engines(hfg_handle h, char* buf, size_t cap);
+
+/* Utterances per forward the library would pick for a [B, T] batch (one activation buffer <= 1 GiB; the host path keeps
+ * two micro-batches so copies overlap compute).  Callers of hfg_forward that split large batches can use the same rule. */
+int hfg_auto_micro_batch(hfg_handle h, int B, int T, int host_path, int* out);
+
+/* Time-fold factors chosen per layer on the tcgen05 path: lines "<layer>:<fold_in>:<fold_out>:<kernel-view taps>\n"
+ * (a [L, C] tensor is bit-identical to [L/f, C*f]). */
+int hfg_layer_folds(hfg_handle h, char* buf, size_t cap);
 
 /* Kernels launched by the last hfg_forward / hfg_forward_host on this handle. */
 int hfg_last_launch_count(hfg_handle h, long long* out);

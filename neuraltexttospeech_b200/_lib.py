@@ -60,6 +60,8 @@ SIGNATURES = {
     "hfg_forward_host_pcm16": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "hfg_set_option": (C.c_int, [C.c_void_p, C.c_char_p, C.c_longlong]),
     "hfg_layer_engines": (C.c_int, [C.c_void_p, C.c_char_p, C.c_size_t]),
+    "hfg_auto_micro_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]),
+    "hfg_layer_folds": (C.c_int, [C.c_void_p, C.c_char_p, C.c_size_t]),
     "hfg_last_launch_count": (C.c_int, [C.c_void_p, C.POINTER(C.c_longlong)]),
     "hfg_stage_times_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int)]),
     "hfg_op_tapped_conv": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,

@@ -118,7 +118,7 @@ class Generator:
 
     def set_option(self, key: str, value: int) -> None:
         _lib.check(self._lib.hfg_set_option(self._handle, key.encode(), int(value)), self._handle, key)
-        if key == "force_ffma":
+        if key in ("force_ffma", "auto_fold"):
             self._weights_loaded = False
 
     # ------------------------------------------------------------------ forward
@@ -237,6 +237,17 @@ class Generator:
         buf = C.create_string_buffer(1 << 14)
         _lib.check(self._lib.hfg_layer_engines(self._handle, buf, len(buf)), self._handle)
         return dict(line.split(":") for line in buf.value.decode().strip().split("\n"))
+
+    def auto_micro_batch(self, B: int, T: int, host_path: bool = False) -> int:
+        n = C.c_int()
+        _lib.check(self._lib.hfg_auto_micro_batch(self._handle, int(B), int(T), int(host_path), C.byref(n)), self._handle)
+        return int(n.value)
+
+    def layer_folds(self) -> Dict[str, tuple]:
+        """layer name -> (fold_in, fold_out, kernel-view taps) chosen for the tcgen05 kernel."""
+        buf = C.create_string_buffer(1 << 14)
+        _lib.check(self._lib.hfg_layer_folds(self._handle, buf, len(buf)), self._handle)
+        return {p[0]: tuple(int(v) for v in p[1:]) for p in (line.split(":") for line in buf.value.decode().strip().split("\n"))}
 
     def stage_times_ms(self):
         buf = (C.c_float * 16)()

@@ -166,3 +166,34 @@ def test_tensor_core_path_covers_every_conv(v, gens):
     assert set(eng.values()) == {"tc"}, {k: e for k, e in eng.items() if e != "tc"}
     eng32 = gens(v, "fp32").layer_engines()
     assert "tc" not in set(eng32.values()) and eng32["conv_post"] == "post"
+
+
+def test_auto_fold_picks_wider_tiles_for_narrow_d1_convs_and_keeps_parity():
+    """Per-layer time folding: same tensors, block-Toeplitz weights; results stay within the
+    tensor-core tolerance of the oracle with the choice on or off."""
+    h = HParams.builtin("2")
+    w = synthetic_weights(h, "B")
+    mel = synthetic_mel(2, 21, h.num_mels)
+    ref = O.generator_forward(h, w, mel, "torch32")
+    g = Generator(h, precision="fp16").load_weights(w)
+    folds = g.layer_folds()
+    assert folds["resblocks.11.convs2.0"][0] == 8 and folds["resblocks.8.convs2.0"][0] == 4     # C=8 / C=16, k=11, d=1
+    assert folds["resblocks.0.convs1.0"][0] == 1                                               # C=64 stays unfolded
+    assert all(e == "tc" for e in g.layer_engines().values())
+    on = g(mel)
+    g.set_option("auto_fold", 0)
+    g.load_weights(w)
+    assert max(f[0] for f in g.layer_folds().values()) == 2                                    # only the C=8 -> 16 minimum fold
+    off = g(mel)
+    for out in (on, off):
+        assert np.abs(out - ref).max() <= TC_TOL and snr_db(ref, out) >= TC_SNR
+    g.close()
+
+
+def test_auto_micro_batch_rule():
+    h = HParams.builtin("1")
+    g = Generator(h, precision="fp16").load_weights(synthetic_weights(h, "A"))
+    assert g.auto_micro_batch(64, 862) == 64 and g.auto_micro_batch(512, 862) == 76
+    assert g.auto_micro_batch(64, 862, host_path=True) == 32 and g.auto_micro_batch(3, 862, host_path=True) == 3
+    assert g.auto_micro_batch(0, 862) == 0
+    g.close()
