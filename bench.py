@@ -37,6 +37,9 @@ CONFIGS = {            # name -> (config version, per-GPU batch, frames)
 }
 
 
+emit = None
+
+
 def peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -143,7 +146,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": val, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
@@ -160,6 +163,12 @@ def main():
     ap.add_argument("--no-adjacent", action="store_true", help="skip the PCM16 / mel front-end side measurements")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    # stdout carries exactly ONE JSON line: anything libraries print there (NCCL's version banner ...) goes to stderr
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    global emit
+    emit = lambda line: (real_stdout.write(json.dumps(line) + "\n"), real_stdout.flush())
 
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -344,7 +353,7 @@ def main():
             line["cpu_baseline"] = {"value": best, "unit": "audio-s/s", "cores": threads, "kind": "port",
                                     "sample": "V1 batch 1 x 256 frames (configs[0]), best of 5; torch-CPU fp32 restatement of "
                                               "HiFiGAN_TF/model.py (TensorFlow not installable on this image)"}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
