@@ -108,7 +108,9 @@ int hfg_forward_pcm16(hfg_handle h, const float* mel_dev, int B, int T, int16_t*
 int hfg_forward_host_pcm16(hfg_handle h, const float* mel_host, int B, int T, int16_t* pcm_host);
 
 /* Options: "micro_batch" = utterances per forward of hfg_forward_host (0 = auto, the default: hfg_auto_micro_batch);
- * "stage_timing" 0/1; "force_ffma" 0/1 and "auto_fold" 0/1 (both need a new hfg_finalize_weights). */
+ * "stage_timing" 0/1; "cuda_graphs" 0/1 (default 1: launch-bound micro-batches of hfg_forward_host, <= 8192 frames,
+ * are replayed from a CUDA graph captured on their second use); "force_ffma" 0/1 and "auto_fold" 0/1 (both need a
+ * new hfg_finalize_weights). */
 int hfg_set_option(hfg_handle h, const char* key, long long value);
 
 /* Which kernel family each layer was bound to by hfg_finalize_weights: lines "<layer>:<tc|ffma|post>\n"

@@ -198,6 +198,10 @@ __device__ __forceinline__ void umma_commit_2cta(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
                ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
 }
+// Programmatic dependent launch: `pdl_launch_dependents` lets the next kernel of the stream start its prologue on free
+// SMs; `pdl_wait` blocks until the previous kernel has completed and its writes are visible.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(tm) : "memory");
 }
@@ -339,6 +343,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;       // 0 = leader of the pair
+  pdl_launch_dependents();            // the next layer's kernel may begin its prologue on SMs this grid leaves free
   const int tile0 = blockIdx.x / CG, tile_step = gridDim.x / CG;
 
   if (tid == 0) {
@@ -356,6 +361,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
   if (CG == 2) cluster_sync_all(); else __syncthreads();   // pair: the peer's barriers are initialised before any remote signal
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // Everything above (barriers, TMEM, bias, descriptor prefetch) touched only constants and ran while the previous
+  // layer's kernel was still draining; activations are read / written only past this point.
+  if (warp != 1) pdl_wait();          // the weight producer reads constants only: it starts staging right away
 
   // tile index -> (utterance b, row tile qt, variant v, channel tile nt)
   auto decode = [&](int t, int& b, int& qt, int& v, int& nt) {
@@ -662,6 +670,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
 // ------------------------------------------------------------------ host side
 int g_num_sms = 0;
 
+int tc_num_sms() {
+  if (!g_num_sms) {
+    int dev = 0; cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (g_num_sms <= 0) g_num_sms = 148;
+  }
+  return g_num_sms;
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -800,11 +817,7 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total);
     if (e != cudaSuccess) return e;
     configured = pl.total;
-    if (!g_num_sms) {
-      int dev = 0; cudaGetDevice(&dev);
-      cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-      if (g_num_sms <= 0) g_num_sms = 148;
-    }
+    tc_num_sms();
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kTcThreads, pl.total);
     if (e != cudaSuccess) return e;
     constexpr int NACC = (2 * MB * N <= 512) ? 2 : 1;
@@ -813,23 +826,27 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
     if (occ < 1) occ = 1;
   }
   int grid = g_num_sms * occ;
+  static const bool use_pdl = tc_env_int("HFG_PDL", 1) != 0;
+  cudaLaunchAttribute at[2];
+  int nat = 0;
+  if (use_pdl) { at[nat].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[nat].val.programmaticStreamSerializationAllowed = 1; ++nat; }
+  cudaLaunchConfig_t lc{};
+  lc.blockDim = dim3(kTcThreads); lc.dynamicSmemBytes = pl.total; lc.stream = s; lc.attrs = at;
   if (CG == 1) {
     if (grid > ka.total_tiles) grid = ka.total_tiles;
     if (grid_out) *grid_out = grid;
-    kern<<<grid, kTcThreads, pl.total, s>>>(tm_x, tm_res, tm_out, tm_w, ka);
-    return cudaGetLastError();
+    lc.gridDim = dim3(grid); lc.numAttrs = nat;
+    return cudaLaunchKernelEx(&lc, kern, tm_x, tm_res, tm_out, tm_w, ka);
   }
   // CTA pairs: cluster of 2 (same TPC), one pair per pair-tile stride
   int pairs = g_num_sms / 2;
   if (pairs > ka.total_tiles) pairs = ka.total_tiles;
   grid = 2 * pairs;
   if (grid_out) *grid_out = grid;
-  cudaLaunchConfig_t lc{};
-  lc.gridDim = dim3(grid); lc.blockDim = dim3(kTcThreads); lc.dynamicSmemBytes = pl.total; lc.stream = s;
-  cudaLaunchAttribute at[1];
-  at[0].id = cudaLaunchAttributeClusterDimension;
-  at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-  lc.attrs = at; lc.numAttrs = 1;
+  at[nat].id = cudaLaunchAttributeClusterDimension;
+  at[nat].val.clusterDim.x = 2; at[nat].val.clusterDim.y = 1; at[nat].val.clusterDim.z = 1;
+  ++nat;
+  lc.gridDim = dim3(grid); lc.numAttrs = nat;
   return cudaLaunchKernelEx(&lc, kern, tm_x, tm_res, tm_out, tm_w, ka);
 }
 
@@ -859,6 +876,19 @@ struct TcRow { int c_in, c_out_tile; TcConfig cfg; };
   X(32, 16, 4, 32, 32, 4, 4, 3, 8, 1)    \
   X(16, 16, 4, 16, 16, 4, 4, 3, 8, 1)
 
+// Small-problem variants: the same operand staging (identical packed weights: n, ks, kbw, tps, cg) with half the rows
+// per tile, used when a layer has fewer tiles than the GPU has SMs (single utterances, the short early stages): twice
+// the CTAs at work and half the serial MMA chain per tile.  V1, 1 x 256 frames: 1.09 -> see DESIGN.md section 5.
+#define HFG_TC_SMALL(X)                  \
+  X(256, 128, 1, 64, 64, 1, 6, 2, 5, 2)  \
+  X(128, 128, 1, 64, 64, 1, 6, 2, 5, 2)  \
+  X(128, 64, 1, 64, 64, 2, 6, 2, 5, 2)   \
+  X(64, 64, 1, 64, 64, 2, 6, 2, 5, 2)    \
+  X(64, 32, 2, 64, 64, 2, 4, 2, 5, 1)    \
+  X(32, 32, 2, 32, 32, 4, 4, 3, 8, 1)    \
+  X(32, 16, 2, 32, 32, 4, 4, 3, 8, 1)    \
+  X(16, 16, 2, 16, 16, 4, 4, 3, 8, 1)
+
 const TcRow kTcTable[] = {
 #define X(CI, NN, MB, KS, KBW, TPS, NST, NSL, NSTG, CG) {CI, NN, {NN, MB, KS, KBW, TPS, NST, NSL, NSTG, CG}},
     HFG_TC_TABLE(X)
@@ -879,6 +909,16 @@ cudaError_t launch_shape(const TcArgs& a, ActType act, cudaStream_t s, int* grid
   for (int v = 0; v < a.nvar; ++v)
     for (int j = 0; j < a.var[v].ntaps; ++j) { mn = a.var[v].tap_off[j] < mn ? a.var[v].tap_off[j] : mn; mx = a.var[v].tap_off[j] > mx ? a.var[v].tap_off[j] : mx; }
   if (!tc_config(a.c_in, a.c_out, mx - mn, &c)) return cudaErrorInvalidValue;
+  // fewer tiles than SMs -> the half-height variant of the same row, if there is one
+  static const bool allow_small = tc_env_int("HFG_TC_SMALL", 1) != 0;
+  const long long ctas = (long long)a.B * ((a.n_q + c.cg * c.mb * 128 - 1) / (c.cg * c.mb * 128)) * a.nvar * (a.c_out / c.n) * c.cg;
+  if (allow_small && ctas < tc_num_sms()) {
+#define X(CI, NN, MB, KS, KBW, TPS, NST, NSL, NSTG, CG) \
+    if (ci == CI && n == NN && c.cg == CG && c.nst == NST && c.nstg == NSTG && c.mb == 2 * MB && c.tps == TPS) \
+      return launch_t<T, CI, NN, MB, KS, KBW, TPS, NST, NSL, NSTG, CG>(a, act, s, grid_out);
+    HFG_TC_SMALL(X)
+#undef X
+  }
 #define X(CI, NN, MB, KS, KBW, TPS, NST, NSL, NSTG, CG) \
   if (ci == CI && n == NN && c.cg == CG && c.nst == NST && c.nstg == NSTG) return launch_t<T, CI, NN, MB, KS, KBW, TPS, NST, NSL, NSTG, CG>(a, act, s, grid_out);
   HFG_TC_TABLE(X)

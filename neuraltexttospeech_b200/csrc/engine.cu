@@ -80,6 +80,11 @@ struct hfg_ctx {
   cudaStream_t stream = nullptr;
   cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;   // host path: copies overlap the forward of the neighbouring micro-batch
   std::vector<cudaEvent_t> copy_events;                      // 2 per micro-batch (mel landed, audio ready)
+  // host path, small forwards (launch-bound): the launch sequence of one micro-batch is captured into a CUDA graph on
+  // its second use and replayed afterwards (tensor maps and pointers are baked in: the cache is keyed on them)
+  struct GraphEntry { const void* mel; const void* out; const void* ws; int B, T, sample_bytes; int uses; long long launches; cudaGraphExec_t exec; };
+  std::vector<GraphEntry> graphs;
+  bool use_graphs = true;
   void* ws = nullptr; size_t ws_bytes = 0;
   float* d_mel = nullptr; size_t d_mel_bytes = 0;
   void* d_audio = nullptr; size_t d_audio_bytes = 0;   // fp32 audio or 16-bit PCM
@@ -89,6 +94,11 @@ struct hfg_ctx {
 };
 
 namespace {
+
+void clear_graphs(hfg_ctx* h) {
+  for (auto& g : h->graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
+  h->graphs.clear();
+}
 
 int fail(hfg_ctx* h, int code, const char* fmt, ...) {
   char buf[512];
@@ -578,6 +588,7 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
   for (const Layer& L : h->layers)
     if (!L.has_v || !L.has_g || !L.has_b) return fail(h, HFG_ERR_STATE, "layer '%s' is missing %s", L.name.c_str(), !L.has_v ? "v" : (!L.has_g ? "g" : "b"));
   CUDA_TRY(h, cudaSetDevice(h->device));
+  clear_graphs(h);                                     // weight pointers are baked into captured launches
   h->precision = precision;
   h->act = precision == HFG_PRECISION_FP32 ? ACT_F32 : (precision == HFG_PRECISION_FP16 ? ACT_F16 : ACT_BF16);
   const hfg_config& c = h->cfg;
@@ -705,6 +716,46 @@ int hfg_forward_pcm16(hfg_handle h, const float* mel_dev, int B, int T, int16_t*
   return forward_device(h, mel_dev, B, T, nullptr, pcm_dev, workspace_dev, workspace_bytes, stream, "hfg_forward_pcm16");
 }
 
+// One micro-batch of the host path on h->stream.  Launch-bound forwards (few frames) are replayed from a CUDA graph
+// captured on the second use of the same (buffers, shape): 79 launches + 230 tensor-map encodes become one graph launch.
+static int forward_maybe_graph(hfg_ctx* h, const float* mel, int nb, int T, char* dev_out, int sample_bytes) {
+  float* audio = sample_bytes == 4 ? (float*)dev_out : nullptr;
+  int16_t* pcm = sample_bytes == 2 ? (int16_t*)dev_out : nullptr;
+  const bool eligible = h->use_graphs && !h->stage_timing && (long long)nb * T <= 8192;
+  if (!eligible) return run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->stream);
+  hfg_ctx::GraphEntry* e = nullptr;
+  for (auto& g : h->graphs)
+    if (g.mel == mel && g.out == dev_out && g.ws == h->ws && g.B == nb && g.T == T && g.sample_bytes == sample_bytes) { e = &g; break; }
+  if (!e) {
+    if (h->graphs.size() >= 16) { if (h->graphs.front().exec) cudaGraphExecDestroy(h->graphs.front().exec); h->graphs.erase(h->graphs.begin()); }
+    h->graphs.push_back({mel, dev_out, h->ws, nb, T, sample_bytes, 0, 0, nullptr});
+    e = &h->graphs.back();
+  }
+  if (e->exec) {
+    h->launches = e->launches;
+    CUDA_TRY(h, cudaGraphLaunch(e->exec, h->stream));
+    return HFG_OK;
+  }
+  if (e->uses++ == 0) return run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->stream);   // first use: plain (also warms per-kernel attributes)
+  CUDA_TRY(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+  int rc = run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->stream);
+  cudaGraph_t graph = nullptr;
+  cudaError_t ce = cudaStreamEndCapture(h->stream, &graph);
+  if (rc || ce != cudaSuccess || !graph) {
+    if (graph) cudaGraphDestroy(graph);
+    cudaGetLastError();
+    h->use_graphs = false;                               // capture unsupported here: stay on plain launches
+    if (rc) return rc;
+    return run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->stream);
+  }
+  ce = cudaGraphInstantiate(&e->exec, graph, 0);
+  cudaGraphDestroy(graph);
+  if (ce != cudaSuccess) { e->exec = nullptr; cudaGetLastError(); h->use_graphs = false; return run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->stream); }
+  e->launches = h->launches;
+  CUDA_TRY(h, cudaGraphLaunch(e->exec, h->stream));
+  return HFG_OK;
+}
+
 // host-buffer forward; `sample_bytes` = 4 (fp32 audio) or 2 (16-bit PCM)
 static int forward_host(hfg_handle h, const float* mel_host, int B, int T, void* out_host, int sample_bytes, const char* fn) {
   if (!h) return HFG_ERR_INVALID;
@@ -719,18 +770,21 @@ static int forward_host(hfg_handle h, const float* mel_host, int B, int T, void*
   const size_t mel_elems = (size_t)T * h->cfg.num_mels, aud_elems = (size_t)T * h->total_up;
   const size_t need_ws = workspace_layout(h, mb, T, nullptr, nullptr);
   if (need_ws > h->ws_bytes) {
+    clear_graphs(h);
     if (h->ws) cudaFree(h->ws);
     h->ws = nullptr; h->ws_bytes = 0;
     CUDA_TRY(h, cudaMalloc(&h->ws, need_ws));
     h->ws_bytes = need_ws;
   }
   if ((size_t)B * mel_elems * 4 > h->d_mel_bytes) {
+    clear_graphs(h);
     if (h->d_mel) cudaFree(h->d_mel);
     h->d_mel = nullptr; h->d_mel_bytes = 0;
     CUDA_TRY(h, cudaMalloc((void**)&h->d_mel, (size_t)B * mel_elems * 4));
     h->d_mel_bytes = (size_t)B * mel_elems * 4;
   }
   if ((size_t)B * aud_elems * sample_bytes > h->d_audio_bytes) {
+    clear_graphs(h);
     if (h->d_audio) cudaFree(h->d_audio);
     h->d_audio = nullptr; h->d_audio_bytes = 0;
     CUDA_TRY(h, cudaMalloc((void**)&h->d_audio, (size_t)B * aud_elems * sample_bytes));
@@ -757,8 +811,7 @@ static int forward_host(hfg_handle h, const float* mel_host, int B, int T, void*
     const int nb = (B - b0 < mb) ? B - b0 : mb;
     char* dev_out = (char*)h->d_audio + (size_t)b0 * aud_elems * sample_bytes;
     CUDA_TRY(h, cudaStreamWaitEvent(h->stream, h->copy_events[2 * i], 0));
-    int rc = run_forward(h, h->d_mel + (size_t)b0 * mel_elems, nb, T, sample_bytes == 4 ? (float*)dev_out : nullptr,
-                         sample_bytes == 2 ? (int16_t*)dev_out : nullptr, (char*)h->ws, h->stream);
+    int rc = forward_maybe_graph(h, h->d_mel + (size_t)b0 * mel_elems, nb, T, dev_out, sample_bytes);
     launches += h->launches; h->launches = 0;
     if (rc) { cudaStreamSynchronize(h->h2d_stream); cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->d2h_stream); return rc; }
     CUDA_TRY(h, cudaEventRecord(h->copy_events[2 * i + 1], h->stream));
@@ -786,6 +839,7 @@ int hfg_set_option(hfg_handle h, const char* key, long long value) {
   if (k == "micro_batch") { if (value < 0) return fail(h, HFG_ERR_INVALID, "micro_batch must be >= 0"); h->micro_batch = (int)value; return HFG_OK; }
   if (k == "stage_timing") { h->stage_timing = value != 0; h->timed_forwards = 0; return HFG_OK; }
   if (k == "force_ffma") { h->force_ffma = value != 0; h->finalized = false; return HFG_OK; }
+  if (k == "cuda_graphs") { h->use_graphs = value != 0; if (!h->use_graphs) clear_graphs(h); return HFG_OK; }
   if (k == "auto_fold") { h->auto_fold = value != 0; h->finalized = false; return HFG_OK; }
   return fail(h, HFG_ERR_INVALID, "unknown option '%s'", key);
 }
@@ -936,6 +990,7 @@ void hfg_destroy(hfg_handle h) {
   if (h->h2d_stream) cudaStreamDestroy(h->h2d_stream);
   if (h->d2h_stream) cudaStreamDestroy(h->d2h_stream);
   for (auto& ev : h->copy_events) cudaEventDestroy(ev);
+  clear_graphs(h);
   delete h;
 }
 

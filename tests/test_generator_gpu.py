@@ -197,3 +197,35 @@ def test_auto_micro_batch_rule():
     assert g.auto_micro_batch(64, 862, host_path=True) == 32 and g.auto_micro_batch(3, 862, host_path=True) == 3
     assert g.auto_micro_batch(0, 862) == 0
     g.close()
+
+
+def test_host_path_cuda_graph_replay_is_bit_identical():
+    """Small host-path forwards are captured into a CUDA graph on their second use and replayed from the third:
+    every call must return the same bits as plain launches, also after the buffers or the weights change."""
+    h = HParams.builtin("1")
+    w = synthetic_weights(h, "B")
+    g = Generator(h, precision="fp16").load_weights(w)
+    mel = synthetic_mel(2, 16, h.num_mels)
+    g.set_option("cuda_graphs", 0)
+    plain = g(mel).copy()
+    g.set_option("cuda_graphs", 1)
+    outs = [g(mel).copy() for _ in range(4)]                    # plain, capture, replay, replay
+    assert all((o == plain).all() for o in outs)
+    assert g.last_launch_count() == 79
+    mel2 = synthetic_mel(2, 16, h.num_mels, seed=7)             # same shape, new data: the graph reads the same device buffer
+    g.set_option("cuda_graphs", 0)
+    plain2 = g(mel2).copy()
+    g.set_option("cuda_graphs", 1)
+    assert all((g(mel2) == plain2).all() for _ in range(3))
+    big = synthetic_mel(5, 40, h.num_mels)                      # grows the internal buffers: cached graphs must be dropped
+    ref_big = O.generator_forward(h, w, big, "torch32")
+    assert np.abs(g(big) - ref_big).max() <= TC_TOL
+    assert all((g(mel2) == plain2).all() for _ in range(3))
+    w2 = synthetic_weights(h, "A")                              # new weights: graphs hold the old weight pointers
+    g.load_weights(w2)
+    ref2 = O.generator_forward(h, w2, mel2, "torch32")
+    for _ in range(3):
+        assert np.abs(g(mel2) - ref2).max() <= TC_TOL
+    pcm = [g.synthesize_pcm16(mel2) for _ in range(3)]
+    assert all((p == pcm[0]).all() for p in pcm)
+    g.close()
