@@ -812,20 +812,25 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
   else tm_res = tm_out;
   if (CG == 1) tm_w = tm_out;
   auto kern = conv_tc_kernel<T, C_IN, N, MB, KS, KBW, TPS, NST, NSL, NSTG, CG>;
-  static int configured = 0, occ = 1;      // per instantiation
-  if (pl.total > configured) {
+  // per instantiation AND per device: function attributes live in the device's context (a process may hold handles
+  // on several GPUs even though the intended deployment is one process per GPU)
+  constexpr int kMaxDev = 32;
+  static int configured_dev[kMaxDev] = {0}, occ_dev[kMaxDev] = {0};
+  int dev = 0; cudaGetDevice(&dev);
+  if (dev < 0 || dev >= kMaxDev) return cudaErrorInvalidDevice;
+  if (pl.total > configured_dev[dev]) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total);
     if (e != cudaSuccess) return e;
-    configured = pl.total;
-    tc_num_sms();
+    configured_dev[dev] = pl.total;
+    int occ = 1;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kTcThreads, pl.total);
     if (e != cudaSuccess) return e;
     constexpr int NACC = (2 * MB * N <= 512) ? 2 : 1;
     const int tmem_occ = 512 / (int)tc_tmem_cols(NACC * MB * N);
     if (occ > tmem_occ) occ = tmem_occ;
-    if (occ < 1) occ = 1;
+    occ_dev[dev] = occ < 1 ? 1 : occ;
   }
-  int grid = g_num_sms * occ;
+  int grid = tc_num_sms() * occ_dev[dev];
   static const bool use_pdl = tc_env_int("HFG_PDL", 1) != 0;
   cudaLaunchAttribute at[2];
   int nat = 0;
@@ -839,7 +844,7 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
     return cudaLaunchKernelEx(&lc, kern, tm_x, tm_res, tm_out, tm_w, ka);
   }
   // CTA pairs: cluster of 2 (same TPC), one pair per pair-tile stride
-  int pairs = g_num_sms / 2;
+  int pairs = tc_num_sms() / 2;
   if (pairs > ka.total_tiles) pairs = ka.total_tiles;
   grid = 2 * pairs;
   if (grid_out) *grid_out = grid;

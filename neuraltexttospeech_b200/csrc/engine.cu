@@ -63,7 +63,11 @@ struct hfg_ctx {
   hfg_config cfg{};
   int device = 0;
   std::vector<Layer> layers;
-  std::map<std::string, int> index;
+  std::map<std::string, int> index;     // weight name -> layer (hfg_set_weight)
+  // forward plan (indices into `layers`, fixed at create): run_forward does no string work
+  int i_pre = -1, i_post = -1;
+  std::vector<int> i_ups;               // [stage]
+  std::vector<int> i_rb;                // [resblock n][dilation m][0 = convs1 / convs, 1 = convs2]: (n * HFG_MAX_DILATIONS + m) * 2 + which
   int total_up = 1;
   bool finalized = false;
   int precision = HFG_PRECISION_FP32;
@@ -138,19 +142,25 @@ void build_layers(hfg_ctx* h) {
     h->layers.push_back(std::move(L));
   };
   const int c0 = c.upsample_initial_channel;
+  h->i_rb.assign((size_t)c.num_upsamples * c.num_kernels * HFG_MAX_DILATIONS * 2, -1);
+  auto rb_slot = [&](int n, int m, int which) -> int& { return h->i_rb[((size_t)n * HFG_MAX_DILATIONS + m) * 2 + which]; };
+  h->i_pre = (int)h->layers.size();
   add("conv_pre", false, 7, 1, 1, c.num_mels, c0);
   int cprev = c0;
   h->total_up = 1;
   for (int i = 0; i < c.num_upsamples; ++i) {
     const int ch = c0 >> (i + 1);
+    h->i_ups.push_back((int)h->layers.size());
     add("ups." + std::to_string(i), true, c.upsample_kernel_sizes[i], 1, c.upsample_rates[i], cprev, ch);
     h->total_up *= c.upsample_rates[i];
     for (int j = 0; j < c.num_kernels; ++j) {
       const int n = i * c.num_kernels + j;
       for (int m = 0; m < c.num_dilations[j]; ++m) {
         const std::string base = "resblocks." + std::to_string(n);
+        rb_slot(n, m, 0) = (int)h->layers.size();
         if (c.resblock == 1) {
           add(base + ".convs1." + std::to_string(m), false, c.resblock_kernel_sizes[j], c.resblock_dilation_sizes[j][m], 1, ch, ch);
+          rb_slot(n, m, 1) = (int)h->layers.size();
           add(base + ".convs2." + std::to_string(m), false, c.resblock_kernel_sizes[j], 1, 1, ch, ch);
         } else {
           add(base + ".convs." + std::to_string(m), false, c.resblock_kernel_sizes[j], c.resblock_dilation_sizes[j][m], 1, ch, ch);
@@ -159,6 +169,7 @@ void build_layers(hfg_ctx* h) {
     }
     cprev = ch;
   }
+  h->i_post = (int)h->layers.size();
   add("conv_post", false, 7, 1, 1, cprev, 1);
 }
 
@@ -444,11 +455,12 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
   auto stamp = [&]() {
     if (h->stage_timing && mark < h->marks_per_fwd) cudaEventRecord(h->events[(size_t)slot * h->marks_per_fwd + mark++], s);
   };
-  auto layer = [&](const std::string& name) -> const Layer& { return h->layers[h->index[name]]; };
+  auto rb = [&](int n, int m, int which) -> const Layer& { return h->layers[h->i_rb[((size_t)n * HFG_MAX_DILATIONS + m) * 2 + which]]; };
+  auto up_layer = [&](int i) -> const Layer& { return h->layers[h->i_ups[i]]; };
   stamp();
 
   // conv_pre (model.py:156); its consumer is ups[0] behind lrelu(0.1)
-  const Layer& pre = layer("conv_pre");
+  const Layer& pre = h->layers[h->i_pre];
   const void* x0 = mel_dev;
   if (h->act != ACT_F32 || pre.cin_pad != pre.cin) {
     cudaError_t e = launch_cast_pad(mel_dev, w.MEL, (long long)B * T, pre.cin, pre.cin_pad, h->act, s);
@@ -456,18 +468,17 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
     if (e != cudaSuccess) return fail(h, HFG_ERR_CUDA, "cast_pad launch failed: %s", cudaGetErrorString(e));
     x0 = w.MEL;
   }
-  r.conv(pre, x0, T, w.P, 1.0f, nullptr, kSlope, layer("ups.0").use_tc);
+  r.conv(pre, x0, T, w.P, 1.0f, nullptr, kSlope, up_layer(0).use_tc);
   stamp();
 
   char* x = w.P;          // current stage input
   int L = T;
-  bool x_preact = layer("ups.0").use_tc;   // is x stored already activated for its consumer?
+  bool x_preact = up_layer(0).use_tc;      // is x stored already activated for its consumer?
   for (int i = 0; i < c.num_upsamples; ++i) {
-    const Layer& up = layer("ups." + std::to_string(i));
-    const std::string first_rb = "resblocks." + std::to_string(i * c.num_kernels) + (c.resblock == 1 ? ".convs1.0" : ".convs.0");
-    const bool rb_tc = layer(first_rb).use_tc;                   // a stage's resblock convs all share one shape
+    const Layer& up = up_layer(i);
+    const bool rb_tc = rb(i * c.num_kernels, 0, 0).use_tc;       // a stage's resblock convs all share one shape
     const bool last_stage = (i == c.num_upsamples - 1);
-    const bool next_tc = last_stage ? rb_tc : layer("ups." + std::to_string(i + 1)).use_tc;   // conv_post reads either form
+    const bool next_tc = last_stage ? rb_tc : up_layer(i + 1).use_tc;   // conv_post reads either form
     const float next_slope = last_stage ? kFinalSlope : kSlope;
     r.conv(up, x, L, w.U, x_preact ? 1.0f : kSlope, nullptr, kSlope, rb_tc);   // model.py:159-160
     L *= up.stride;
@@ -481,15 +492,14 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
         const bool last = (m == nd - 1);
         char* rnext = (rcur == w.P) ? w.Q : w.P;
         if (last && j == c.num_kernels - 1) next_x = rnext;
-        const std::string base = "resblocks." + std::to_string(n);
         if (c.resblock == 1) {                                   // ResBlock1.call model.py:71-80
-          const Layer& c1 = layer(base + ".convs1." + std::to_string(m));
-          const Layer& c2 = layer(base + ".convs2." + std::to_string(m));
+          const Layer& c1 = rb(n, m, 0);
+          const Layer& c2 = rb(n, m, 1);
           r.conv(c1, rcur, L, w.T, kSlope, nullptr, kSlope, rb_tc);
           if (last) r.conv_mrf(c2, w.T, L, rnext, w.S, kSlope, rcur, w.ACC, j, c.num_kernels, next_slope, next_tc);
           else r.conv(c2, w.T, L, rnext, kSlope, rcur, kSlope, rb_tc);
         } else {                                                 // ResBlock2.call model.py:106-112
-          const Layer& c1 = layer(base + ".convs." + std::to_string(m));
+          const Layer& c1 = rb(n, m, 0);
           if (last) r.conv_mrf(c1, rcur, L, rnext, w.S, kSlope, rcur, w.ACC, j, c.num_kernels, next_slope, next_tc);
           else r.conv(c1, rcur, L, rnext, kSlope, rcur, kSlope, rb_tc);
         }
@@ -503,7 +513,7 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
   if (r.status != cudaSuccess) return fail(h, HFG_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(r.status));
 
   // leakyReLU(0.3) -> conv_post -> tanh (model.py:169-171)
-  const Layer& post = layer("conv_post");
+  const Layer& post = h->layers[h->i_post];
   if (post.use_tc) {            // x is stored activated with the final slope (see hfg_finalize_weights); w.T is free scratch here
     r.conv_tc(post, x, L, w.T, nullptr, 1.0f, nullptr, 1.0f, 1.0f, audio_dev, pcm_dev);
     if (r.status != cudaSuccess) return fail(h, HFG_ERR_CUDA, "conv_post launch failed: %s", cudaGetErrorString(r.status));

@@ -137,7 +137,19 @@ class Generator:
             if x.is_cuda:
                 return self._call_device(x)
             return torch.from_numpy(self._call_host(x.detach().numpy()))
+        if hasattr(x, "__cuda_array_interface__"):      # cupy / numba / any raw device buffer
+            return self._call_device(self._from_cuda_array_interface(x))
         return self._call_host(np.asarray(x))
+
+    def _from_cuda_array_interface(self, x):
+        """Zero-copy torch view of a foreign device array (fp32, C-contiguous); the result of the call is a torch
+        CUDA tensor, which exposes `__cuda_array_interface__` itself."""
+        if torch is None:
+            raise RuntimeError("device-pointer inputs need torch for the output / workspace allocation")
+        cai = x.__cuda_array_interface__
+        if cai.get("typestr") not in ("<f4", "=f4", "|f4") or cai.get("strides") is not None:
+            raise ValueError("device mel must be float32 and C-contiguous")
+        return torch.as_tensor(x, device=torch.device("cuda", self.device))
 
     def _check_shape(self, shape):
         if len(shape) != 3 or int(shape[2]) != int(self.hparams.num_mels):
