@@ -107,7 +107,21 @@ def _load_folded(gen, h, weights):
                 put(rb.convs[m], f"resblocks.{n}.convs.{m}", "conv")
 
 
+def make_adjacent():
+    """adjacent_frontend.npz: seeded waveform + the fp64 oracle's log-mel (stored fp32) and its 16-bit PCM."""
+    from oracle import adjacent_oracle as A
+    rng = np.random.default_rng(4321)
+    n = 1024 + 256 * 9 + 17
+    t = np.arange(n)[None, :] / 22050.0
+    f0 = np.array([[110.0], [196.0]])
+    wav = sum((0.3 / h_) * np.sin(2 * np.pi * f0 * h_ * t + h_) for h_ in range(1, 24)) + 0.005 * rng.standard_normal((2, n))
+    wav = (wav / np.abs(wav).max() * 0.9).astype(np.float32)
+    np.savez_compressed(os.path.join(HERE, "adjacent_frontend.npz"), wav=wav,
+                        mel=A.mel_spectrogram(wav.astype(np.float64)).astype(np.float32), pcm=A.pcm16(wav))
+
+
 def main():
+    make_adjacent()
     import torch
     torch.manual_seed(0)
     B, T = 2, 9

@@ -115,3 +115,13 @@ def test_wav_to_mel_to_wav_round_trip_runs_on_device():
     ref = O.generator_forward(h, synthetic_weights(h, "A"), mel.cpu().numpy(), "torch32")
     assert np.abs(audio.cpu().numpy() - ref).max() <= 2e-3
     g.close(); fe.close()
+
+
+def test_mel_frontend_matches_committed_fixture(golden_dir):
+    import os
+    from neuraltexttospeech_b200 import STFT
+    z = np.load(os.path.join(golden_dir, "adjacent_frontend.npz"))
+    fe = STFT()
+    mel = fe.mel_spectrogram(z["wav"])
+    assert mel.shape == z["mel"].shape and np.abs(mel - z["mel"]).max() <= 2e-3
+    fe.close()

@@ -73,3 +73,11 @@ def test_mel_spectrogram_frames_and_pure_tone():
     # batch and dtype
     b = A.mel_spectrogram(np.stack([wav, wav]).astype(np.float32), dtype=np.float32)
     assert b.shape == (2, 8, 80) and b.dtype == np.float32 and np.abs(b[0] - mel).max() < 1e-2
+
+
+def test_oracle_reproduces_committed_adjacent_fixture(golden_dir):
+    z = np.load(os.path.join(golden_dir, "adjacent_frontend.npz"))
+    mel = A.mel_spectrogram(z["wav"].astype(np.float64))
+    assert mel.shape == z["mel"].shape == (2, 10, 80)
+    assert np.abs(mel - z["mel"]).max() < 1e-5
+    assert (A.pcm16(z["wav"]) == z["pcm"]).all()
