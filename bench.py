@@ -67,7 +67,7 @@ def ncu_traffic(stage_label, workload, mb):
 class ClockSampler:
     """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,power.draw,power.limit")
 
     def __init__(self, index):
         self.index, self.samples, self.stop_flag, self.th = index, [], False, None
@@ -97,8 +97,16 @@ class ClockSampler:
         mx = [int(s[1]) for s in self.samples if len(s) > 1 and s[1].isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = sorted({n for s in self.samples for n, v in zip(names, s[2:6]) if v.lower().startswith("active")})
+        def fl(v):
+            try:
+                return float(v)
+            except Exception:
+                return None
+        pw = sorted(p for p in (fl(s[6]) for s in self.samples if len(s) > 6) if p is not None)
+        lim = [p for p in (fl(s[7]) for s in self.samples if len(s) > 7) if p is not None]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(self.samples)}
+                "reasons": reasons, "samples": len(self.samples),
+                "power_w": pw[len(pw) // 2] if pw else None, "power_limit_w": max(lim) if lim else None}
 
 
 def cpu_port_audio_s_per_s(version, B, T, repeats, threads=None):
