@@ -879,7 +879,9 @@ struct TcRow { int c_in, c_out_tile; TcConfig cfg; };
   X(64, 32, 4, 64, 64, 2, 4, 2, 5, 1)    \
   X(32, 32, 4, 32, 32, 4, 4, 3, 8, 1)    \
   X(32, 16, 4, 32, 32, 4, 4, 3, 8, 1)    \
-  X(16, 16, 4, 16, 16, 4, 4, 3, 8, 1)
+  X(16, 16, 4, 16, 16, 4, 4, 3, 8, 1)    \
+  X(64, 16, 4, 64, 64, 2, 4, 2, 8, 1)    \
+  X(128, 16, 4, 64, 64, 1, 4, 2, 8, 1)
 
 // Small-problem variants: the same operand staging (identical packed weights: n, ks, kbw, tps, cg) with half the rows
 // per tile, used when a layer has fewer tiles than the GPU has SMs (single utterances, the short early stages): twice

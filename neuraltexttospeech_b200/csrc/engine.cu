@@ -620,6 +620,25 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
     if (tc_mode && (!is_post || post_tc)) {
       int fi = fold_of(L.cin, L.in_rate), fo = is_post ? fi : fold_of(L.cout, L.out_rate);
       if (L.transposed ? (fi != 1 || L.stride % fo != 0) : (!is_post && fi != fo)) fi = fo = 1;
+      if (post_tc && h->auto_fold) {
+        // conv_post (C_out = 1 in a 16-column tile): every MMA streams a 4 KB A tile for 8 cycles of math, so the
+        // fewest MMAs per sample win: folding by f turns 7 taps x C/16 K-steps per row into about (6 + f) / f + 1
+        // taps x C*f/16 K-steps per f samples
+        double best = 1e30;
+        int best_f = fi;
+        for (int f = 1; f <= 16; f *= 2) {
+          const int cf = L.cin * f;
+          if (cf < 16 || cf > 128 || L.in_rate % f != 0) continue;
+          std::map<int, int> taps;
+          for (int sidx = 0; sidx < f; ++sidx)
+            for (int j = 0; j < L.k; ++j) taps[floordiv(sidx + j - pl, f)] = 1;
+          const int nt = (int)taps.size(), span = taps.rbegin()->first - taps.begin()->first;
+          if (nt > kMaxTaps || !tc_supported(cf, 16, nt, span)) continue;
+          const double cst = (double)nt * (cf / 16.0) / f;
+          if (cst < best) { best = cst; best_f = f; }
+        }
+        fi = fo = best_f;
+      }
       if (!L.transposed && !is_pre && !is_post && L.cin == L.cout && h->auto_fold) {
         // ResBlock convs: folding is free in memory (bit-identical tensor), so pick the fold factor with the lowest
         // modelled MMA + operand-staging time per output row (see fold_cost)
