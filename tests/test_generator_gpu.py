@@ -272,3 +272,20 @@ def test_launch_path_knobs_off_in_a_subprocess():
     r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_generator_gpu.py"), "-q", "-x", "-m", "gpu",
                         "-k", "golden or seeded or batch_independence"], env=env, cwd=root, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+@pytest.mark.parametrize("v", "13")
+def test_bf16_mode_tracks_the_bf16_emulating_oracle(v):
+    """precision="bf16" is offered for range, not accuracy: it must agree with the oracle run with bf16 operand /
+    storage rounding (same arithmetic, different summation order) and stay a sane waveform; the north-star tolerance is only claimed for the fp16 default (tests/test_oracle.py)."""
+    h = HParams.builtin(v)
+    w = synthetic_weights(h, "B")
+    mel = synthetic_mel(2, 15, h.num_mels)
+    ref32 = O.generator_forward(h, w, mel, "torch32")
+    emul = O.generator_forward(h, w, mel, "torch_emul:bf16:bf16")
+    g = Generator(h, precision="bf16").load_weights(w)
+    out = g(mel)
+    g.close()
+    assert np.isfinite(out).all() and np.abs(out).max() <= 1.0
+    assert snr_db(ref32, out) >= 25.0                       # bf16's 8-bit mantissa: ~30 dB
+    assert snr_db(emul, out) >= 20.0                        # and is consistent with the oracle's bf16 emulation
