@@ -48,6 +48,9 @@ constexpr int kTcMaxCout = 512;
 constexpr int kTcMaxSpan = 96;       // largest max_off - min_off supported (V1: 50, V3: 72)
 constexpr size_t kTcMaxSmem = 227 * 1024;
 
+constexpr int kTcMaxAcc = 4;          // accumulator buffers in TMEM (acc_full / acc_empty barrier pairs)
+__host__ __device__ constexpr int tc_nacc(int mb, int n) { return 2 * mb * n <= 512 ? 2 : 1; }   // 4 buffers were tried: the epilogue, not the accumulator ring, paces the narrow layers
+
 __host__ __device__ constexpr uint32_t tc_tmem_cols(int need) { return need <= 32 ? 32 : need <= 64 ? 64 : need <= 128 ? 128 : need <= 256 ? 256 : 512; }
 
 __host__ __device__ inline int tc_rows_padded(int rows, int chunks) {
@@ -273,12 +276,21 @@ __host__ __device__ inline TcSmemPlan tc_plan(int n, int ks, int kbw, int nst, i
   p.off_w = off; off += nst * p.stage_bytes;
   p.off_bias = off; off += kTcMaxCout * 4;     // bias of every output channel of the layer
   off = (off + 15) & ~15;
-  p.off_bar = off; off += (2 * nsl + 2 * nst + 3 * nstg + 4) * 8 + 16;
+  p.off_bar = off; off += (2 * nsl + 2 * nst + 3 * nstg + 2 * kTcMaxAcc) * 8 + 16;
   p.total = off;
   return p;
 }
 
+// Debug build only (-DHFG_TC_TRACE, tools/trace_layer.py): CTA 0 stamps clock64() per role / tile / event.
+#ifdef HFG_TC_TRACE
+#define TC_TRACE(role, tile_i, ev)                                                                                   \
+  do { if (ka.trace && blockIdx.x == 0 && (tile_i) < 64u) ka.trace[((role) * 64u + (tile_i)) * 8u + (ev)] = clock64(); } while (0)
+#else
+#define TC_TRACE(role, tile_i, ev) do { } while (0)
+#endif
+
 struct TcKArgs {
+  long long* trace;                    // HFG_TC_TRACE builds: [6 roles][64 tiles][8 events] clock64 stamps of CTA 0, else unused
   const float* bias;
   const void* res2;
   int n_q, c_out, has_res;
@@ -293,6 +305,7 @@ struct TcKArgs {
   float* post_out;                     // conv_post mode: audio[b, q*post_f + s] = tanh(channel s) written as fp32, no 16-bit tile
   int post_f;
   int16_t* post_pcm;                   // conv_post mode: 16-bit PCM output instead of post_out (pcm16_of)
+  int store_in_flight;                 // debug knob: TMA stores kept in flight by the store warp (-1 = default rule)
   int nsl, nstg;                       // ring depths actually used (>= the table's NSL / NSTG when shared memory allows)
 };
 
@@ -314,7 +327,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
   constexpr int ROWB = KS * 2;                    // bytes per slab row within a slice (= swizzle width)
   constexpr int PW = N < 64 ? N : 64;             // output columns per epilogue pass
   constexpr int SROWB = PW * 2;                   // bytes per staging row (= swizzle width)
-  constexpr int NACC = (2 * MB * N <= 512) ? 2 : 1;
+  constexpr int NACC = tc_nacc(MB, N);
   constexpr int ACC_COLS = MB * N;
   constexpr uint32_t TMEM_COLS = tc_tmem_cols(NACC * ACC_COLS);
   constexpr uint32_t IDESC = make_idesc(N, std::is_same<T, __nv_bfloat16>::value, 128 * CG);
@@ -338,8 +351,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
   uint64_t* stg_empty = stg_full + nstg;
   uint64_t* stg_done = stg_empty + nstg;
   uint64_t* acc_full = stg_done + nstg;
-  uint64_t* acc_empty = acc_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  uint64_t* acc_empty = acc_full + kTcMaxAcc;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + kTcMaxAcc);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;       // 0 = leader of the pair
@@ -350,7 +363,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
     for (int s = 0; s < nsl; ++s) { mbar_init(&slice_full[s], 1); mbar_init(&slice_empty[s], 1); }
     for (int s = 0; s < NST; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
     for (int s = 0; s < nstg; ++s) { mbar_init(&stg_full[s], 1); mbar_init(&stg_empty[s], 1); mbar_init(&stg_done[s], 4); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 8 * CG); }
+    for (int s = 0; s < kTcMaxAcc; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 8 * CG); }
     fence_mbar_init();
     tma_prefetch_desc(&tm_x); tma_prefetch_desc(&tm_res); tma_prefetch_desc(&tm_out);
     if (CG == 2) tma_prefetch_desc(&tm_w);
@@ -386,6 +399,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
         const int pos = scnt % (uint32_t)nsl;
         mbar_wait(&slice_empty[pos], ((scnt / (uint32_t)nsl) & 1) ^ 1);
         if (elect_one()) {
+          if (s == 0) TC_TRACE(0u, (uint32_t)((t - tile0) / tile_step), 0u);      // slot free, load issued
           uint8_t* dst = slab + pos * pl.slice_bytes;
           if (CG == 1) {
             mbar_expect_tx(&slice_full[pos], box_bytes * ka.nbox);
@@ -447,7 +461,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
       int b, qt, v, nt; decode(t, b, qt, v, nt);
       const int ntaps = ka.var[v].ntaps;
       const int abuf = tcnt % NACC;
+      if (lane == 0) TC_TRACE(2u, tcnt, 0u);                      // MMA warp arrives at the tile
       mbar_wait(&acc_empty[abuf], ((tcnt / NACC) & 1) ^ 1);
+      if (lane == 0) TC_TRACE(2u, tcnt, 1u);                      // accumulator free
       tc_fence_after();
       const uint32_t tacc = tmem_base + abuf * ACC_COLS;
       uint32_t first = 1;
@@ -456,6 +472,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
       for (int s = 0; s < NKS; ++s, ++scnt) {
         const int pos = scnt % (uint32_t)nsl;
         mbar_wait(&slice_full[pos], (scnt / (uint32_t)nsl) & 1);
+        if (lane == 0 && s == 0) TC_TRACE(2u, tcnt, 2u);          // first slab slice landed
         tc_fence_after();
         const uint32_t sl = slab_addr + pos * pl.slice_bytes;
 #pragma unroll 1
@@ -491,7 +508,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
               if (!ka.resident) { if (CG == 2) umma_commit_2cta(&w_empty[st]); else umma_commit(&w_empty[st]); }   // frees the weight stage
               if (kb == NKB - 1 && j0 + TPS >= ntaps) {
                 if (CG == 2) umma_commit_2cta(&slice_empty[pos]); else umma_commit(&slice_empty[pos]);   // slab slice may be overwritten
-                if (s == NKS - 1) { if (CG == 2) umma_commit_2cta(&acc_full[abuf]); else umma_commit(&acc_full[abuf]); }   // tile complete
+                if (s == NKS - 1) { if (CG == 2) umma_commit_2cta(&acc_full[abuf]); else umma_commit(&acc_full[abuf]); TC_TRACE(2u, tcnt, 3u); }   // tile complete (all MMAs issued)
               }
             }
             first = 0;
@@ -512,6 +529,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
           const int buf = pcnt % (uint32_t)nstg;
           mbar_wait(&stg_empty[buf], ((pcnt / (uint32_t)nstg) & 1) ^ 1);
           if (elect_one()) {
+            if (mb == 0 && p0 == 0) TC_TRACE(1u, (uint32_t)((t - tile0) / tile_step), 0u);   // first staging buffer of the tile granted
             if (ka.has_res && q0 < ka.n_q) {
               mbar_expect_tx(&stg_full[buf], pl.stg_bytes);
               tma_load_4d(stg + buf * pl.stg_bytes, &tm_res, nt * N + p0, 0, q0, b, &stg_full[buf]);
@@ -525,6 +543,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
     }
   } else if (warp == 12) {
     // ===================== store issuer: TMA tensor store of every finished staging tile =====================
+    // Up to two stores stay in flight: the buffer of pass p is handed back only once the store of pass p has finished
+    // READING shared memory, which is checked two passes later (bulk groups retire in order).  Waiting for each store
+    // right after issuing it serialised ~0.5 us per 8-16 KB tile and bounded the short-k layers of the narrow stages.
+    // Holding buffers longer shortens the residual prefetch distance, so small rings keep fewer stores in flight.
+    const int infl_env = ka.store_in_flight;            // debug knob (HFG_TC_STORES): -1 = default rule
+    const uint32_t in_flight = infl_env >= 0 ? (uint32_t)(infl_env < nstg - 1 ? infl_env : nstg - 2)
+                                             : (nstg >= 5 ? 2u : (nstg == 4 ? 1u : 0u));
     uint32_t pcnt = 0;
     for (int t = tile0; t < ka.total_tiles; t += tile_step) {
       int b, qt, v, nt; decode(t, b, qt, v, nt);
@@ -535,17 +560,27 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
           const int buf = pcnt % (uint32_t)nstg;
           mbar_wait(&stg_done[buf], (pcnt / (uint32_t)nstg) & 1);
           if (elect_one()) {
-            if (q0 < ka.n_q && ka.post_out == nullptr && ka.post_pcm == nullptr) {
+            if (mb == 0 && p0 == 0) TC_TRACE(3u, (uint32_t)((t - tile0) / tile_step), 0u);   // first finished pass of the tile seen by the store warp
+            if (mb == MB - 1 && p0 + PW >= N) TC_TRACE(3u, (uint32_t)((t - tile0) / tile_step), 1u);   // last one
+            if (q0 < ka.n_q && ka.post_out == nullptr && ka.post_pcm == nullptr)
               tma_store_4d(&tm_out, stg + buf * pl.stg_bytes, nt * N + p0, out_off, q0, b);
-              bulk_commit();
-              bulk_wait_read<0>();                      // the store has read the tile: the buffer may be refilled
+            bulk_commit();                              // one (possibly empty) group per pass keeps the group count = pass count
+            switch (in_flight) {                        // every group but the in_flight newest has been read out
+              case 0: bulk_wait_read<0>(); break;
+              case 1: bulk_wait_read<1>(); break;
+              case 2: bulk_wait_read<2>(); break;
+              case 3: bulk_wait_read<3>(); break;
+              case 4: bulk_wait_read<4>(); break;
+              case 5: bulk_wait_read<5>(); break;
+              default: bulk_wait_read<6>(); break;
             }
-            mbar_arrive(&stg_empty[buf]);
+            if (pcnt >= in_flight) mbar_arrive(&stg_empty[(pcnt - in_flight) % (uint32_t)nstg]);
           }
           __syncwarp();
         }
       }
     }
+    // the last in_flight buffers are not handed back: no pass is left to use them
     if (elect_one()) bulk_wait_all();                   // same lane every time (elect.sync picks the lowest)
     __syncwarp();
   } else {
@@ -562,7 +597,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
       int b, qt, v, nt; decode(t, b, qt, v, nt);
       const int n0 = nt * N;
       const int abuf = tcnt % NACC;
+      if (quarter == 0 && lane == 0) TC_TRACE(4u + grp, tcnt, 0u);   // epilogue group arrives at the tile
       mbar_wait(&acc_full[abuf], (tcnt / NACC) & 1);
+      if (quarter == 0 && lane == 0) TC_TRACE(4u + grp, tcnt, 1u);   // accumulator complete
       tc_fence_after();
       const uint32_t tacc = tmem_base + lane_base + abuf * ACC_COLS;
 #pragma unroll 1
@@ -576,12 +613,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
           if ((int)(pcnt & 1) != grp) continue;
           const int buf = pcnt % (uint32_t)nstg;
           uint8_t* my = stg + buf * pl.stg_bytes + er * SROWB;
-          mbar_wait(&stg_full[buf], (pcnt / (uint32_t)nstg) & 1);   // residual tile landed / buffer granted
 #pragma unroll
           for (int c0 = 0; c0 < PW; c0 += CW) {
             uint32_t r[32];
             if (CW == 32) tmem_ld32(tacc + mb * N + p0 + c0, r);
             else tmem_ld16(tacc + mb * N + p0 + c0, r);
+            if (c0 == 0) {                               // the accumulator load is in flight while the staging buffer is awaited
+              mbar_wait(&stg_full[buf], (pcnt / (uint32_t)nstg) & 1);   // residual tile landed / buffer granted
+              if (quarter == 0 && lane == 0 && mb == 0 && p0 < 2 * PW) TC_TRACE(4u + grp, tcnt, 2u);   // first pass of the group: staging buffer ready
+            }
             uint4 rr[CW / 8], rr2[CW / 8];
             if (has_res) {
 #pragma unroll
@@ -653,6 +693,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
       }
       tc_fence_before();
       __syncwarp();
+      if (quarter == 0 && lane == 0) TC_TRACE(4u + grp, tcnt, 3u);   // all passes of the tile done
       if (lane == 0) {                                  // one arrival per warp: accumulator buffer may be overwritten
         if (CG == 2) mbar_arrive_cluster(mapa_u32(smem_u32(&acc_empty[abuf]), 0));   // the leader's MMA warp waits for both CTAs
         else mbar_arrive(&acc_empty[abuf]);
@@ -669,6 +710,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
 
 // ------------------------------------------------------------------ host side
 int g_num_sms = 0;
+long long* g_tc_trace = nullptr;       // device buffer for HFG_TC_TRACE builds (hfgdbg_set_trace)
 
 int tc_num_sms() {
   if (!g_num_sms) {
@@ -756,7 +798,7 @@ int tc_env_int(const char* name, int dflt) { const char* e = getenv(name); retur
 // shared memory allows (Little's law: ~80 KB in flight per SM saturate HBM), trading staging slots above 3 for slab slots.
 void tc_ring_depths(int n, int ks, int kbw_tps, int nst, int nsl0, int nstg0, int slice_rows, int cg, bool resident, int* nsl, int* nstg) {
   *nsl = nsl0; *nstg = nstg0;
-  static const int want_nsl = tc_env_int("HFG_TC_NSL", 4), min_nstg = tc_env_int("HFG_TC_NSTG_MIN", 3);
+  static const int want_nsl = tc_env_int("HFG_TC_NSL", 0), min_nstg = tc_env_int("HFG_TC_NSTG_MIN", 3);
   if (!resident || want_nsl <= nsl0) return;
   auto fits = [&](int a, int b) { return (size_t)tc_plan(n, ks, kbw_tps, nst, a, b, slice_rows, cg).total <= kTcMaxSmem; };
   int a = nsl0, b = nstg0;
@@ -796,6 +838,9 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
   ka.tiles_q = (a.n_q + CG * MB * 128 - 1) / (CG * MB * 128);
   ka.w_base = a.w_base;
   ka.post_out = a.post_out; ka.post_f = a.post_f; ka.post_pcm = a.post_pcm;
+  ka.trace = g_tc_trace;
+  static const int stores_env = tc_env_int("HFG_TC_STORES", -1);
+  ka.store_in_flight = stores_env > 6 ? 6 : stores_env;
   const bool post_mode = a.post_out || a.post_pcm;
   if (post_mode && (a.post_f < 1 || a.post_f > 16)) return cudaErrorInvalidValue;
   if (post_mode && (a.out_stride != 1 || a.res || a.res2)) return cudaErrorInvalidValue;
@@ -825,7 +870,7 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
     int occ = 1;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kTcThreads, pl.total);
     if (e != cudaSuccess) return e;
-    constexpr int NACC = (2 * MB * N <= 512) ? 2 : 1;
+    constexpr int NACC = tc_nacc(MB, N);
     const int tmem_occ = 512 / (int)tc_tmem_cols(NACC * MB * N);
     if (occ > tmem_occ) occ = tmem_occ;
     occ_dev[dev] = occ < 1 ? 1 : occ;
@@ -986,6 +1031,8 @@ void tc_pack_weights(const float* w, int ntaps, int c_in, int c_out, int span, A
                   dst[o++] = bits;
                 }
 }
+
+void tc_set_trace(long long* dev) { g_tc_trace = dev; }
 
 cudaError_t launch_conv_tc(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out) {
   if (a.nvar < 1 || a.nvar > kMaxVariants) return cudaErrorInvalidValue;

@@ -993,6 +993,11 @@ int hfg_op_tapped_conv(int act, int engine, const void* x_dev, int B, int x_rows
   return HFG_OK;
 }
 
+#ifdef HFG_TC_TRACE
+// debug builds only (tools/trace_layer.py); not part of the C ABI
+void hfgdbg_set_trace(void* dev) { tc_set_trace((long long*)dev); }
+#endif
+
 int hfg_host_alloc(void** out, size_t bytes) {
   if (!out) return HFG_ERR_INVALID;
   cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault);

@@ -119,5 +119,6 @@ size_t tc_packed_weight_bytes(int c_in, int c_out, int ntaps);
 void tc_pack_weights(const float* w, int ntaps, int c_in, int c_out, int span, ActType act, void* dst_host);
 // returns cudaSuccess or an error; *msg (optional) receives a static description on failure
 cudaError_t launch_conv_tc(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out);
+void tc_set_trace(long long* dev);   // debug builds (-DHFG_TC_TRACE): device buffer of [6][64][8] clock stamps, see conv_tc.cu
 
 }  // namespace hfg
