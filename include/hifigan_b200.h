@@ -142,7 +142,7 @@ int hfg_stage_times_ms(hfg_handle h, float* out, int* n);
  *     mrf_mode 0: out = lrelu(v, out_slope); 1: acc = v; 2: acc += v; 3: out = lrelu((acc + v) / mrf_div, out_slope)
  *   engine 1, persistent tcgen05 kernel (16-bit only; x is stored already activated, in_slope must be 1):
  *     v = bias[co] + sum_j sum_ci x[b, q + tap_off[j], ci] * w[j][ci][co] + unact(res[...]) + res2[...]
- *     out = lrelu(v * out_scale, out_slope),   unact(y) = y >= 0 ? y : y * res_inv
+ *     out = lrelu(v * out_scale, out_slope),   unact(y) = y >= 0 ? y : y * res_inv     (0 < out_slope <= 1 <= res_inv)
  *   out is indexed [b, q*out_stride + out_off, co]; res, res2, acc like out. */
 int hfg_op_tapped_conv(int act, int engine, const void* x_dev, int B, int x_rows, int c_in,
                        const float* w_host, const float* bias_host, int c_out, int ntaps, const int* tap_off,

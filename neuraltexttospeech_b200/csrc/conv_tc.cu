@@ -251,6 +251,9 @@ template <> struct H2<__nv_bfloat16> {
 };
 
 __device__ __forceinline__ float lrelu_f(float v, float s) { return v >= 0.f ? v : v * s; }
+// two-instruction forms (FMUL + FMNMX) for slopes known to lie on one side of 1
+__device__ __forceinline__ float lrelu_le1(float v, float s) { return fmaxf(v, v * s); }   // 0 < s <= 1: leaky relu
+__device__ __forceinline__ float lrelu_ge1(float v, float s) { return fminf(v, v * s); }   // s >= 1: its inverse
 
 // ------------------------------------------------------------------ shared-memory plan
 struct TcSmemPlan {
@@ -635,18 +638,24 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
               for (int i = 0; i < CW / 8; ++i) rr2[i] = rp[i];
             }
             tmem_ld_wait();
+            if (quarter == 0 && lane == 0 && mb == 0 && p0 < 2 * PW && c0 == 0) TC_TRACE(4u + grp, tcnt, 4u);   // accumulator chunk in registers
             float vv[CW];
+            const float4* b4 = reinterpret_cast<const float4*>(bias_s + n0 + p0 + c0);   // 16-byte broadcast loads
 #pragma unroll
-            for (int i = 0; i < CW; ++i) vv[i] = __uint_as_float(r[i]) + bias_s[n0 + p0 + c0 + i];
+            for (int i = 0; i < CW / 4; ++i) {
+              const float4 bb = b4[i];
+              vv[4 * i + 0] = __uint_as_float(r[4 * i + 0]) + bb.x; vv[4 * i + 1] = __uint_as_float(r[4 * i + 1]) + bb.y;
+              vv[4 * i + 2] = __uint_as_float(r[4 * i + 2]) + bb.z; vv[4 * i + 3] = __uint_as_float(r[4 * i + 3]) + bb.w;
+            }
             if (has_res) {
               const float ri = ka.res_inv;
 #pragma unroll
               for (int i = 0; i < CW / 8; ++i) {
                 float2 f;
-                f = H2<T>::up(rr[i].x); vv[i * 8 + 0] += lrelu_f(f.x, ri); vv[i * 8 + 1] += lrelu_f(f.y, ri);
-                f = H2<T>::up(rr[i].y); vv[i * 8 + 2] += lrelu_f(f.x, ri); vv[i * 8 + 3] += lrelu_f(f.y, ri);
-                f = H2<T>::up(rr[i].z); vv[i * 8 + 4] += lrelu_f(f.x, ri); vv[i * 8 + 5] += lrelu_f(f.y, ri);
-                f = H2<T>::up(rr[i].w); vv[i * 8 + 6] += lrelu_f(f.x, ri); vv[i * 8 + 7] += lrelu_f(f.y, ri);
+                f = H2<T>::up(rr[i].x); vv[i * 8 + 0] += lrelu_ge1(f.x, ri); vv[i * 8 + 1] += lrelu_ge1(f.y, ri);
+                f = H2<T>::up(rr[i].y); vv[i * 8 + 2] += lrelu_ge1(f.x, ri); vv[i * 8 + 3] += lrelu_ge1(f.y, ri);
+                f = H2<T>::up(rr[i].z); vv[i * 8 + 4] += lrelu_ge1(f.x, ri); vv[i * 8 + 5] += lrelu_ge1(f.y, ri);
+                f = H2<T>::up(rr[i].w); vv[i * 8 + 6] += lrelu_ge1(f.x, ri); vv[i * 8 + 7] += lrelu_ge1(f.y, ri);
               }
             }
             if (has_res2) {
@@ -676,8 +685,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
               continue;
             }
             const float osc = ka.out_scale, osl = ka.out_slope;
+            if (osc != 1.0f) {                            // only the last conv of a stage scales (1 / num_kernels)
 #pragma unroll
-            for (int i = 0; i < CW; ++i) vv[i] = lrelu_f(vv[i] * osc, osl);
+              for (int i = 0; i < CW; ++i) vv[i] *= osc;
+            }
+#pragma unroll
+            for (int i = 0; i < CW; ++i) vv[i] = lrelu_le1(vv[i], osl);
 #pragma unroll
             for (int i = 0; i < CW / 8; ++i) {
               uint4 u;
@@ -686,9 +699,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
               *reinterpret_cast<uint4*>(my + (((c0 / 8 + i) ^ sx) * 16)) = u;
             }
           }
+          if (quarter == 0 && lane == 0 && mb == 0 && p0 < 2 * PW) TC_TRACE(4u + grp, tcnt, 5u);   // pass computed and staged
           fence_proxy_async();                          // staging writes -> visible to the TMA engine
           __syncwarp();
+          if (quarter == 0 && lane == 0 && mb == 0 && p0 < 2 * PW) TC_TRACE(4u + grp, tcnt, 6u);   // fenced
           if (lane == 0) mbar_arrive(&stg_done[buf]);   // one arrival per warp: hand the tile to the store warp
+          if (quarter == 0 && lane == 0 && mb == 0 && p0 < 2 * PW) TC_TRACE(4u + grp, tcnt, 7u);   // handed over
         }
       }
       tc_fence_before();
@@ -825,6 +841,8 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
   ka.min_off = mn; ka.span = mx - mn;
   if (ka.span > kTcMaxSpan) return cudaErrorInvalidValue;
   if ((a.res || a.res2) && a.out_stride != 1) return cudaErrorInvalidValue;
+  // the epilogue uses max / min forms of the leaky relu and of its inverse: slopes must lie on the right side of 1
+  if (!(a.out_slope > 0.f && a.out_slope <= 1.f) || (a.res && !(a.res_inv >= 1.f))) return cudaErrorInvalidValue;
   tc_boxes(MB * 128 + ka.span, &ka.box_rows, &ka.nbox);
   {
     int max_taps = 0;

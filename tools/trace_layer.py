@@ -30,7 +30,7 @@ torch.cuda.synchronize()
 t = trace.cpu().numpy().reshape(6, 64, 8)
 t0 = t[t > 0].min()
 names = {0: "slab", 1: "stg", 2: "mma", 3: "store", 4: "epi0", 5: "epi1"}
-ev = {0: ["issue"], 1: ["grant"], 2: ["arrive", "acc_free", "slab_in", "issued"], 3: ["first", "last"], 4: ["arrive", "acc_full", "stg_rdy", "done"], 5: ["arrive", "acc_full", "stg_rdy", "done"]}
+ev = {0: ["issue"], 1: ["grant"], 2: ["arrive", "acc_free", "slab_in", "issued"], 3: ["first", "last"], 4: ["arrive", "acc_full", "stg_rdy", "done", "ld", "staged", "fenced", "handed"], 5: ["arrive", "acc_full", "stg_rdy", "done", "ld", "staged", "fenced", "handed"]}
 print(f"C={c} k={k} d={dil} res={use_res} B={B} rows={rows}; clocks relative to the first stamp")
 for tile in range(4, 14):
     parts = []
