@@ -20,6 +20,8 @@ SOURCES = ("conv_ffma.cu", "conv_tc.cu", "engine.cu", "mel_frontend.cu")
 HEADERS = (os.path.join(CSRC, "kernels.cuh"), os.path.join(ROOT, "include", "hifigan_b200.h"))
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC"]
+if os.environ.get("HFG_BUILD_EPI_GROUPS"):       # experiment: number of 4-warp epilogue groups in conv_tc_kernel
+    NVCC_FLAGS.append("-DHFG_TC_EPI_GROUPS=" + os.environ["HFG_BUILD_EPI_GROUPS"])
 if os.environ.get("HFG_BUILD_TRACE") == "1":     # debug build: per-role clock stamps in conv_tc_kernel (tools/trace_layer.py)
     NVCC_FLAGS.append("-DHFG_TC_TRACE")
 

@@ -43,7 +43,12 @@ namespace hfg {
 
 namespace {
 
-constexpr int kTcThreads = 416;       // 13 warps: 4 producers/MMA, 2 x 4 epilogue, 1 store issuer
+#ifndef HFG_TC_EPI_GROUPS
+#define HFG_TC_EPI_GROUPS 2
+#endif
+constexpr int kEpiGroups = HFG_TC_EPI_GROUPS;                 // groups of 4 epilogue warps taking passes round-robin
+constexpr int kStoreWarp = 4 + 4 * kEpiGroups;                // warp index of the store issuer
+constexpr int kTcThreads = (kStoreWarp + 1) * 32;             // 4 producer/MMA warps, kEpiGroups x 4 epilogue warps, 1 store issuer
 constexpr int kTcMaxCout = 512;
 constexpr int kTcMaxSpan = 96;       // largest max_off - min_off supported (V1: 50, V3: 72)
 constexpr size_t kTcMaxSmem = 227 * 1024;
@@ -366,7 +371,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
     for (int s = 0; s < nsl; ++s) { mbar_init(&slice_full[s], 1); mbar_init(&slice_empty[s], 1); }
     for (int s = 0; s < NST; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
     for (int s = 0; s < nstg; ++s) { mbar_init(&stg_full[s], 1); mbar_init(&stg_empty[s], 1); mbar_init(&stg_done[s], 4); }
-    for (int s = 0; s < kTcMaxAcc; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 8 * CG); }
+    for (int s = 0; s < kTcMaxAcc; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 4 * kEpiGroups * CG); }
     fence_mbar_init();
     tma_prefetch_desc(&tm_x); tma_prefetch_desc(&tm_res); tma_prefetch_desc(&tm_out);
     if (CG == 2) tma_prefetch_desc(&tm_w);
@@ -544,7 +549,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
         }
       }
     }
-  } else if (warp == 12) {
+  } else if (warp == kStoreWarp) {
     // ===================== store issuer: TMA tensor store of every finished staging tile =====================
     // Up to two stores stay in flight: the buffer of pass p is handed back only once the store of pass p has finished
     // READING shared memory, which is checked two passes later (bulk groups retire in order).  Waiting for each store
@@ -613,7 +618,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
         const bool has_res = ka.has_res != 0 && q0 < ka.n_q;
 #pragma unroll 1
         for (int p0 = 0; p0 < N; p0 += PW, ++pcnt) {
-          if ((int)(pcnt & 1) != grp) continue;
+          if ((int)(pcnt % (uint32_t)kEpiGroups) != grp) continue;
           const int buf = pcnt % (uint32_t)nstg;
           uint8_t* my = stg + buf * pl.stg_bytes + er * SROWB;
 #pragma unroll
