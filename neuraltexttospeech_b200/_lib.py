@@ -88,9 +88,14 @@ def load():
     if _lib is not None:
         return _lib
     if not os.path.exists(LIB_PATH):
-        raise ImportError(
-            f"{LIB_PATH} is missing: build it with `python -m neuraltexttospeech_b200.build` "
-            "(or __graft_entry__.build()). There is no CPU / PyTorch fallback for the generator.")
+        # a fresh checkout (the .so is a git-ignored artefact): compile it in-tree if nvcc is here; never fall back
+        try:
+            from .build import build
+            build()
+        except Exception as e:
+            raise ImportError(
+                f"{LIB_PATH} is missing and could not be built ({e}): run `python -m neuraltexttospeech_b200.build` "
+                "(or __graft_entry__.build()). There is no CPU / PyTorch fallback for the generator.") from e
     lib = C.CDLL(LIB_PATH)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)          # AttributeError if the .so does not export it
