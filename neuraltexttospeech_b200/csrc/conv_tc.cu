@@ -56,6 +56,12 @@ constexpr size_t kTcMaxSmem = 227 * 1024;
 constexpr int kTcMaxAcc = 4;          // accumulator buffers in TMEM (acc_full / acc_empty barrier pairs)
 __host__ __device__ constexpr int tc_nacc(int mb, int n) { return 2 * mb * n <= 512 ? 2 : 1; }   // 4 buffers were tried: the epilogue, not the accumulator ring, paces the narrow layers
 
+// 128-row blocks handled by one epilogue pass: narrow tiles (N < 64) take several, so that a pass always moves ~64
+// values per thread (N = 32) and the per-pass fixed costs (barrier hand-offs, proxy fence, TMA issue) are paid half as often
+// staging ring depth when a pass covers rb row blocks: the table's NSTG counts 128-row buffers
+__host__ __device__ constexpr int tc_nstg(int nstg, int rb) { return nstg / rb < 3 ? 3 : nstg / rb; }
+__host__ __device__ constexpr int tc_rb(int n, int mb) { return (n >= 64 || mb < 2) ? 1 : 2; }   // a TMA box holds at most 256 rows
+
 __host__ __device__ constexpr uint32_t tc_tmem_cols(int need) { return need <= 32 ? 32 : need <= 64 ? 64 : need <= 128 ? 128 : need <= 256 ? 256 : 512; }
 
 __host__ __device__ inline int tc_rows_padded(int rows, int chunks) {
@@ -265,18 +271,18 @@ struct TcSmemPlan {
   int slice_rows;       // rows of one K-slice buffer (nbox * box_rows)
   int slice_bytes;
   int stage_bytes;      // one weight stage
-  int stg_bytes;        // one staging tile [128 rows][PW * 2 bytes]
+  int stg_bytes;        // one staging tile [RB * 128 rows][PW * 2 bytes]
   int off_stg, off_w, off_bias, off_bar;
   int total;
 };
 
-__host__ __device__ inline TcSmemPlan tc_plan(int n, int ks, int kbw, int nst, int nsl, int nstg, int slice_rows, int cg = 1) {
+__host__ __device__ inline TcSmemPlan tc_plan(int n, int ks, int kbw, int nst, int nsl, int nstg, int slice_rows, int cg = 1, int rb = 1) {
   TcSmemPlan p;
   const int pw = n < 64 ? n : 64;
   p.slice_rows = slice_rows;
   p.slice_bytes = slice_rows * ks * 2;            // multiple of the swizzle atom (slice_rows % 8 == 0)
   p.stage_bytes = (n / cg) * kbw * 2;     // a CTA of a pair stages half of the weight rows
-  p.stg_bytes = 128 * pw * 2;
+  p.stg_bytes = rb * 128 * pw * 2;
   int off = nsl * p.slice_bytes;
   off = (off + 1023) & ~1023;
   p.off_stg = off; off += nstg * p.stg_bytes;
@@ -335,6 +341,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
   constexpr int ROWB = KS * 2;                    // bytes per slab row within a slice (= swizzle width)
   constexpr int PW = N < 64 ? N : 64;             // output columns per epilogue pass
   constexpr int SROWB = PW * 2;                   // bytes per staging row (= swizzle width)
+  constexpr int RB = tc_rb(N, MB);                // 128-row blocks per epilogue pass
   constexpr int NACC = tc_nacc(MB, N);
   constexpr int ACC_COLS = MB * N;
   constexpr uint32_t TMEM_COLS = tc_tmem_cols(NACC * ACC_COLS);
@@ -344,7 +351,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
   static_assert(KS == 64 || KS == 32 || KS == 16, "K-slice = one swizzle row");
   static_assert(N % PW == 0, "pass width");
   const int nsl = ka.nsl, nstg = ka.nstg;          // runtime ring depths (the template values are the table defaults)
-  const TcSmemPlan pl = tc_plan(N, KS, KBW * TPS, NST, nsl, nstg, ka.nbox * ka.box_rows, CG);
+  const TcSmemPlan pl = tc_plan(N, KS, KBW * TPS, NST, nsl, nstg, ka.nbox * ka.box_rows, CG, RB);
 
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* slab = smem;
@@ -531,7 +538,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
     uint32_t pcnt = 0;
     for (int t = tile0; t < ka.total_tiles; t += tile_step) {
       int b, qt, v, nt; decode(t, b, qt, v, nt);
-      for (int mb = 0; mb < MB; ++mb) {
+      for (int mb = 0; mb < MB; mb += RB) {
         const int q0 = qt * (MB * 128) + mb * 128;
         for (int p0 = 0; p0 < N; p0 += PW, ++pcnt) {
           const int buf = pcnt % (uint32_t)nstg;
@@ -562,14 +569,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
     for (int t = tile0; t < ka.total_tiles; t += tile_step) {
       int b, qt, v, nt; decode(t, b, qt, v, nt);
       const int out_off = ka.var[v].out_off;
-      for (int mb = 0; mb < MB; ++mb) {
+      for (int mb = 0; mb < MB; mb += RB) {
         const int q0 = qt * (MB * 128) + mb * 128;
         for (int p0 = 0; p0 < N; p0 += PW, ++pcnt) {
           const int buf = pcnt % (uint32_t)nstg;
           mbar_wait(&stg_done[buf], (pcnt / (uint32_t)nstg) & 1);
           if (elect_one()) {
             if (mb == 0 && p0 == 0) TC_TRACE(3u, (uint32_t)((t - tile0) / tile_step), 0u);   // first finished pass of the tile seen by the store warp
-            if (mb == MB - 1 && p0 + PW >= N) TC_TRACE(3u, (uint32_t)((t - tile0) / tile_step), 1u);   // last one
+            if (mb + RB >= MB && p0 + PW >= N) TC_TRACE(3u, (uint32_t)((t - tile0) / tile_step), 1u);   // last one
             if (q0 < ka.n_q && ka.post_out == nullptr && ka.post_pcm == nullptr)
               tma_store_4d(&tm_out, stg + buf * pl.stg_bytes, nt * N + p0, out_off, q0, b);
             bulk_commit();                              // one (possibly empty) group per pass keeps the group count = pass count
@@ -611,22 +618,24 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
       tc_fence_after();
       const uint32_t tacc = tmem_base + lane_base + abuf * ACC_COLS;
 #pragma unroll 1
-      for (int mb = 0; mb < MB; ++mb) {
+      for (int mb = 0; mb < MB; mb += RB) {
         const int q0 = qt * (MB * 128) + mb * 128;
-        const int q = q0 + er;
-        const bool valid = q < ka.n_q;
         const bool has_res = ka.has_res != 0 && q0 < ka.n_q;
 #pragma unroll 1
         for (int p0 = 0; p0 < N; p0 += PW, ++pcnt) {
           if ((int)(pcnt % (uint32_t)kEpiGroups) != grp) continue;
           const int buf = pcnt % (uint32_t)nstg;
-          uint8_t* my = stg + buf * pl.stg_bytes + er * SROWB;
+#pragma unroll 1
+          for (int rb = 0; rb < RB; ++rb) {              // the pass's 128-row blocks (one unless the tile is narrow)
+          const int q = q0 + rb * 128 + er;
+          const bool valid = q < ka.n_q;
+          uint8_t* my = stg + buf * pl.stg_bytes + (rb * 128 + er) * SROWB;   // 128 rows keep the swizzle phase: sx is unchanged
 #pragma unroll
           for (int c0 = 0; c0 < PW; c0 += CW) {
             uint32_t r[32];
-            if (CW == 32) tmem_ld32(tacc + mb * N + p0 + c0, r);
-            else tmem_ld16(tacc + mb * N + p0 + c0, r);
-            if (c0 == 0) {                               // the accumulator load is in flight while the staging buffer is awaited
+            if (CW == 32) tmem_ld32(tacc + (mb + rb) * N + p0 + c0, r);
+            else tmem_ld16(tacc + (mb + rb) * N + p0 + c0, r);
+            if (rb == 0 && c0 == 0) {                    // the accumulator load is in flight while the staging buffer is awaited
               mbar_wait(&stg_full[buf], (pcnt / (uint32_t)nstg) & 1);   // residual tile landed / buffer granted
               if (quarter == 0 && lane == 0 && mb == 0 && p0 < 2 * PW) TC_TRACE(4u + grp, tcnt, 2u);   // first pass of the group: staging buffer ready
             }
@@ -704,6 +713,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
               *reinterpret_cast<uint4*>(my + (((c0 / 8 + i) ^ sx) * 16)) = u;
             }
           }
+          }
           if (quarter == 0 && lane == 0 && mb == 0 && p0 < 2 * PW) TC_TRACE(4u + grp, tcnt, 5u);   // pass computed and staged
           fence_proxy_async();                          // staging writes -> visible to the TMA engine
           __syncwarp();
@@ -775,12 +785,12 @@ bool make_map3(CUtensorMap* m, ActType act, const void* base, int C, int rows, i
 }
 
 // rank-4 map over outputs viewed as [B][q][u][C] (row q*u + phase), box = [box_c][1][128][1]
-bool make_map4(CUtensorMap* m, ActType act, const void* base, int C, int u, int nq, int B, int box_c) {
+bool make_map4(CUtensorMap* m, ActType act, const void* base, int C, int u, int nq, int B, int box_c, int box_rows = 128) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return false;
   cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)u, (cuuint64_t)nq, (cuuint64_t)B};
   cuuint64_t gstr[3] = {(cuuint64_t)C * 2, (cuuint64_t)C * 2 * u, (cuuint64_t)C * 2 * u * (cuuint64_t)nq};
-  cuuint32_t box[4] = {(cuuint32_t)box_c, 1, 128, 1};
+  cuuint32_t box[4] = {(cuuint32_t)box_c, 1, (cuuint32_t)box_rows, 1};
   cuuint32_t est[4] = {1, 1, 1, 1};
   return fn(m, act == ACT_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, const_cast<void*>(base), gdim, gstr,
             box, est, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(box_c * 2), CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -817,11 +827,11 @@ int tc_env_int(const char* name, int dflt) { const char* e = getenv(name); retur
 // (C <= 64: the HBM-bound layers) have per-tile MMA time far below the latency of one slab load, so with the table's
 // two slab slots only ONE load is in flight per SM while the other slot is consumed: their depth is raised as far as
 // shared memory allows (Little's law: ~80 KB in flight per SM saturate HBM), trading staging slots above 3 for slab slots.
-void tc_ring_depths(int n, int ks, int kbw_tps, int nst, int nsl0, int nstg0, int slice_rows, int cg, bool resident, int* nsl, int* nstg) {
+void tc_ring_depths(int n, int ks, int kbw_tps, int nst, int nsl0, int nstg0, int slice_rows, int cg, int rb, bool resident, int* nsl, int* nstg) {
   *nsl = nsl0; *nstg = nstg0;
   static const int want_nsl = tc_env_int("HFG_TC_NSL", 0), min_nstg = tc_env_int("HFG_TC_NSTG_MIN", 3);
   if (!resident || want_nsl <= nsl0) return;
-  auto fits = [&](int a, int b) { return (size_t)tc_plan(n, ks, kbw_tps, nst, a, b, slice_rows, cg).total <= kTcMaxSmem; };
+  auto fits = [&](int a, int b) { return (size_t)tc_plan(n, ks, kbw_tps, nst, a, b, slice_rows, cg, rb).total <= kTcMaxSmem; };
   int a = nsl0, b = nstg0;
   while (a < want_nsl) {
     if (fits(a + 1, b)) { ++a; continue; }
@@ -855,8 +865,9 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
     const int stages = (C_IN / KS) * ((max_taps + TPS - 1) / TPS) * (KS / KBW);
     ka.resident = (a.nvar == 1 && a.c_out == N && stages <= NST) ? 1 : 0;
   }
-  tc_ring_depths(N, KS, KBW * TPS, NST, NSL, NSTG, ka.nbox * ka.box_rows, CG, ka.resident != 0, &ka.nsl, &ka.nstg);
-  const TcSmemPlan pl = tc_plan(N, KS, KBW * TPS, NST, ka.nsl, ka.nstg, ka.nbox * ka.box_rows, CG);
+  constexpr int RB = tc_rb(N, MB);
+  tc_ring_depths(N, KS, KBW * TPS, NST, NSL, tc_nstg(NSTG, RB), ka.nbox * ka.box_rows, CG, RB, ka.resident != 0, &ka.nsl, &ka.nstg);
+  const TcSmemPlan pl = tc_plan(N, KS, KBW * TPS, NST, ka.nsl, ka.nstg, ka.nbox * ka.box_rows, CG, RB);
   if ((size_t)pl.total > kTcMaxSmem) return cudaErrorInvalidConfiguration;
   ka.tiles_q = (a.n_q + CG * MB * 128 - 1) / (CG * MB * 128);
   ka.w_base = a.w_base;
@@ -875,8 +886,8 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
     if (!make_map_w(&tm_w, a.w_base, a.w_bytes, (N / CG) * KBW * 2 / 256)) return cudaErrorNotSupported;
   }
   if (!make_map3(&tm_x, act, a.x, C_IN, a.x_rows, a.B, KS, ka.box_rows)) return cudaErrorNotSupported;
-  if (!make_map4(&tm_out, act, a.out, a.c_out, a.out_stride, a.n_q, a.B, PW)) return cudaErrorNotSupported;
-  if (a.res) { if (!make_map4(&tm_res, act, a.res, a.c_out, 1, a.n_q, a.B, PW)) return cudaErrorNotSupported; }
+  if (!make_map4(&tm_out, act, a.out, a.c_out, a.out_stride, a.n_q, a.B, PW, RB * 128)) return cudaErrorNotSupported;
+  if (a.res) { if (!make_map4(&tm_res, act, a.res, a.c_out, 1, a.n_q, a.B, PW, RB * 128)) return cudaErrorNotSupported; }
   else tm_res = tm_out;
   if (CG == 1) tm_w = tm_out;
   auto kern = conv_tc_kernel<T, C_IN, N, MB, KS, KBW, TPS, NST, NSL, NSTG, CG>;
@@ -1014,7 +1025,8 @@ bool tc_config(int c_in, int c_out, int span, TcConfig* cfg) {
       const TcConfig& c = r.cfg;
       int br, nb;
       tc_boxes(c.mb * 128 + span, &br, &nb);
-      if ((size_t)tc_plan(c.n, c.ks, c.kbw * c.tps, c.nst, c.nsl, c.nstg, br * nb, c.cg).total <= kTcMaxSmem) {
+      const int rb = tc_rb(c.n, c.mb);
+      if ((size_t)tc_plan(c.n, c.ks, c.kbw * c.tps, c.nst, c.nsl, tc_nstg(c.nstg, rb), br * nb, c.cg, rb).total <= kTcMaxSmem) {
         if (cfg) *cfg = c;
         return true;
       }
