@@ -19,17 +19,22 @@
 //           dilated conv is the SAME slab addressed at row offset tap_off[j]-min_off (the swizzle is a
 //           function of the absolute smem address, so an unaligned descriptor start is legal): no im2col.
 //   warp 1  weight producer: host-prepacked weight stages [KBW/8 chunks][N rows][16 B] through an NST-deep
-//           ring with cp.async.bulk + mbarrier complete_tx.
-//   warp 2  MMA issuer: one thread issues tcgen05.mma (cta_group::1, kind::f16, M=128, N, K=16) into TMEM
-//           accumulators (NACC buffers of MB x N columns); tcgen05.commit releases weight stages / slab
+//           ring with cp.async.bulk + mbarrier complete_tx (pair mode: TMA 2-D loads of each CTA's half);
+//           weights that fit the ring and are shared by every tile are loaded once (resident mode).
+//   warp 2  MMA issuer: one thread issues tcgen05.mma (kind::f16, M=128 or 256 for a CTA pair, N, K=16) into
+//           TMEM accumulators (NACC buffers of MB x N columns); tcgen05.commit releases weight stages / slab
 //           slices and hands the accumulator to the epilogue.
 //   warp 3  staging producer: TMA-loads the residual tile of each epilogue pass into the staging ring.
-//   warps 4-7 epilogue: tcgen05.ld (one TMEM lane quarter each, thread = output row) -> +bias -> +residual
-//           (model.py:79,111) -> +MRF partial sum, *1/num_kernels (model.py:161-167) -> activation for the
-//           consumer -> 16-bit, in place in the swizzled staging tile -> TMA tensor store.
+//   warps 4-11 epilogue, two groups of four taking alternate passes: tcgen05.ld (one TMEM lane quarter per
+//           warp, thread = output row) -> +bias -> +residual (model.py:79,111) -> +MRF partial sum,
+//           *1/num_kernels (model.py:161-167) -> activation for the consumer -> 16-bit, in place in the
+//           swizzled staging tile; conv_post mode: tanh -> fp32 / 16-bit PCM samples (model.py:170-171).
+//   warp 12 store issuer: TMA tensor store of every finished staging tile, two stores in flight.
 //
 // Loads of tile i+1, MMAs of tile i and the epilogue of tile i-1 overlap (slab ring, TMEM double
-// buffering where 2*MB*N <= 512 columns, NSTG-deep staging ring).
+// buffering where 2*MB*N <= 512 columns, NSTG-deep staging ring).  CG = 2 runs the kernel as CTA pairs
+// (cta_group::2).  Every launch is a programmatic dependent launch: the prologue overlaps the previous
+// layer's drain (griddepcontrol).
 #include <cuda.h>
 #include <cstdio>
 #include <cstdlib>
