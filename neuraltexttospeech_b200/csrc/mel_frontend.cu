@@ -8,11 +8,18 @@
 //     -> log(clip(., 1e-5))                                     dynamic_range_compression, audio_processing_tf.py:27-32
 // Output layout = the generator's input layout, [B, T, n_mel] fp32 channels-last, so wav -> mel -> wav runs on device.
 //
-// One CTA = two consecutive frames of one utterance: the two real frames ride one complex FFT (z = a + i b;
-// A[k] = (Z[k] + conj Z[N-k]) / 2, B[k] = (Z[k] - conj Z[N-k]) / 2i).  The FFT is a radix-4 Stockham autosort in
-// shared memory (N/4 threads, one butterfly per thread per pass, twiddles from a host-computed fp64-accurate table);
-// the power spectra stay in shared memory and each (frame, mel bin) is one thread's dot product over the triangle's
-// non-zero span.  HBM traffic is the compulsory one: the waveform once (frame overlap is served by L2) and the mels.
+// Two consecutive real frames of one utterance ride one complex FFT (z = a + i b;
+// A[k] = (Z[k] + conj Z[N-k]) / 2, B[k] = (Z[k] - conj Z[N-k]) / 2i).  HBM traffic is the compulsory one: the waveform
+// once (frame overlap is served by L1/L2) and the mels.  Two kernels:
+//   * fft_length 1024 (the reference's configuration): mel_frontend_r16_kernel.  64 threads per FFT, 16 points per
+//     thread in registers: Stockham passes of radix 16, 16, 4 (two shared-memory exchanges instead of five, padded
+//     rows so every exchange is conflict-free, 64-thread named barriers), first pass straight from global memory
+//     with the second frame's samples taken from the first frame's registers (hop 256 = 4 x 64).  Four FFTs (eight
+//     frames) per CTA.  The filterbank is a host-built list of (mel bin, span chunk) items of bounded length so that
+//     the 64 threads get equal work; partial sums are combined in a fixed order (deterministic).
+//   * fft_length 256 / 4096: mel_frontend_kernel, a radix-4 Stockham autosort in shared memory (N/4 threads, one
+//     butterfly per thread per pass), one thread per (frame, mel bin) dot product.
+// Twiddles come from a host-computed fp64-accurate table in both.
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -34,6 +41,12 @@ struct MelKArgs {
   const int* fb_start;   // [n_mel] first spectrogram bin of the span
   const int* fb_len;     // [n_mel]
   int fb_stride;
+  const float2* tw16;    // r16 kernel: [16][16] w^(4 r k) (pass 2) then [3][256] w^(r j), r = 1..3 (pass 3): lane-contiguous
+  const float* fb_wt;    // r16 kernel: item weights transposed, [chunk][item_stride]: lanes (items) read consecutive floats
+  int item_stride;
+  const int4* items;     // r16 kernel: (mel bin, first spectrogram bin, length, -) chunks of the triangles
+  const int2* item_of;   // r16 kernel: [n_mel] (first item, item count) of each mel bin
+  int n_items;
   int n_samples, T, n_mel, frame_length, frame_step;
   float floor_;          // 1e-5
 };
@@ -106,6 +119,161 @@ __global__ void __launch_bounds__(N / 4) mel_frontend_kernel(const MelKArgs a) {
   }
 }
 
+// ---------------------------------------------------------------- fft_length 1024: radix 16 x 16 x 4 in registers
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+
+// forward 4-point DFT in place: (a, b, c, d) -> (Y0, Y1, Y2, Y3)
+__device__ __forceinline__ void dft4(float2& a, float2& b, float2& c, float2& d) {
+  const float2 s02 = cadd(a, c), d02 = csub(a, c), s13 = cadd(b, d), d13 = csub(b, d);
+  a = cadd(s02, s13);
+  b = make_float2(d02.x + d13.y, d02.y - d13.x);       // d02 - i d13
+  c = csub(s02, s13);
+  d = make_float2(d02.x - d13.y, d02.y + d13.x);       // d02 + i d13
+}
+
+// forward 16-point DFT in place; on return u[4 c + d] holds Y[c + 4 d]
+__device__ __forceinline__ void dft16(float2 (&u)[16]) {
+  constexpr float C1 = 0.92387953251128674f, S1 = 0.38268343236508977f, H = 0.70710678118654752f;
+#pragma unroll
+  for (int b = 0; b < 4; ++b) dft4(u[b], u[4 + b], u[8 + b], u[12 + b]);      // u[4 c + b] = t[b][c]
+  // t[b][c] *= W16^(b c)
+  u[4 * 1 + 1] = cmul(u[4 * 1 + 1], make_float2(C1, -S1));                      // e = 1
+  u[4 * 1 + 2] = cmul(u[4 * 1 + 2], make_float2(H, -H));                        // e = 2
+  u[4 * 1 + 3] = cmul(u[4 * 1 + 3], make_float2(S1, -C1));                      // e = 3
+  u[4 * 2 + 1] = cmul(u[4 * 2 + 1], make_float2(H, -H));                        // e = 2
+  u[4 * 2 + 2] = make_float2(u[4 * 2 + 2].y, -u[4 * 2 + 2].x);                  // e = 4: * -i
+  u[4 * 2 + 3] = cmul(u[4 * 2 + 3], make_float2(-H, -H));                       // e = 6
+  u[4 * 3 + 1] = cmul(u[4 * 3 + 1], make_float2(S1, -C1));                      // e = 3
+  u[4 * 3 + 2] = cmul(u[4 * 3 + 2], make_float2(-H, -H));                       // e = 6
+  u[4 * 3 + 3] = cmul(u[4 * 3 + 3], make_float2(-C1, S1));                      // e = 9
+#pragma unroll
+  for (int c = 0; c < 4; ++c) dft4(u[4 * c], u[4 * c + 1], u[4 * c + 2], u[4 * c + 3]);
+}
+
+constexpr int kR16Fft = 4;                 // FFTs (frame pairs) per CTA
+constexpr int kR16Row = 1024 + 128;        // float2 per FFT buffer: 16-element rows padded by 2 (see phys)
+constexpr int kR16Partial = 640;           // partial sums of the filterbank items live above the 513 power bins
+constexpr int kR16MaxItems = 448;
+
+__device__ __forceinline__ int phys(int i) { return i + 2 * (i >> 4); }
+__device__ __forceinline__ void group_sync(int g) {        // immediate ids: a register operand would reserve all 16 barriers
+  switch (g) {
+    case 0: asm volatile("bar.sync 1, 64;" ::: "memory"); break;
+    case 1: asm volatile("bar.sync 2, 64;" ::: "memory"); break;
+    case 2: asm volatile("bar.sync 3, 64;" ::: "memory"); break;
+    default: asm volatile("bar.sync 4, 64;" ::: "memory"); break;
+  }
+}
+
+// HOP4: frame_length == 1024 and frame_step == 256, so the second frame's samples are the first frame's, 4 registers on
+template <bool HOP4>
+__global__ void __launch_bounds__(64 * kR16Fft, 5) mel_frontend_r16_kernel(const MelKArgs a) {
+  constexpr int N = 1024;
+  __shared__ __align__(16) float2 r16sm[kR16Fft * kR16Row];
+  const int g = threadIdx.x >> 6, j = threadIdx.x & 63;
+  float2* sm = r16sm + g * kR16Row;
+  const int b = blockIdx.y, f0 = (blockIdx.x * kR16Fft + g) * 2;
+  if (f0 >= a.T) return;                                   // whole 64-thread group: its barrier is never used
+  const bool two = f0 + 1 < a.T;
+  const float* xa = a.wav + (size_t)b * a.n_samples + (size_t)f0 * a.frame_step;
+  float2 u[16];
+  // ---- pass 1 (ns = 1): u_r = z[j + 64 r], no twiddles; out[16 j + q]
+  if (HOP4) {
+    float x[20];
+#pragma unroll
+    for (int r = 0; r < 16; ++r) x[r] = __ldg(xa + j + 64 * r);
+#pragma unroll
+    for (int r = 16; r < 20; ++r) x[r] = two ? __ldg(xa + j + 64 * r) : 0.f;
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+      const float w = __ldg(a.window + j + 64 * r);
+      u[r] = make_float2(x[r] * w, two ? x[r + 4] * w : 0.f);
+    }
+  } else {
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+      const int i = j + 64 * r;
+      float2 z = make_float2(0.f, 0.f);
+      if (i < a.frame_length) {
+        const float w = __ldg(a.window + i);
+        z.x = __ldg(xa + i) * w;
+        if (two) z.y = __ldg(xa + i + a.frame_step) * w;
+      }
+      u[r] = z;
+    }
+  }
+  dft16(u);
+  {
+    float4* row = reinterpret_cast<float4*>(sm + 18 * j);  // phys(16 j) = 18 j: 16-byte aligned, lanes 144 B apart
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {                          // Y[2p], Y[2p+1]; Y[c + 4 d] sits in u[4 c + d]
+      const float2 y0 = u[4 * ((2 * p) & 3) + ((2 * p) >> 2)], y1 = u[4 * ((2 * p + 1) & 3) + ((2 * p + 1) >> 2)];
+      row[p] = make_float4(y0.x, y0.y, y1.x, y1.y);
+    }
+  }
+  group_sync(g);
+  // ---- pass 2 (ns = 16): u_r = in[j + 64 r] * w^(4 r k), k = j mod 16; out[(j / 16) 256 + k + 16 q]
+  const int k2 = j & 15;
+  {
+    const int base = j + 2 * (j >> 4);                     // phys(j + 64 r) = base + 72 r
+    u[0] = sm[base];
+#pragma unroll
+    for (int r = 1; r < 16; ++r) u[r] = cmul(sm[base + 72 * r], __ldg(a.tw16 + 16 * r + k2));
+  }
+  dft16(u);
+  group_sync(g);                                           // everyone has read: the exchange is in place
+  {
+    float2* o = sm + (j >> 4) * 288 + k2;                  // phys((j / 16) 256 + k + 16 q) = (j / 16) 288 + k + 18 q
+#pragma unroll
+    for (int q = 0; q < 16; ++q) o[18 * q] = u[4 * (q & 3) + (q >> 2)];
+  }
+  group_sync(g);
+  // ---- pass 3 (ns = 256, radix 4): butterfly jj = j + 64 i reads and writes the same four slots jj + 256 r
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int jj = j + 64 * i;
+    float2* p = sm + jj + 2 * (jj >> 4);                   // phys(jj + 256 r) = phys(jj) + 288 r
+    float2 v0 = p[0];
+    float2 v1 = cmul(p[288], __ldg(a.tw16 + 256 + jj));
+    float2 v2 = cmul(p[576], __ldg(a.tw16 + 512 + jj));
+    float2 v3 = cmul(p[864], __ldg(a.tw16 + 768 + jj));
+    dft4(v0, v1, v2, v3);
+    p[0] = v0; p[288] = v1; p[576] = v2; p[864] = v3;
+  }
+  group_sync(g);
+  // ---- the two power spectra, in place: slot k <- (|A[k]|^2, |B[k]|^2); slot k and N - k are touched by this k only
+  for (int k = j; k <= N / 2; k += 64) {
+    const float2 z = sm[phys(k)], zc = sm[phys((N - k) & (N - 1))];
+    const float ar = 0.5f * (z.x + zc.x), ai = 0.5f * (z.y - zc.y);
+    const float br = 0.5f * (z.y + zc.y), bi = 0.5f * (zc.x - z.x);
+    sm[phys(k)] = make_float2(ar * ar + ai * ai, br * br + bi * bi);
+  }
+  group_sync(g);
+  // ---- filterbank: bounded-length chunks of the triangles, then a fixed-order sum per mel bin
+  for (int it = j; it < a.n_items; it += 64) {
+    const int4 d = __ldg(a.items + it);                    // (mel bin, first bin, length, -)
+    const float* w = a.fb_wt + it;
+    float pa = 0.f, pb = 0.f;
+    for (int q = 0; q < d.z; ++q) {
+      const float2 p = sm[phys(d.y + q)];
+      const float wq = __ldg(w + q * a.item_stride);
+      pa = fmaf(p.x, wq, pa);
+      pb = fmaf(p.y, wq, pb);
+    }
+    sm[kR16Partial + it] = make_float2(pa, pb);
+  }
+  group_sync(g);
+  for (int m = j; m < a.n_mel; m += 64) {
+    const int2 io = __ldg(a.item_of + m);
+    float pa = 0.f, pb = 0.f;
+    for (int q = 0; q < io.y; ++q) { const float2 p = sm[kR16Partial + io.x + q]; pa += p.x; pb += p.y; }
+    float* dst = a.mel + ((size_t)b * a.T + f0) * a.n_mel + m;
+    dst[0] = logf(fmaxf(pa, a.floor_));
+    if (two) dst[a.n_mel] = logf(fmaxf(pb, a.floor_));
+  }
+}
+
 thread_local std::string g_mel_create_error;
 
 }  // namespace
@@ -119,6 +287,12 @@ struct hfg_mel_ctx {
   float* d_fbw = nullptr;
   int* d_fbstart = nullptr;
   int* d_fblen = nullptr;
+  int4* d_items = nullptr;
+  float2* d_tw16 = nullptr;
+  float* d_fbwt = nullptr;
+  int item_stride = 0;
+  int2* d_item_of = nullptr;
+  int n_items = 0;
   cudaStream_t stream = nullptr;
   float* d_wav = nullptr; size_t d_wav_bytes = 0;
   float* d_mel = nullptr; size_t d_mel_bytes = 0;
@@ -205,6 +379,40 @@ int hfg_mel_create(const hfg_mel_config* cfg, int device, hfg_mel_handle* out) {
   if (e == cudaSuccess) e = up((void**)&h->d_fbw, fbw.data(), fbw.size() * sizeof(float));
   if (e == cudaSuccess) e = up((void**)&h->d_fbstart, start.data(), start.size() * sizeof(int));
   if (e == cudaSuccess) e = up((void**)&h->d_fblen, len.data(), len.size() * sizeof(int));
+  if (N == 1024) {
+    // work items of the r16 kernel: the smallest chunk length that fits the triangles into two rounds of 64 threads
+    std::vector<int4> items;
+    std::vector<int2> item_of(M);
+    for (int chunk = 4;; ++chunk) {
+      items.clear();
+      for (int m = 0; m < M; ++m) {
+        item_of[m] = make_int2((int)items.size(), 0);
+        for (int q0 = 0; q0 < len[m]; q0 += chunk) {
+          items.push_back(make_int4(m, start[m] + q0, std::min(chunk, len[m] - q0), m * stride + q0));
+          ++item_of[m].y;
+        }
+      }
+      if ((int)items.size() <= 128 || chunk >= nbins) break;
+    }
+    if ((int)items.size() > kR16MaxItems) { hfg_mel_destroy(h); return mfail(nullptr, HFG_ERR_UNSUPPORTED, "too many mel channels for the fft_length 1024 kernel"); }
+    h->n_items = (int)items.size();
+    if (items.empty()) items.push_back(make_int4(0, 0, 0, 0));
+    int chunk_len = 1;
+    for (const int4& it : items) chunk_len = std::max(chunk_len, it.z);
+    h->item_stride = ((int)items.size() + 31) / 32 * 32;
+    std::vector<float> wt((size_t)chunk_len * h->item_stride, 0.f);
+    for (size_t i = 0; i < items.size(); ++i)
+      for (int q = 0; q < items[i].z; ++q) wt[(size_t)q * h->item_stride + i] = fbw[(size_t)items[i].w + q];
+    std::vector<float2> tw16(1024);
+    for (int r = 0; r < 16; ++r)
+      for (int k = 0; k < 16; ++k) tw16[16 * r + k] = tw[(4 * r * k) % N];
+    for (int r = 1; r < 4; ++r)
+      for (int jj = 0; jj < 256; ++jj) tw16[256 * r + jj] = tw[(r * jj) % N];
+    if (e == cudaSuccess) e = up((void**)&h->d_tw16, tw16.data(), tw16.size() * sizeof(float2));
+    if (e == cudaSuccess) e = up((void**)&h->d_fbwt, wt.data(), wt.size() * sizeof(float));
+    if (e == cudaSuccess) e = up((void**)&h->d_items, items.data(), items.size() * sizeof(int4));
+    if (e == cudaSuccess) e = up((void**)&h->d_item_of, item_of.data(), item_of.size() * sizeof(int2));
+  }
   if (e != cudaSuccess) { hfg_mel_destroy(h); return mfail(nullptr, HFG_ERR_CUDA, "mel front-end setup failed: %s", cudaGetErrorString(e)); }
   *out = h;
   return HFG_OK;
@@ -235,7 +443,13 @@ int hfg_mel_forward(hfg_mel_handle h, const float* wav_dev, int B, long long n_s
   const size_t smem = (size_t)2 * N * sizeof(float2);
   cudaError_t e = cudaSuccess;
   if (N == 256) mel_frontend_kernel<256><<<grid, 64, smem, s>>>(a);
-  else if (N == 1024) mel_frontend_kernel<1024><<<grid, 256, smem, s>>>(a);
+  else if (N == 1024) {
+    a.items = h->d_items; a.item_of = h->d_item_of; a.n_items = h->n_items;
+    a.tw16 = h->d_tw16; a.fb_wt = h->d_fbwt; a.item_stride = h->item_stride;
+    const dim3 g16((unsigned)((T + 2 * kR16Fft - 1) / (2 * kR16Fft)), (unsigned)B);
+    if (a.frame_length == 1024 && a.frame_step == 256) mel_frontend_r16_kernel<true><<<g16, 64 * kR16Fft, 0, s>>>(a);
+    else mel_frontend_r16_kernel<false><<<g16, 64 * kR16Fft, 0, s>>>(a);
+  }
   else {
     e = cudaFuncSetAttribute(mel_frontend_kernel<4096>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e == cudaSuccess) mel_frontend_kernel<4096><<<grid, 1024, smem, s>>>(a);
@@ -284,6 +498,10 @@ void hfg_mel_destroy(hfg_mel_handle h) {
   if (h->d_fbw) cudaFree(h->d_fbw);
   if (h->d_fbstart) cudaFree(h->d_fbstart);
   if (h->d_fblen) cudaFree(h->d_fblen);
+  if (h->d_items) cudaFree(h->d_items);
+  if (h->d_tw16) cudaFree(h->d_tw16);
+  if (h->d_fbwt) cudaFree(h->d_fbwt);
+  if (h->d_item_of) cudaFree(h->d_item_of);
   if (h->d_wav) cudaFree(h->d_wav);
   if (h->d_mel) cudaFree(h->d_mel);
   if (h->stream) cudaStreamDestroy(h->stream);
