@@ -109,8 +109,12 @@ int hfg_forward_host_pcm16(hfg_handle h, const float* mel_host, int B, int T, in
 
 /* Options: "micro_batch" = utterances per forward of hfg_forward_host (0 = auto, the default: hfg_auto_micro_batch);
  * "stage_timing" 0/1; "cuda_graphs" 0/1 (default 1: launch-bound micro-batches of hfg_forward_host, <= 8192 frames,
- * are replayed from a CUDA graph captured on their second use); "force_ffma" 0/1 and "auto_fold" 0/1 (both need a
- * new hfg_finalize_weights). */
+ * are replayed from a CUDA graph captured on their second use); "concurrent_resblocks" = largest B*T in frames
+ * (default 2048, 0 = never) for which the resblocks of a stage -- independent up to their last conv, reference
+ * HiFiGAN_TF/model.py:161-166 -- run as concurrent chains on internal streams forked from and joined to the caller's
+ * stream (same kernels, same bits; the workspace holds two more P/Q/T sets per extra chain, so query
+ * hfg_workspace_bytes after changing it); "force_ffma" 0/1 and "auto_fold" 0/1 (both need a new
+ * hfg_finalize_weights). */
 int hfg_set_option(hfg_handle h, const char* key, long long value);
 
 /* Which kernel family each layer was bound to by hfg_finalize_weights: lines "<layer>:<tc|ffma|post>\n"

@@ -95,6 +95,12 @@ struct hfg_ctx {
   bool force_ffma = false;
   bool auto_fold = true;       // per-layer fold factor from fold_cost (option "auto_fold")
   bool need_acc = true, need_sum = false;
+  // launch-bound forwards (B*T <= chain_frames): the resblocks of a stage are independent chains up to their last conv
+  // (reference model.py:161-166 sums rb_j(x) over j), so chain j >= 1 runs on its own stream with its own scratch
+  // buffers; only the running-sum convs are ordered (events).  0 disables (option "concurrent_resblocks").
+  long long chain_frames = 2048;
+  cudaStream_t side[HFG_MAX_KERNELS] = {};
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_sum[HFG_MAX_KERNELS] = {};
 };
 
 namespace {
@@ -347,7 +353,13 @@ int auto_micro_batch(const hfg_ctx* h, int B, int T, bool host_path, int sample_
   return (int)mb;
 }
 
-struct Workspace { char* U; char* P; char* Q; char* T; char* S; float* ACC; char* MEL; };
+struct Workspace { char* U; char* P; char* Q; char* T; char* S; float* ACC; char* MEL;
+                   char* CP[HFG_MAX_KERNELS]; char* CQ[HFG_MAX_KERNELS]; char* CT[HFG_MAX_KERNELS]; };   // per-chain P/Q/T ([0] = P/Q/T)
+
+bool use_chains(const hfg_ctx* h, int B, int T) {
+  return h->chain_frames > 0 && h->cfg.num_kernels > 1 && h->need_sum && !h->need_acc && h->ev_fork &&
+         (long long)B * T <= h->chain_frames;
+}
 
 size_t workspace_layout(const hfg_ctx* h, int B, int T, char* base, Workspace* w) {
   const Sizes s = compute_sizes(h, B, T);
@@ -361,6 +373,11 @@ size_t workspace_layout(const hfg_ctx* h, int B, int T, char* base, Workspace* w
   char* S = take(sumb);
   float* ACC = (float*)take(accb); char* MEL = take(melb);
   if (w) { w->U = U; w->P = P; w->Q = Q; w->T = Tt; w->S = S; w->ACC = ACC; w->MEL = MEL; }
+  for (int j = 0; j < h->cfg.num_kernels; ++j) {
+    const bool own = j > 0 && use_chains(h, B, T);
+    char* cp = own ? take(ab) : P; char* cq = own ? take(ab) : Q; char* ct = own ? take(ab) : Tt;
+    if (w) { w->CP[j] = cp; w->CQ[j] = cq; w->CT[j] = ct; }
+  }
   return off;
 }
 
@@ -448,6 +465,9 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
   Workspace w;
   workspace_layout(h, B, T, ws, &w);
   Runner r{h, s, B};
+  const bool chains = use_chains(h, B, T);
+  const int nk = c.num_kernels;
+  auto cu = [&](cudaError_t e) { if (r.status == cudaSuccess) r.status = e; };
   const float kSlope = 0.1f;                                    // LRELU_SLOPE, reference model.py:14
   const float kFinalSlope = c.compat == 0 ? 0.3f : 0.01f;       // keras LeakyReLU() default, model.py:152
   int mark = 0;
@@ -484,27 +504,38 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
     L *= up.stride;
     r.slope_of_res = rb_tc ? kSlope : 1.0f;
     char* next_x = nullptr;
-    for (int j = 0; j < c.num_kernels; ++j) {                   // model.py:162-166
-      const int n = i * c.num_kernels + j;
+    if (chains) cu(cudaEventRecord(h->ev_fork, s));             // ups[i] done: the resblock chains may start
+    for (int j = 0; j < nk; ++j) {                              // model.py:162-166
+      const int n = i * nk + j;
       const int nd = c.num_dilations[j];
       const char* rcur = w.U;
+      char* const P = w.CP[j]; char* const Q = w.CQ[j]; char* const Tj = w.CT[j];
+      if (chains && j > 0) { r.s = h->side[j]; cu(cudaStreamWaitEvent(r.s, h->ev_fork, 0)); }
       for (int m = 0; m < nd; ++m) {
         const bool last = (m == nd - 1);
-        char* rnext = (rcur == w.P) ? w.Q : w.P;
-        if (last && j == c.num_kernels - 1) next_x = rnext;
+        char* rnext = (rcur == P) ? Q : P;
+        if (last && j == nk - 1) next_x = rnext;
         if (c.resblock == 1) {                                   // ResBlock1.call model.py:71-80
           const Layer& c1 = rb(n, m, 0);
           const Layer& c2 = rb(n, m, 1);
-          r.conv(c1, rcur, L, w.T, kSlope, nullptr, kSlope, rb_tc);
-          if (last) r.conv_mrf(c2, w.T, L, rnext, w.S, kSlope, rcur, w.ACC, j, c.num_kernels, next_slope, next_tc);
-          else r.conv(c2, w.T, L, rnext, kSlope, rcur, kSlope, rb_tc);
+          r.conv(c1, rcur, L, Tj, kSlope, nullptr, kSlope, rb_tc);
+          if (last && chains && j > 0) cu(cudaStreamWaitEvent(r.s, h->ev_sum[j - 1], 0));   // the running sum of chain j-1
+          if (last) r.conv_mrf(c2, Tj, L, rnext, w.S, kSlope, rcur, w.ACC, j, nk, next_slope, next_tc);
+          else r.conv(c2, Tj, L, rnext, kSlope, rcur, kSlope, rb_tc);
         } else {                                                 // ResBlock2.call model.py:106-112
           const Layer& c1 = rb(n, m, 0);
-          if (last) r.conv_mrf(c1, rcur, L, rnext, w.S, kSlope, rcur, w.ACC, j, c.num_kernels, next_slope, next_tc);
+          if (last && chains && j > 0) cu(cudaStreamWaitEvent(r.s, h->ev_sum[j - 1], 0));
+          if (last) r.conv_mrf(c1, rcur, L, rnext, w.S, kSlope, rcur, w.ACC, j, nk, next_slope, next_tc);
           else r.conv(c1, rcur, L, rnext, kSlope, rcur, kSlope, rb_tc);
         }
+        if (last && chains && j < nk - 1) cu(cudaEventRecord(h->ev_sum[j], r.s));
         rcur = rnext;
       }
+    }
+    if (chains) {                                                // the last chain's final conv depends on every other chain
+      cu(cudaEventRecord(h->ev_join, r.s));
+      r.s = s;
+      cu(cudaStreamWaitEvent(s, h->ev_join, 0));
     }
     x = next_x;                                                  // x = xs / num_kernels (model.py:167)
     x_preact = next_tc;
@@ -555,6 +586,7 @@ int hfg_create(const hfg_config* cfg, int device, hfg_handle* out) {
   hfg_ctx* h = new hfg_ctx();
   h->cfg = *cfg; h->device = device;
   if (const char* e = getenv("HFG_AUTO_FOLD")) h->auto_fold = atoi(e) != 0;   // A/B knob
+  if (const char* e = getenv("HFG_CHAIN_FRAMES")) h->chain_frames = atoll(e);  // A/B knob (option "concurrent_resblocks")
   build_layers(h);
   *out = h;
   return HFG_OK;
@@ -698,6 +730,12 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
     h->marks_per_fwd = c.num_upsamples + 3;
     h->events.resize((size_t)h->marks_per_fwd * kTimingSlots);
     for (auto& ev : h->events) CUDA_TRY(h, cudaEventCreate(&ev));
+  }
+  if (!h->ev_fork && c.num_kernels > 1) {                        // resblock chains of launch-bound forwards (run_forward)
+    for (int j = 1; j < c.num_kernels; ++j) CUDA_TRY(h, cudaStreamCreateWithFlags(&h->side[j], cudaStreamNonBlocking));
+    for (int j = 0; j < c.num_kernels; ++j) CUDA_TRY(h, cudaEventCreateWithFlags(&h->ev_sum[j], cudaEventDisableTiming));
+    CUDA_TRY(h, cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
+    CUDA_TRY(h, cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
   }
   h->finalized = true;
   return HFG_OK;
@@ -870,6 +908,10 @@ int hfg_set_option(hfg_handle h, const char* key, long long value) {
   if (k == "force_ffma") { h->force_ffma = value != 0; h->finalized = false; return HFG_OK; }
   if (k == "cuda_graphs") { h->use_graphs = value != 0; if (!h->use_graphs) clear_graphs(h); return HFG_OK; }
   if (k == "auto_fold") { h->auto_fold = value != 0; h->finalized = false; return HFG_OK; }
+  if (k == "concurrent_resblocks") {      // largest B*T (frames) whose resblocks run as concurrent chains; 0 = never
+    if (value < 0) return fail(h, HFG_ERR_INVALID, "concurrent_resblocks must be >= 0 (frames)");
+    h->chain_frames = value; clear_graphs(h); return HFG_OK;
+  }
   return fail(h, HFG_ERR_INVALID, "unknown option '%s'", key);
 }
 
@@ -1024,6 +1066,10 @@ void hfg_destroy(hfg_handle h) {
   if (h->h2d_stream) cudaStreamDestroy(h->h2d_stream);
   if (h->d2h_stream) cudaStreamDestroy(h->d2h_stream);
   for (auto& ev : h->copy_events) cudaEventDestroy(ev);
+  for (auto& st : h->side) if (st) cudaStreamDestroy(st);
+  for (auto& ev : h->ev_sum) if (ev) cudaEventDestroy(ev);
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  if (h->ev_join) cudaEventDestroy(h->ev_join);
   clear_graphs(h);
   delete h;
 }

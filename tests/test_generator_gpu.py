@@ -289,3 +289,32 @@ def test_bf16_mode_tracks_the_bf16_emulating_oracle(v):
     assert np.isfinite(out).all() and np.abs(out).max() <= 1.0
     assert snr_db(ref32, out) >= 25.0                       # bf16's 8-bit mantissa: ~30 dB
     assert snr_db(emul, out) >= 20.0                        # and is consistent with the oracle's bf16 emulation
+
+
+@pytest.mark.parametrize("v", "123")
+def test_concurrent_resblock_chains_are_bit_identical(v):
+    """Launch-bound forwards run the resblocks of a stage as concurrent chains on side streams (own scratch buffers,
+    running-sum convs ordered by events): same kernels, so the bits must match the single-stream order, on the device
+    path, the host path and its graph replay."""
+    import torch
+    h = HParams.builtin(v)
+    w = synthetic_weights(h, "B")
+    g = Generator(h, precision="fp16").load_weights(w)
+    mel = synthetic_mel(2, 37, h.num_mels)
+    mel_dev = torch.from_numpy(mel).cuda()
+    g.set_option("concurrent_resblocks", 0)
+    serial_host = g(mel).copy()
+    serial_dev = g(mel_dev).cpu().numpy()
+    n_serial = g.last_launch_count()
+    g.set_option("concurrent_resblocks", 2048)
+    for _ in range(4):                                          # plain, capture, replay, replay
+        assert (g(mel) == serial_host).all()
+    assert g.last_launch_count() == n_serial
+    for _ in range(3):
+        assert (g(mel_dev).cpu().numpy() == serial_dev).all()
+    assert (serial_host == serial_dev).all()
+    ref = O.generator_forward(h, w, mel, "torch32")
+    assert np.abs(serial_host - ref).max() <= TC_TOL
+    big = synthetic_mel(3, 1000, h.num_mels)                    # above the limit: single stream, smaller workspace
+    assert np.abs(g(big) - O.generator_forward(h, w, big, "torch32")).max() <= TC_TOL
+    g.close()

@@ -12,4 +12,4 @@ for B, T in ((1, 64), (1, 256), (4, 256), (1, 862), (8, 862)):
     t0 = time.perf_counter()
     for _ in range(50): gen(mel)
     ms = (time.perf_counter() - t0) / 50 * 1e3
-    print(f"v{v} B {B} T {T} ms/call {ms:.3f}  audio-s/s {B * T * 256 / 22050 / ms * 1e3:.0f}")
+    print(f"v{v} B {B} T {T} ms/call {ms:.3f}  audio-s/s {B * T * 256 / 22050 / ms * 1e3:.0f}  (HFG_CHAIN_FRAMES={os.environ.get('HFG_CHAIN_FRAMES', 'default')})")
