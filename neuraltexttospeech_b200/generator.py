@@ -165,6 +165,31 @@ class Generator:
                                               out.ctypes.data_as(C.c_void_p)), self._handle, "hfg_forward_host")
         return out
 
+    # ------------------------------------------------------------------ ragged batches
+    def call_ragged(self, mels, pcm16: bool = False):
+        """Utterances of different lengths: `mels` is a sequence of [T_i, num_mels] arrays (numpy, or torch CUDA
+        tensors on this generator's device).  Equal-length utterances ride one dense batch (longest first); nothing is
+        padded, so every waveform is bit-identical to the one `call(mel[None])` gives (utterances are independent,
+        reference model.py:155-173).  Returns a list, in input order, of [T_i*prod(rates), 1] fp32 waveforms (or
+        [T_i*prod(rates)] int16 PCM with pcm16=True), of the same container kind as the input."""
+        from .sharding import group_by_length
+        mels = list(mels)
+        for m in mels:
+            if len(m.shape) != 2 or int(m.shape[1]) != int(self.hparams.num_mels):
+                raise ValueError(f"each mel must be [T, {self.hparams.num_mels}] (channels-last), got {tuple(m.shape)}")
+        on_device = bool(mels) and torch is not None and isinstance(mels[0], torch.Tensor) and mels[0].is_cuda
+        out = [None] * len(mels)
+        for group in group_by_length([int(m.shape[0]) for m in mels], range(len(mels))):
+            if on_device:
+                batch = torch.stack([mels[i].float() for i in group])
+            else:
+                batch = np.stack([np.asarray(mels[i].detach().numpy() if torch is not None and isinstance(mels[i], torch.Tensor)
+                                             else mels[i], dtype=np.float32) for i in group])
+            wav = self.synthesize_pcm16(batch) if pcm16 else self.call(batch)
+            for j, i in enumerate(group):
+                out[i] = wav[j]
+        return out
+
     # ------------------------------------------------------------------ 16-bit PCM output (SURVEY 8f next-2)
     def synthesize_pcm16(self, x):
         """mel [B, T, num_mels] fp32 -> int16 PCM [B, T*prod(rates)]: `(audio.clamp(-1, 1) * 32768).astype(int16)`

@@ -318,3 +318,24 @@ def test_concurrent_resblock_chains_are_bit_identical(v):
     big = synthetic_mel(3, 1000, h.num_mels)                    # above the limit: single stream, smaller workspace
     assert np.abs(g(big) - O.generator_forward(h, w, big, "torch32")).max() <= TC_TOL
     g.close()
+
+
+def test_ragged_batches_equal_their_utterances_run_alone(gens):
+    # the would-be synthesis caller (Grad-TTS_TF/inference.py:52-93) hands over utterances of different lengths;
+    # equal lengths share a dense batch, nothing is padded -> each waveform is the one a lone call gives
+    import torch
+    from oracle import adjacent_oracle as A
+    g = gens("3", "fp16")
+    lengths = [9, 4, 9, 1, 0, 4, 9]
+    mels = [synthetic_mel(1, t, 80, seed=30 + i)[0] for i, t in enumerate(lengths)]
+    outs = g.call_ragged(mels)
+    pcm = g.call_ragged(mels, pcm16=True)
+    assert [o.shape for o in outs] == [(t * 256, 1) for t in lengths]
+    for m, o, p in zip(mels, outs, pcm):
+        assert np.array_equal(g(m[None])[0], o)
+        assert p.dtype == np.int16 and np.array_equal(A.pcm16(o[:, 0]), p)
+    dev = g.call_ragged([torch.from_numpy(m).cuda() for m in mels])
+    assert all(d.is_cuda and np.array_equal(d.cpu().numpy(), o) for d, o in zip(dev, outs))
+    assert g.call_ragged([]) == []
+    with pytest.raises(ValueError):
+        g.call_ragged([np.zeros((3, 64), np.float32)])

@@ -31,6 +31,31 @@ def test_shard_utterances_partitions_and_balances():
     assert group_by_length(lengths, [1, 3, 4, 6]) == [[1], [6], [3, 4]]
 
 
+def test_call_ragged_groups_equal_lengths_and_keeps_input_order():
+    # host logic only: the dense-batch call is replaced by a recorder (the GPU test runs the real one)
+    from neuraltexttospeech_b200 import Generator, HParams
+    g = Generator.__new__(Generator)
+    g.hparams = HParams.builtin("1")
+    batches = []
+
+    def fake_call(batch):
+        batches.append(batch.shape)
+        return np.repeat(batch[:, :, :1], 2, axis=1)          # [B, 2T, 1], tagged by the utterance's first mel bin
+
+    g.call = fake_call
+    lengths = [5, 2, 5, 0, 2, 7]
+    mels = [np.full((t, 80), float(i), np.float32) for i, t in enumerate(lengths)]
+    outs = g.call_ragged(mels)
+    assert batches == [(1, 7, 80), (2, 5, 80), (2, 2, 80), (1, 0, 80)]      # longest first, one batch per length
+    assert [o.shape for o in outs] == [(2 * t, 1) for t in lengths]
+    assert all((o == i).all() for i, o in enumerate(outs))
+    assert g.call_ragged([]) == []
+    with pytest.raises(ValueError):
+        g.call_ragged([np.zeros((4, 79), np.float32)])
+    with pytest.raises(ValueError):
+        g.call_ragged([np.zeros((1, 4, 80), np.float32)])
+
+
 def _worker(rank, world, port, q):
     import torch.distributed as dist
     os.environ["MASTER_ADDR"] = "127.0.0.1"
