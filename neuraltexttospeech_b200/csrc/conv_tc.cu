@@ -53,7 +53,21 @@ namespace {
 #endif
 constexpr int kEpiGroups = HFG_TC_EPI_GROUPS;                 // groups of 4 epilogue warps taking passes round-robin
 constexpr int kStoreWarp = 4 + 4 * kEpiGroups;                // warp index of the store issuer
-constexpr int kTcThreads = (kStoreWarp + 1) * 32;             // 4 producer/MMA warps, kEpiGroups x 4 epilogue warps, 1 store issuer
+// Register re-allocation between roles (setmaxnreg, per warpgroup of 4 warps).  Each SM sub-partition holds one warp of
+// every warpgroup and 512 registers per lane, so 13 warps cap every role at 128 registers and a third epilogue group
+// would cap them at 96 (measured -6 %: the epilogue spills).  With HFG_TC_REGS_EPI > 0 the store issuer's warpgroup is
+// padded to 4 warps (3 idle), the kernel starts at the launch bound and the producer / MMA / store warpgroups hand
+// registers to the epilogue groups: 2 x kRegsIo + kEpiGroups x kRegsEpi <= warps-per-partition x launch registers.
+#ifndef HFG_TC_REGS_EPI
+#define HFG_TC_REGS_EPI (HFG_TC_EPI_GROUPS >= 3 ? 128 : 0)
+#endif
+#ifndef HFG_TC_REGS_IO
+#define HFG_TC_REGS_IO 48
+#endif
+constexpr int kRegsEpi = HFG_TC_REGS_EPI, kRegsIo = HFG_TC_REGS_IO;
+constexpr int kTcThreads = (kStoreWarp + (kRegsEpi > 0 ? 4 : 1)) * 32;   // 4 producer/MMA warps, kEpiGroups x 4 epilogue warps, store issuer
+template <int R> __device__ __forceinline__ void regs_release() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R)); }
+template <int R> __device__ __forceinline__ void regs_acquire() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(R)); }
 constexpr int kTcMaxCout = 512;
 constexpr int kTcMaxSpan = 96;       // largest max_off - min_off supported (V1: 50, V3: 72)
 constexpr size_t kTcMaxSmem = 227 * 1024;
@@ -408,6 +422,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
 
   // Producer / MMA warps run their loops with ALL lanes (warp-uniform control flow keeps barrier addresses and
   // descriptors in uniform registers) and issue the asynchronous instructions from one elected lane.
+  if (warp < 4) {
+  if constexpr (kRegsEpi > 0) regs_release<kRegsIo>();
   if (warp == 0) {
     // ===================== slab producer (TMA) =====================
     uint32_t scnt = 0;
@@ -561,7 +577,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
         }
       }
     }
-  } else if (warp == kStoreWarp) {
+  }
+  } else if (warp >= kStoreWarp) {
+  if constexpr (kRegsEpi > 0) regs_release<kRegsIo>();
+  if (warp == kStoreWarp) {
     // ===================== store issuer: TMA tensor store of every finished staging tile =====================
     // Up to two stores stay in flight: the buffer of pass p is handed back only once the store of pass p has finished
     // READING shared memory, which is checked two passes later (bulk groups retire in order).  Waiting for each store
@@ -603,8 +622,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
     // the last in_flight buffers are not handed back: no pass is left to use them
     if (elect_one()) bulk_wait_all();                   // same lane every time (elect.sync picks the lowest)
     __syncwarp();
+  }
   } else {
-    // ===================== epilogue: two groups of 4 warps (4-7, 8-11) take alternate passes =====================
+    // ===================== epilogue: kEpiGroups groups of 4 warps (4-7, 8-11, ...) take passes round-robin =====================
+    if constexpr (kRegsEpi > 0) regs_acquire<kRegsEpi>();
     const int grp = (warp - 4) >> 2;
     const int quarter = warp & 3;                       // TMEM lane quarter this warp may access
     const int er = quarter * 32 + lane;                 // row of the 128-row block owned by this thread
