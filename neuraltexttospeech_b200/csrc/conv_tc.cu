@@ -66,6 +66,20 @@ constexpr int kStoreWarp = 4 + 4 * kEpiGroups;                // warp index of t
 #endif
 constexpr int kRegsEpi = HFG_TC_REGS_EPI, kRegsIo = HFG_TC_REGS_IO;
 constexpr int kTcThreads = (kStoreWarp + (kRegsEpi > 0 ? 4 : 1)) * 32;   // 4 producer/MMA warps, kEpiGroups x 4 epilogue warps, store issuer
+// Active epilogue groups of one instantiation (<= kEpiGroups; the others idle at 24 registers and the active ones take
+// theirs).  HFG_TC_EG_RULE: 0 = every kernel uses all groups, 1 = the 128-wide CTA-pair kernels (operand-bound wide
+// stages) keep two, 2 = every CTA-pair kernel keeps two.
+#ifndef HFG_TC_EG_RULE
+#define HFG_TC_EG_RULE 0
+#endif
+__host__ __device__ constexpr int tc_epi_groups(int n, int cg) {
+  if (kRegsEpi == 0 || kEpiGroups <= 2) return kEpiGroups;
+  if (HFG_TC_EG_RULE == 1 && cg == 2 && n >= 128) return 2;
+  if (HFG_TC_EG_RULE == 2 && cg == 2) return 2;
+  return kEpiGroups;
+}
+// registers of an active epilogue warp: what the idle groups give up is shared out (launch bound 96 x 5 warps per partition)
+__host__ __device__ constexpr int tc_epi_regs(int eg) { return eg == kEpiGroups ? kRegsEpi : ((kEpiGroups * kRegsEpi - (kEpiGroups - eg) * 24) / eg) / 8 * 8; }
 template <int R> __device__ __forceinline__ void regs_release() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(R)); }
 template <int R> __device__ __forceinline__ void regs_acquire() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(R)); }
 constexpr int kTcMaxCout = 512;
@@ -353,6 +367,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
                const __grid_constant__ TcKArgs ka) {
   static_assert(CG == 1 || CG == 2, "cta group");
   constexpr int NB = N / CG;                      // weight rows (B operand) staged by this CTA
+  constexpr int EG = tc_epi_groups(N, CG);        // epilogue groups at work in this instantiation
   constexpr int NKS = C_IN / KS;                  // K-slices per tile
   constexpr int NKB = KS / KBW;                   // weight k-blocks per (slice, tap)
   constexpr int BLK_BYTES = NB * KBW * 2;         // this CTA's part of one (tap, k-block) weight block; a stage holds TPS
@@ -397,7 +412,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
     for (int s = 0; s < nsl; ++s) { mbar_init(&slice_full[s], 1); mbar_init(&slice_empty[s], 1); }
     for (int s = 0; s < NST; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
     for (int s = 0; s < nstg; ++s) { mbar_init(&stg_full[s], 1); mbar_init(&stg_empty[s], 1); mbar_init(&stg_done[s], 4); }
-    for (int s = 0; s < kTcMaxAcc; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 4 * kEpiGroups * CG); }
+    for (int s = 0; s < kTcMaxAcc; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 4 * EG * CG); }
     fence_mbar_init();
     tma_prefetch_desc(&tm_x); tma_prefetch_desc(&tm_res); tma_prefetch_desc(&tm_out);
     if (CG == 2) tma_prefetch_desc(&tm_w);
@@ -625,7 +640,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
   }
   } else {
     // ===================== epilogue: kEpiGroups groups of 4 warps (4-7, 8-11, ...) take passes round-robin =====================
-    if constexpr (kRegsEpi > 0) regs_acquire<kRegsEpi>();
+    if constexpr (EG < kEpiGroups) {
+      if (warp >= 4 + 4 * EG) { regs_release<24>(); goto done; }     // idle group (whole warpgroup)
+    }
+    if constexpr (kRegsEpi > 0) regs_acquire<tc_epi_regs(EG)>();
     const int grp = (warp - 4) >> 2;
     const int quarter = warp & 3;                       // TMEM lane quarter this warp may access
     const int er = quarter * 32 + lane;                 // row of the 128-row block owned by this thread
@@ -649,7 +667,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
         const bool has_res = ka.has_res != 0 && q0 < ka.n_q;
 #pragma unroll 1
         for (int p0 = 0; p0 < N; p0 += PW, ++pcnt) {
-          if ((int)(pcnt % (uint32_t)kEpiGroups) != grp) continue;
+          if ((int)(pcnt % (uint32_t)EG) != grp) continue;
           const int buf = pcnt % (uint32_t)nstg;
 #pragma unroll 1
           for (int rb = 0; rb < RB; ++rb) {              // the pass's 128-row blocks (one unless the tile is narrow)
@@ -757,6 +775,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
       }
     }
   }
+done:
   tc_fence_before();
   if (CG == 2) cluster_sync_all(); else __syncthreads();   // pair: nobody exits while the peer may still signal its barriers
   if (warp == 2) {
