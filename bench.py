@@ -332,7 +332,10 @@ def main():
         dw, dst = per_stage_work(h, act_b)[dom], stages[dom]
         dom_flops_launch = 2.0 * dw["macs"] * T * mb / dw["launches"]
         dom_ms_launch = dst["ms"] / dw["launches"]
-        achieved = dom_flops_launch / (dom_ms_launch * 1e-3) / 1e12
+        dom_bytes_launch = float(dw["bytes"]) * T * mb / dw["launches"]
+        dom_tensor = dst["bound"] == "tensor"              # the dominant stage's own binding roof (V2 / V3: HBM)
+        achieved = (dom_flops_launch / (dom_ms_launch * 1e-3) / 1e12) if dom_tensor else (dom_bytes_launch / (dom_ms_launch * 1e-3) / 1e9)
+        dom_peak = pk["tflops_sustained"] if dom_tensor else pk["hbm_gbs"]
         traffic = ncu_traffic(dst["label"], args.config, mb)
         line = {
             "metric": "HiFi-GAN V1 audio-seconds/sec", "value": world * audio_s_per_step / (dev_ms / 1000), "unit": "audio-s/s",
@@ -345,12 +348,13 @@ def main():
                        "l2": "per-step working set (GBs of activations) exceeds the 126 MB L2; no flush needed",
                        "sharding": "utterances sharded across ranks, no collective on the data path"},
             "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps), "clocks": clocks,
-            "roofline": {"bound": "tensor" if tensor_bound else "hbm", "achieved": achieved, "peak": pk["tflops_sustained"] if tensor_bound else None,
-                         "unit": "TFLOP/s", "frac": achieved / pk["tflops_sustained"] if tensor_bound else None, "traffic": traffic,
+            "roofline": {"bound": "tensor" if dom_tensor else "hbm", "achieved": achieved, "peak": dom_peak,
+                         "unit": "TFLOP/s" if dom_tensor else "GB/s", "frac": achieved / dom_peak, "traffic": traffic,
                          "kernel": f"conv_tc_kernel (tcgen05 implicit GEMM), {dst['label']}: {dw['launches']} launches per forward of {mb} utterances",
-                         "flops_per_launch": dom_flops_launch, "ms_per_launch": dom_ms_launch,
+                         "flops_per_launch": dom_flops_launch, "bytes_per_launch": dom_bytes_launch, "ms_per_launch": dom_ms_launch,
                          "timing": "CUDA events on the launch stream around the stage, inside the timed region, averaged over its forwards",
-                         "peak_source": pk["source"] + " bf16 sustained (fp16 runs at the same tcgen05 rate; kernel timed inside a long step)"},
+                         "peak_source": pk["source"] + (" bf16 sustained (fp16 runs at the same tcgen05 rate; kernel timed inside a long step)" if dom_tensor
+                                                        else " HBM copy bandwidth, sustained (layer-boundary bytes of the stage, SURVEY 8d)")},
             "roofline_step": {"achieved_tflops": flops / (dev_ms / 1000) / 1e12, "frac_of_tensor_peak": flops / (dev_ms / 1000) / p_tensor,
                               "per_stage_roof_ms_per_step": t_roof_sum * (B / mb), "frac_of_per_stage_roofline": t_roof_sum * (B / mb) / dev_ms,
                               "algorithmic_flops_per_step": flops, "layer_boundary_bytes_per_step": bytes_boundary,

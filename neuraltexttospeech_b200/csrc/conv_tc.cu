@@ -25,11 +25,12 @@
 //           TMEM accumulators (NACC buffers of MB x N columns); tcgen05.commit releases weight stages / slab
 //           slices and hands the accumulator to the epilogue.
 //   warp 3  staging producer: TMA-loads the residual tile of each epilogue pass into the staging ring.
-//   warps 4-11 epilogue, two groups of four taking alternate passes: tcgen05.ld (one TMEM lane quarter per
-//           warp, thread = output row) -> +bias -> +residual (model.py:79,111) -> +MRF partial sum,
+//   warps 4-15 epilogue, three groups of four taking passes round-robin (two on the 128-wide pair kernels, the third
+//           then only gives its registers away): tcgen05.ld (one TMEM lane quarter per warp, thread = output row) -> +bias -> +residual (model.py:79,111) -> +MRF partial sum,
 //           *1/num_kernels (model.py:161-167) -> activation for the consumer -> 16-bit, in place in the
 //           swizzled staging tile; conv_post mode: tanh -> fp32 / 16-bit PCM samples (model.py:170-171).
-//   warp 12 store issuer: TMA tensor store of every finished staging tile, two stores in flight.
+//   warp 16 store issuer: TMA tensor store of every finished staging tile, two stores in flight (warps 17-19 idle:
+//           they complete the warpgroup so that registers can be re-allocated between roles with setmaxnreg).
 //
 // Loads of tile i+1, MMAs of tile i and the epilogue of tile i-1 overlap (slab ring, TMEM double
 // buffering where 2*MB*N <= 512 columns, NSTG-deep staging ring).  CG = 2 runs the kernel as CTA pairs
@@ -49,7 +50,7 @@ namespace hfg {
 namespace {
 
 #ifndef HFG_TC_EPI_GROUPS
-#define HFG_TC_EPI_GROUPS 2
+#define HFG_TC_EPI_GROUPS 3
 #endif
 constexpr int kEpiGroups = HFG_TC_EPI_GROUPS;                 // groups of 4 epilogue warps taking passes round-robin
 constexpr int kStoreWarp = 4 + 4 * kEpiGroups;                // warp index of the store issuer
@@ -59,10 +60,10 @@ constexpr int kStoreWarp = 4 + 4 * kEpiGroups;                // warp index of t
 // padded to 4 warps (3 idle), the kernel starts at the launch bound and the producer / MMA / store warpgroups hand
 // registers to the epilogue groups: 2 x kRegsIo + kEpiGroups x kRegsEpi <= warps-per-partition x launch registers.
 #ifndef HFG_TC_REGS_EPI
-#define HFG_TC_REGS_EPI (HFG_TC_EPI_GROUPS >= 3 ? 128 : 0)
+#define HFG_TC_REGS_EPI (HFG_TC_EPI_GROUPS >= 3 ? 112 : 0)
 #endif
 #ifndef HFG_TC_REGS_IO
-#define HFG_TC_REGS_IO 48
+#define HFG_TC_REGS_IO 64
 #endif
 constexpr int kRegsEpi = HFG_TC_REGS_EPI, kRegsIo = HFG_TC_REGS_IO;
 constexpr int kTcThreads = (kStoreWarp + (kRegsEpi > 0 ? 4 : 1)) * 32;   // 4 producer/MMA warps, kEpiGroups x 4 epilogue warps, store issuer
@@ -70,7 +71,7 @@ constexpr int kTcThreads = (kStoreWarp + (kRegsEpi > 0 ? 4 : 1)) * 32;   // 4 pr
 // theirs).  HFG_TC_EG_RULE: 0 = every kernel uses all groups, 1 = the 128-wide CTA-pair kernels (operand-bound wide
 // stages) keep two, 2 = every CTA-pair kernel keeps two.
 #ifndef HFG_TC_EG_RULE
-#define HFG_TC_EG_RULE 0
+#define HFG_TC_EG_RULE 1
 #endif
 __host__ __device__ constexpr int tc_epi_groups(int n, int cg) {
   if (kRegsEpi == 0 || kEpiGroups <= 2) return kEpiGroups;
@@ -96,15 +97,6 @@ __host__ __device__ constexpr int tc_nstg(int nstg, int rb) { return nstg / rb <
 __host__ __device__ constexpr int tc_rb(int n, int mb) { return (n >= 64 || mb < 2) ? 1 : 2; }   // a TMA box holds at most 256 rows
 
 __host__ __device__ constexpr uint32_t tc_tmem_cols(int need) { return need <= 32 ? 32 : need <= 64 ? 64 : need <= 128 ? 128 : need <= 256 ? 256 : 512; }
-
-__host__ __device__ inline int tc_rows_padded(int rows, int chunks) {
-  // conflict-free 16-byte staging stores: R_pad mod 8 == 1 when a quarter-warp spans 8 chunks of one
-  // row, 2 / 4 when a row has only 4 / 2 chunks
-  const int want = chunks >= 8 ? 1 : (chunks >= 2 ? 8 / chunks : 0);
-  int r = rows;
-  while (r % 8 != want) ++r;
-  return r;
-}
 
 // ------------------------------------------------------------------ PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -139,9 +131,6 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, uint32_t bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(smem_u32(src_smem)), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
@@ -294,7 +283,6 @@ template <> struct H2<__nv_bfloat16> {
   }
 };
 
-__device__ __forceinline__ float lrelu_f(float v, float s) { return v >= 0.f ? v : v * s; }
 // two-instruction forms (FMUL + FMNMX) for slopes known to lie on one side of 1
 __device__ __forceinline__ float lrelu_le1(float v, float s) { return fmaxf(v, v * s); }   // 0 < s <= 1: leaky relu
 __device__ __forceinline__ float lrelu_ge1(float v, float s) { return fminf(v, v * s); }   // s >= 1: its inverse
@@ -640,9 +628,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
   }
   } else {
     // ===================== epilogue: kEpiGroups groups of 4 warps (4-7, 8-11, ...) take passes round-robin =====================
-    if constexpr (EG < kEpiGroups) {
-      if (warp >= 4 + 4 * EG) { regs_release<24>(); goto done; }     // idle group (whole warpgroup)
-    }
+    const bool idle = EG < kEpiGroups && warp >= 4 + 4 * EG;       // a whole warpgroup: it only gives its registers away
+    if constexpr (EG < kEpiGroups) { if (idle) regs_release<24>(); }
+    if (!idle) {
     if constexpr (kRegsEpi > 0) regs_acquire<tc_epi_regs(EG)>();
     const int grp = (warp - 4) >> 2;
     const int quarter = warp & 3;                       // TMEM lane quarter this warp may access
@@ -774,8 +762,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
         else mbar_arrive(&acc_empty[abuf]);
       }
     }
+    }
   }
-done:
   tc_fence_before();
   if (CG == 2) cluster_sync_all(); else __syncthreads();   // pair: nobody exits while the peer may still signal its barriers
   if (warp == 2) {
