@@ -861,21 +861,34 @@ static int forward_host(hfg_handle h, const float* mel_host, int B, int T, void*
   // computes; only the first H2D and the last D2H are exposed.
   if (!h->h2d_stream) CUDA_TRY(h, cudaStreamCreateWithFlags(&h->h2d_stream, cudaStreamNonBlocking));
   if (!h->d2h_stream) CUDA_TRY(h, cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking));
-  const int n_mb = (B + mb - 1) / mb;
+  // Micro-batch schedule.  Only the first upload and the last download are exposed, and both scale with the size of
+  // their micro-batch: under the library's own rule the first and the last one are half-sized (utterances are
+  // independent, so the split does not change a single output bit); an explicit micro_batch option stays uniform.
+  std::vector<int> parts;
+  static const bool taper = []() { const char* e = getenv("HFG_HOST_TAPER"); return e ? atoi(e) != 0 : true; }();   // A/B knob
+  if (taper && h->micro_batch <= 0 && mb >= 8 && B >= 2 * mb) {
+    const int edge = mb / 2;
+    parts.push_back(edge);
+    for (int left = B - 2 * edge; left > 0; left -= mb) parts.push_back(left < mb ? left : mb);
+    parts.push_back(edge);
+  } else {
+    for (int left = B; left > 0; left -= mb) parts.push_back(left < mb ? left : mb);
+  }
+  const int n_mb = (int)parts.size();
   while ((int)h->copy_events.size() < 2 * n_mb) {
     cudaEvent_t ev;
     CUDA_TRY(h, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     h->copy_events.push_back(ev);
   }
   long long launches = 0;
-  for (int i = 0, b0 = 0; b0 < B; b0 += mb, ++i) {
-    const int nb = (B - b0 < mb) ? B - b0 : mb;
+  for (int i = 0, b0 = 0; i < n_mb; b0 += parts[i], ++i) {
+    const int nb = parts[i];
     CUDA_TRY(h, cudaMemcpyAsync(h->d_mel + (size_t)b0 * mel_elems, mel_host + (size_t)b0 * mel_elems, (size_t)nb * mel_elems * 4,
                                 cudaMemcpyHostToDevice, h->h2d_stream));
     CUDA_TRY(h, cudaEventRecord(h->copy_events[2 * i], h->h2d_stream));
   }
-  for (int i = 0, b0 = 0; b0 < B; b0 += mb, ++i) {
-    const int nb = (B - b0 < mb) ? B - b0 : mb;
+  for (int i = 0, b0 = 0; i < n_mb; b0 += parts[i], ++i) {
+    const int nb = parts[i];
     char* dev_out = (char*)h->d_audio + (size_t)b0 * aud_elems * sample_bytes;
     CUDA_TRY(h, cudaStreamWaitEvent(h->stream, h->copy_events[2 * i], 0));
     int rc = forward_maybe_graph(h, h->d_mel + (size_t)b0 * mel_elems, nb, T, dev_out, sample_bytes);

@@ -339,3 +339,22 @@ def test_ragged_batches_equal_their_utterances_run_alone(gens):
     assert g.call_ragged([]) == []
     with pytest.raises(ValueError):
         g.call_ragged([np.zeros((3, 64), np.float32)])
+
+
+def test_host_path_tapered_micro_batches_are_bit_identical(gens):
+    # hfg_forward_host halves its first and last micro-batch under its own rule (shorter exposed upload / download);
+    # utterances are independent, so the result equals the device path run on the whole batch and a uniform split
+    import torch
+    g = gens("3", "fp16")
+    B, T = 40, 12
+    mel = synthetic_mel(B, T, 80, seed=77)
+    assert B >= 2 * g.auto_micro_batch(B, T, host_path=True) >= 16        # the tapered schedule is in use
+    host = g(mel)
+    dev = g(torch.from_numpy(mel).cuda()).cpu().numpy()
+    assert np.array_equal(host, dev)
+    g.set_option("micro_batch", 7)                                           # explicit option: uniform parts, ragged tail
+    try:
+        assert np.array_equal(g(mel), host)
+    finally:
+        g.set_option("micro_batch", 0)
+    assert np.array_equal(g.synthesize_pcm16(mel), g.synthesize_pcm16(torch.from_numpy(mel).cuda()).cpu().numpy())
