@@ -833,7 +833,22 @@ static int forward_host(hfg_handle h, const float* mel_host, int B, int T, void*
   if (!mel_host || !out_host) return fail(h, HFG_ERR_INVALID, "%s: null host pointer", fn);
   CUDA_TRY(h, cudaSetDevice(h->device));
   if (!h->stream) CUDA_TRY(h, cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-  const int mb = h->micro_batch <= 0 ? auto_micro_batch(h, B, T, true, sample_bytes) : (h->micro_batch > B ? B : h->micro_batch);
+  int mb = h->micro_batch <= 0 ? auto_micro_batch(h, B, T, true, sample_bytes) : (h->micro_batch > B ? B : h->micro_batch);
+  // Micro-batch schedule.  Only the first upload and the last download are exposed, and both scale with the size of
+  // their micro-batch; the kernels prefer large batches.  Where the rule asks for four parts (copy-heavy: V2 / V3) the
+  // batch is walked as quarter, half, quarter instead: the same exposed copies with a larger middle part.  Utterances
+  // are independent, so the split does not change a single output bit; an explicit micro_batch option stays uniform.
+  std::vector<int> parts;
+  static const int taper = []() { const char* e = getenv("HFG_HOST_TAPER"); return e ? atoi(e) : 1; }();   // A/B knob
+  if (taper && h->micro_batch <= 0 && mb >= 8 && mb == (B + 3) / 4 && B - 2 * mb <= auto_micro_batch(h, B, T, false)) {
+    const int edge = mb;
+    parts.push_back(edge);
+    parts.push_back(B - 2 * edge);
+    parts.push_back(edge);
+    mb = B - 2 * edge;
+  } else {
+    for (int left = B; left > 0; left -= mb) parts.push_back(left < mb ? left : mb);
+  }
   const size_t mel_elems = (size_t)T * h->cfg.num_mels, aud_elems = (size_t)T * h->total_up;
   const size_t need_ws = workspace_layout(h, mb, T, nullptr, nullptr);
   if (need_ws > h->ws_bytes) {
@@ -861,19 +876,6 @@ static int forward_host(hfg_handle h, const float* mel_host, int B, int T, void*
   // computes; only the first H2D and the last D2H are exposed.
   if (!h->h2d_stream) CUDA_TRY(h, cudaStreamCreateWithFlags(&h->h2d_stream, cudaStreamNonBlocking));
   if (!h->d2h_stream) CUDA_TRY(h, cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking));
-  // Micro-batch schedule.  Only the first upload and the last download are exposed, and both scale with the size of
-  // their micro-batch: under the library's own rule the first and the last one are half-sized (utterances are
-  // independent, so the split does not change a single output bit); an explicit micro_batch option stays uniform.
-  std::vector<int> parts;
-  static const bool taper = []() { const char* e = getenv("HFG_HOST_TAPER"); return e ? atoi(e) != 0 : true; }();   // A/B knob
-  if (taper && h->micro_batch <= 0 && mb >= 8 && B >= 2 * mb) {
-    const int edge = mb / 2;
-    parts.push_back(edge);
-    for (int left = B - 2 * edge; left > 0; left -= mb) parts.push_back(left < mb ? left : mb);
-    parts.push_back(edge);
-  } else {
-    for (int left = B; left > 0; left -= mb) parts.push_back(left < mb ? left : mb);
-  }
   const int n_mb = (int)parts.size();
   while ((int)h->copy_events.size() < 2 * n_mb) {
     cudaEvent_t ev;
