@@ -46,6 +46,8 @@ def test_sass_contains_blackwell_tensor_core_and_bulk_copy_ops():
     assert "UBLKCP" in sass           # cp.async.bulk (weight stages)
     assert "UTMALDG" in sass          # cp.async.bulk.tensor loads (TMA halo slabs)
     assert "UTMASTG" in sass          # TMA tensor stores (epilogue)
+    assert "USETMAXREG.DEALLOC" in sass and "USETMAXREG.TRY_ALLOC" in sass   # setmaxnreg: producer/MMA/store warps hand registers to the epilogue groups
+    assert "UTCHMMA.2CTA" in sass     # cta_group::2 pair kernels of the wide stages
     assert "sm_100a" in sass or "SM100" in sass.upper()
 
 
