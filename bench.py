@@ -131,26 +131,54 @@ def cpu_port_audio_s_per_s(version, B, T, repeats, threads=None):
     return secs / min(ts), secs / (sum(ts) / len(ts)), torch.get_num_threads(), ts
 
 
+def metric_name(version):
+    return f"HiFi-GAN V{version} audio-seconds/sec"
+
+
+def tf_pin():
+    """when a box carries tensorflow + tensorflow_addons and a checkout of the reference's HiFiGAN_TF, run the
+    REAL reference on a tiny case and record how far the oracle is from it; otherwise say why not (oracle/tf_probe.py)."""
+    try:
+        from oracle import tf_probe, hifigan_oracle as O
+        from neuraltexttospeech_b200.hparams import HParams
+        from neuraltexttospeech_b200.synthetic import synthetic_mel, synthetic_weights
+        ok, why = tf_probe.available()
+        if not ok:
+            return {"kind": "port", "tf": "unavailable: " + why}
+        h = HParams.builtin("1")
+        w = synthetic_weights(h, "B")
+        mel = synthetic_mel(1, 16, h.num_mels)
+        return tf_probe.pin_oracle(h, w, mel, O.generator_forward(h, w, mel, "torch32"))
+    except Exception as e:                      # a probe must never take the bench down
+        return {"kind": "port", "tf": f"probe failed: {type(e).__name__}: {e}"}
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
     version, B, T = CONFIGS[args.config]
-    per_step = []
-    import torch
-    # bounded sample of the workload: ONE utterance of the batch per step (same frames, same weights)
-    best, mean, threads, ts = cpu_port_audio_s_per_s(version, 1, T, max(1, args.warmup // 3) + args.steps)
+    # Bounded sample of the workload: `sb` utterances of the batch per step (same frames, same weights), the largest
+    # power of two (<= 16, <= B) whose timed steps fit ~60 s.  The CPU port's rate is nearly flat in the batch size
+    # (profiles/r2_cpu_port_batch_effect.json: audio-s/s at B = 1, 4, 16), so the rate of the sample stands for the batch.
+    best1, _, threads, ts1 = cpu_port_audio_s_per_s(version, 1, T, 1)
+    sb = 1
+    while sb * 2 <= min(B, 16) and ts1[0] * (sb * 2) * (args.steps + 1) <= 60.0:
+        sb *= 2
+    best, mean, threads, ts = cpu_port_audio_s_per_s(version, sb, T, max(1, args.warmup // 3) + args.steps)
     ts = ts[-args.steps:]
     ms = 1000 * sum(ts) / len(ts)
-    val = (T * 256 / SR) / (sum(ts) / len(ts))
+    val = (sb * T * 256 / SR) / (sum(ts) / len(ts))
+    pin = tf_pin()
     line = {
-        "impl": "reference", "metric": "HiFi-GAN V1 audio-seconds/sec", "value": val, "unit": "audio-s/s",
+        "impl": "reference", "metric": metric_name(version), "value": val, "unit": "audio-s/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
         "config": {"workload": args.config, "generator": f"config_v{version}.json", "per_gpu_batch": B, "frames": T,
-                   "sample_per_step": f"1 utterance x {T} frames (1/{B} of the batch)"},
+                   "sample_per_step": f"{sb} utterance(s) x {T} frames ({sb}/{B} of the batch)",
+                   "one_utterance_rate": (T * 256 / SR) / ts1[0]},
         "cpu_baseline": {"value": val, "unit": "audio-s/s", "cores": threads, "kind": "port",
-                         "sample": f"1 utterance x {T} frames per step; torch-CPU fp32 restatement of HiFiGAN_TF/model.py "
-                                   "(TensorFlow/tfa not installable on this image)"},
+                         "sample": f"{sb} utterance(s) x {T} frames per step; torch-CPU fp32 restatement of HiFiGAN_TF/model.py "
+                                   "(TensorFlow/tfa not installable on this image)", "tf_reference": pin},
         "e2e": {"value": val, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -228,6 +256,9 @@ def main():
     mb = max(1, min(args.micro_batch, B)) if args.micro_batch > 0 else gen.auto_micro_batch(B, T)
     stream = torch.cuda.current_stream()
 
+    n_forwards = (B + mb - 1) // mb
+    mean_fwd_batch = B / n_forwards        # stage stamps are averaged over forwards: a ragged tail (512 = 6 x 76 + 56) counts
+
     def step_device():
         n = 0
         for b0 in range(0, B, mb):
@@ -257,35 +288,41 @@ def main():
     e2e = None
     adjacent = {}
     if not args.no_e2e:
-        mel_pin = torch.from_numpy(mel_np).pin_memory()
-        out_pin = torch.empty((B, L, 1), dtype=torch.float32).pin_memory()
-        mel_h, out_h = mel_pin.numpy(), out_pin.numpy()
-        gen.set_option("micro_batch", args.micro_batch if args.micro_batch > 0 else 0)   # 0: two micro-batches, copies overlap compute
+        # The call a user makes: `audio = generator(mel)` on an ordinary (pageable) numpy array, result allocated by the
+        # call.  Inside: the mels are staged to pinned memory and uploaded per micro-batch, the waveforms land in a
+        # page-locked numpy array from the generator's pool (recycled when the previous result is dropped).
+        mel_user = np.array(mel_np, copy=True)                               # plain numpy, not pinned
+        gen.set_option("micro_batch", args.micro_batch if args.micro_batch > 0 else 0)   # 0: the library's own split (copies overlap compute)
         mb_host = args.micro_batch if args.micro_batch > 0 else gen.auto_micro_batch(B, T, host_path=True)
-        for _ in range(2):
-            gen._call_host(mel_h, out_h)
+        audio = None
+        for _ in range(3):
+            audio = gen(mel_user)
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            gen._call_host(mel_h, out_h)          # H2D + forward + D2H + sync, every step
+            audio = gen(mel_user)                 # H2D + forward + D2H + sync, every step; `audio` is read back on the host
+            checksum = float(audio[0, 0, 0]) + float(audio[-1, -1, 0])
         barrier()
         e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1000) / args.steps
+        assert audio.shape == (B, L, 1) and audio.dtype == np.float32 and np.isfinite(checksum)
         e2e = {"value": world * audio_s_per_step / (e2e_ms / 1000), "unit": "audio-s/s",
-               "h2d_bytes_per_step": int(mel_np.nbytes), "d2h_bytes_per_step": int(out_pin.numel() * 4),
-               "ms_per_step": e2e_ms, "micro_batch": mb_host, "api": "Generator.call(numpy) -> hfg_forward_host"}
-        # same call with the 16-bit PCM epilogue: half the D2H bytes
-        pcm_pin = torch.empty((B, L), dtype=torch.int16).pin_memory()
+               "h2d_bytes_per_step": int(mel_np.nbytes), "d2h_bytes_per_step": int(audio.nbytes),
+               "ms_per_step": e2e_ms, "micro_batch": mb_host,
+               "api": "audio = Generator.__call__(mel: pageable numpy [B,T,80]) -> numpy [B,L,1] allocated by the call (hfg_forward_host)"}
+        del audio
+        # same public call with the 16-bit PCM epilogue: half the D2H bytes
         for _ in range(2):
-            gen.forward_host_pcm16_ptr(mel_pin.data_ptr(), B, T, pcm_pin.data_ptr())
+            pcm = gen.synthesize_pcm16(mel_user)
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            gen.forward_host_pcm16_ptr(mel_pin.data_ptr(), B, T, pcm_pin.data_ptr())
+            pcm = gen.synthesize_pcm16(mel_user)
         barrier()
         pcm_ms = max_over_ranks((time.perf_counter() - t0) * 1000) / args.steps
         adjacent["e2e_pcm16"] = {"value": world * audio_s_per_step / (pcm_ms / 1000), "unit": "audio-s/s", "ms_per_step": pcm_ms,
-                                 "h2d_bytes_per_step": int(mel_np.nbytes), "d2h_bytes_per_step": int(pcm_pin.numel() * 2),
-                                 "api": "Generator.synthesize_pcm16 -> hfg_forward_host_pcm16"}
+                                 "h2d_bytes_per_step": int(mel_np.nbytes), "d2h_bytes_per_step": int(pcm.nbytes),
+                                 "api": "Generator.synthesize_pcm16(numpy) -> hfg_forward_host_pcm16"}
+        del pcm
     # mel front-end kernel on the waveforms this step produced: HBM-bound, bytes = wav in + mel out
     if not args.no_adjacent:
         from neuraltexttospeech_b200 import STFT
@@ -319,7 +356,7 @@ def main():
         # per-stage roofline: t_roof = max(F / P_tensor, B / BW_hbm) per forward of `mb` utterances
         stages, t_roof_sum = [], 0.0
         for w, ms in zip(per_stage_work(h, act_b), stage_ms):
-            f_st, b_st = 2.0 * w["macs"] * T * mb, float(w["bytes"]) * T * mb
+            f_st, b_st = 2.0 * w["macs"] * T * mean_fwd_batch, float(w["bytes"]) * T * mean_fwd_batch
             t_t, t_h = f_st / p_tensor * 1e3, b_st / bw * 1e3
             t_roof = max(t_t, t_h) if tensor_bound else t_h
             t_roof_sum += t_roof
@@ -330,15 +367,15 @@ def main():
         # dominant kernel: the stage with the largest measured time; all of its launches are conv_tc_kernel instances
         dom = max(range(len(stages)), key=lambda i: stages[i]["ms"])
         dw, dst = per_stage_work(h, act_b)[dom], stages[dom]
-        dom_flops_launch = 2.0 * dw["macs"] * T * mb / dw["launches"]
+        dom_flops_launch = 2.0 * dw["macs"] * T * mean_fwd_batch / dw["launches"]
         dom_ms_launch = dst["ms"] / dw["launches"]
-        dom_bytes_launch = float(dw["bytes"]) * T * mb / dw["launches"]
+        dom_bytes_launch = float(dw["bytes"]) * T * mean_fwd_batch / dw["launches"]
         dom_tensor = dst["bound"] == "tensor"              # the dominant stage's own binding roof (V2 / V3: HBM)
         achieved = (dom_flops_launch / (dom_ms_launch * 1e-3) / 1e12) if dom_tensor else (dom_bytes_launch / (dom_ms_launch * 1e-3) / 1e9)
         dom_peak = pk["tflops_sustained"] if dom_tensor else pk["hbm_gbs"]
-        traffic = ncu_traffic(dst["label"], args.config, mb)
+        traffic = ncu_traffic(dst["label"], args.config, mean_fwd_batch)
         line = {
-            "metric": "HiFi-GAN V1 audio-seconds/sec", "value": world * audio_s_per_step / (dev_ms / 1000), "unit": "audio-s/s",
+            "metric": metric_name(version), "value": world * audio_s_per_step / (dev_ms / 1000), "unit": "audio-s/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms, "higher_is_better": True,
             "scaling": "strong" if strong else "weak", "vs_baseline": None,
             "dtype": {"fp16": "fp16 (fp32 accumulate)", "bf16": "bf16 (fp32 accumulate)", "fp32": "fp32"}[args.precision],
@@ -356,16 +393,16 @@ def main():
                          "peak_source": pk["source"] + (" bf16 sustained (fp16 runs at the same tcgen05 rate; kernel timed inside a long step)" if dom_tensor
                                                         else " HBM copy bandwidth, sustained (layer-boundary bytes of the stage, SURVEY 8d)")},
             "roofline_step": {"achieved_tflops": flops / (dev_ms / 1000) / 1e12, "frac_of_tensor_peak": flops / (dev_ms / 1000) / p_tensor,
-                              "per_stage_roof_ms_per_step": t_roof_sum * (B / mb), "frac_of_per_stage_roofline": t_roof_sum * (B / mb) / dev_ms,
+                              "per_stage_roof_ms_per_step": t_roof_sum * n_forwards, "frac_of_per_stage_roofline": t_roof_sum * n_forwards / dev_ms,
                               "algorithmic_flops_per_step": flops, "layer_boundary_bytes_per_step": bytes_boundary,
                               "hbm_floor_ms": bytes_boundary / bw * 1000, "tensor_floor_ms": flops / p_tensor * 1000},
-            "stages": {"batch": mb, "rows": stages},
+            "stages": {"batch": mean_fwd_batch, "forwards_per_step": n_forwards, "rows": stages},
             "adjacent": adjacent,
         }
         if not args.no_cpu_baseline and world == 1:
             # CPU baseline on rank 0: BASELINE.json configs[0] (V1, batch 1, 256 frames), oracle port
             best, mean, threads, ts = cpu_port_audio_s_per_s("1", 1, 256, 5)
-            line["cpu_baseline"] = {"value": best, "unit": "audio-s/s", "cores": threads, "kind": "port",
+            line["cpu_baseline"] = {"value": best, "unit": "audio-s/s", "cores": threads, "kind": "port", "tf_reference": tf_pin(),
                                     "sample": "V1 batch 1 x 256 frames (configs[0]), best of 5; torch-CPU fp32 restatement of "
                                               "HiFiGAN_TF/model.py (TensorFlow not installable on this image)"}
         emit(line)

@@ -87,15 +87,23 @@ def load():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
-        # a fresh checkout (the .so is a git-ignored artefact): compile it in-tree if nvcc is here; never fall back
+    # The .so is a git-ignored artefact.  When nvcc and the sources are here, (re)build it whenever the source digest
+    # differs from the stamp of the binary (a stale library would be used silently otherwise); one process builds under a
+    # file lock, the other ranks of a torchrun launch wait for it.  Without nvcc (a box that only received the prebuilt
+    # library) the existing binary is used as shipped.  There is never a fallback to another implementation.
+    from . import build as _build
+    stale = not os.path.exists(LIB_PATH)
+    if not stale and _build.have_nvcc():
+        stale = not _build.is_current()
+    if stale:
         try:
-            from .build import build
-            build()
+            _build.build_locked()
         except Exception as e:
-            raise ImportError(
-                f"{LIB_PATH} is missing and could not be built ({e}): run `python -m neuraltexttospeech_b200.build` "
-                "(or __graft_entry__.build()). There is no CPU / PyTorch fallback for the generator.") from e
+            if not os.path.exists(LIB_PATH):
+                raise ImportError(
+                    f"{LIB_PATH} is missing and could not be built ({e}): run `python -m neuraltexttospeech_b200.build` "
+                    "(or __graft_entry__.build()). There is no CPU / PyTorch fallback for the generator.") from e
+            raise
     lib = C.CDLL(LIB_PATH)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)          # AttributeError if the .so does not export it

@@ -42,6 +42,31 @@ def _digest() -> str:
     return h.hexdigest()
 
 
+def have_nvcc() -> bool:
+    return bool(shutil.which("nvcc")) or os.path.exists("/usr/local/cuda/bin/nvcc")
+
+
+def is_current() -> bool:
+    """True when the in-tree library was built from the sources as they are now."""
+    stamp = os.path.join(BUILD_DIR, "libhifigan_b200.sha256")
+    try:
+        return os.path.exists(LIB_PATH) and open(stamp).read().strip() == _digest()
+    except OSError:
+        return False
+
+
+def build_locked(verbose: bool = False) -> str:
+    """build() under an exclusive file lock: concurrent callers (the ranks of a torchrun launch) compile once."""
+    import fcntl
+    os.makedirs(BUILD_DIR, exist_ok=True)
+    with open(os.path.join(BUILD_DIR, ".build.lock"), "w") as lk:
+        fcntl.flock(lk, fcntl.LOCK_EX)
+        try:
+            return build(verbose=verbose)      # a waiter finds the stamp current and returns at once
+        finally:
+            fcntl.flock(lk, fcntl.LOCK_UN)
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     """Compile (if stale) and return the path of the shared library."""
     os.makedirs(BUILD_DIR, exist_ok=True)

@@ -265,7 +265,9 @@ __host__ __device__ constexpr uint32_t make_idesc(int n, bool bf16, int m = 128)
 template <typename T> struct H2;
 template <> struct H2<__half> {
   static __device__ __forceinline__ float2 up(uint32_t u) { return __half22float2(*reinterpret_cast<__half2*>(&u)); }
-  static __device__ __forceinline__ uint32_t down(float a, float b) { __half2 h = __floats2half2_rn(a, b); return *reinterpret_cast<uint32_t*>(&h); }
+  // saturating down-conversion (F2FP.SATFINITE, one instruction per pair): a value beyond +-65504 clamps instead of
+  // becoming inf (which the next layer's MMA would turn into NaN)
+  static __device__ __forceinline__ uint32_t down(float a, float b) { uint32_t r; asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a)); return r; }
   // leaky-relu on a packed pair: max(v, v*s) for 0 < s <= 1
   static __device__ __forceinline__ uint32_t lrelu(uint32_t u, float s) {
     __half2 v = *reinterpret_cast<__half2*>(&u);
@@ -275,7 +277,7 @@ template <> struct H2<__half> {
 };
 template <> struct H2<__nv_bfloat16> {
   static __device__ __forceinline__ float2 up(uint32_t u) { return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u)); }
-  static __device__ __forceinline__ uint32_t down(float a, float b) { __nv_bfloat162 h = __floats2bfloat162_rn(a, b); return *reinterpret_cast<uint32_t*>(&h); }
+  static __device__ __forceinline__ uint32_t down(float a, float b) { uint32_t r; asm("cvt.rn.satfinite.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a)); return r; }
   static __device__ __forceinline__ uint32_t lrelu(uint32_t u, float s) {
     __nv_bfloat162 v = *reinterpret_cast<__nv_bfloat162*>(&u);
     __nv_bfloat162 r = __hmax2(v, __hmul2(v, __float2bfloat162_rn(s)));

@@ -89,6 +89,10 @@ struct hfg_ctx {
   struct GraphEntry { const void* mel; const void* out; const void* ws; int B, T, sample_bytes; int uses; long long launches; cudaGraphExec_t exec; };
   std::vector<GraphEntry> graphs;
   bool use_graphs = true;
+  // pageable caller buffers are staged through pinned memory owned by the handle (one memcpy per micro-batch, overlapped
+  // with the neighbouring micro-batch's kernels); pinned / registered caller buffers are copied directly
+  char* pin_in = nullptr; size_t pin_in_bytes = 0;
+  char* pin_out = nullptr; size_t pin_out_bytes = 0;
   void* ws = nullptr; size_t ws_bytes = 0;
   float* d_mel = nullptr; size_t d_mel_bytes = 0;
   void* d_audio = nullptr; size_t d_audio_bytes = 0;   // fp32 audio or 16-bit PCM
@@ -460,10 +464,12 @@ struct Runner {
 };
 
 // audio_dev (fp32) or pcm_dev (16-bit PCM, see pcm16_of in kernels.cuh): exactly one is non-NULL
-int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev, int16_t* pcm_dev, char* ws, cudaStream_t s) {
+int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev, int16_t* pcm_dev, char* ws, size_t ws_bytes, cudaStream_t s) {
   const hfg_config& c = h->cfg;
   Workspace w;
-  workspace_layout(h, B, T, ws, &w);
+  // the layout depends on (B, T) (concurrent resblock chains take extra scratch): never trust the caller's sizing
+  const size_t ws_need = workspace_layout(h, B, T, ws, &w);
+  if (ws_need > ws_bytes) return fail(h, HFG_ERR_NOMEM, "workspace too small for %d x %d frames: need %zu bytes, got %zu", B, T, ws_need, ws_bytes);
   Runner r{h, s, B};
   const bool chains = use_chains(h, B, T);
   const int nk = c.num_kernels;
@@ -634,6 +640,12 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
   h->precision = precision;
   h->act = precision == HFG_PRECISION_FP32 ? ACT_F32 : (precision == HFG_PRECISION_FP16 ? ACT_F16 : ACT_BF16);
   const hfg_config& c = h->cfg;
+  // run_forward treats the resblock convs of a stage as one engine (pre-activated 16-bit storage and the 16-bit running
+  // MRF sum on the tcgen05 path, raw storage and the fp32 accumulator on the direct path).  A non-stock config can have
+  // one conv of a stage fall outside the tcgen05 tile table (tap span > kTcMaxSpan): the whole stage is then demoted to
+  // the direct kernels in a second pass.
+  std::vector<char> demote(h->layers.size(), 0);
+  for (int pass = 0; pass < 2; ++pass) {
   for (size_t li = 0; li < h->layers.size(); ++li) {
     Layer& L = h->layers[li];
     free_layer_device(L);
@@ -641,7 +653,7 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
     const bool is_post = (L.name == "conv_post"), is_pre = (L.name == "conv_pre");
     bool ok;
     const int pl = (is_pre || is_post) ? (L.dil * (L.k - 1)) / 2 : (L.transposed ? 0 : conv_pad_left(L.k, L.dil, c.compat, &ok));
-    const bool tc_mode = h->act != ACT_F32 && !h->force_ffma;
+    const bool tc_mode = h->act != ACT_F32 && !h->force_ffma && !demote[li];
     // fold factor of a [rows, C] tensor on the tcgen05 path: C*f = 16 when C < 16 and the row count is divisible
     auto fold_of = [&](int C, int rate) { return (tc_mode && C < 16 && 16 % C == 0 && rate % (16 / C) == 0) ? 16 / C : 1; };
     // conv_post rides the tcgen05 kernel (16-column tile, tanh/fp32 epilogue) when its input is stored pre-activated,
@@ -723,6 +735,23 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
     CUDA_TRY(h, cudaMalloc((void**)&L.d_bias, bias.size() * sizeof(float)));
     CUDA_TRY(h, cudaMemcpy(L.d_bias, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
   }
+  if (pass == 1) break;
+  bool any = false;
+  for (int i = 0; i < c.num_upsamples; ++i) {
+    bool all_tc = true, none_tc = true;
+    std::vector<int> ids;
+    for (int j = 0; j < c.num_kernels; ++j)
+      for (int m = 0; m < c.num_dilations[j]; ++m)
+        for (int which = 0; which < 2; ++which) {
+          const int id = h->i_rb[((size_t)(i * c.num_kernels + j) * HFG_MAX_DILATIONS + m) * 2 + which];
+          if (id < 0) continue;
+          ids.push_back(id);
+          if (h->layers[id].use_tc) none_tc = false; else all_tc = false;
+        }
+    if (!all_tc && !none_tc) { for (int id : ids) demote[id] = 1; any = true; }
+  }
+  if (!any) break;
+  }
   h->need_acc = false; h->need_sum = false;
   for (const Layer& L : h->layers)
     if (!L.transposed && L.name != "conv_pre" && L.name != "conv_post") { if (L.use_tc) h->need_sum = true; else h->need_acc = true; }
@@ -770,7 +799,7 @@ static int forward_device(hfg_handle h, const float* mel_dev, int B, int T, floa
   if ((size_t)(ws - (char*)workspace_dev) + need > workspace_bytes)
     return fail(h, HFG_ERR_NOMEM, "workspace too small: need %zu bytes, got %zu", need + 256, workspace_bytes);
   CUDA_TRY(h, cudaSetDevice(h->device));
-  return run_forward(h, mel_dev, B, T, audio_dev, pcm_dev, ws, (cudaStream_t)stream);
+  return run_forward(h, mel_dev, B, T, audio_dev, pcm_dev, ws, workspace_bytes - (size_t)(ws - (char*)workspace_dev), (cudaStream_t)stream);
 }
 
 int hfg_forward(hfg_handle h, const float* mel_dev, int B, int T, float* audio_dev, void* workspace_dev,
@@ -783,13 +812,29 @@ int hfg_forward_pcm16(hfg_handle h, const float* mel_dev, int B, int T, int16_t*
   return forward_device(h, mel_dev, B, T, nullptr, pcm_dev, workspace_dev, workspace_bytes, stream, "hfg_forward_pcm16");
 }
 
+// true when the CUDA runtime knows `p` as page-locked host memory (cudaHostAlloc / cudaHostRegister / managed)
+static bool host_is_pinned(const void* p) {
+  cudaPointerAttributes at{};
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged;
+}
+
+static int grow_pinned(hfg_ctx* h, char** buf, size_t* have, size_t need) {
+  if (need <= *have) return HFG_OK;
+  if (*buf) cudaFreeHost(*buf);
+  *buf = nullptr; *have = 0;
+  CUDA_TRY(h, cudaHostAlloc((void**)buf, need, cudaHostAllocDefault));
+  *have = need;
+  return HFG_OK;
+}
+
 // One micro-batch of the host path on h->stream.  Launch-bound forwards (few frames) are replayed from a CUDA graph
 // captured on the second use of the same (buffers, shape): 79 launches + 230 tensor-map encodes become one graph launch.
 static int forward_maybe_graph(hfg_ctx* h, const float* mel, int nb, int T, char* dev_out, int sample_bytes) {
   float* audio = sample_bytes == 4 ? (float*)dev_out : nullptr;
   int16_t* pcm = sample_bytes == 2 ? (int16_t*)dev_out : nullptr;
   const bool eligible = h->use_graphs && !h->stage_timing && (long long)nb * T <= 8192;
-  if (!eligible) return run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->stream);
+  if (!eligible) return run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->ws_bytes, h->stream);
   hfg_ctx::GraphEntry* e = nullptr;
   for (auto& g : h->graphs)
     if (g.mel == mel && g.out == dev_out && g.ws == h->ws && g.B == nb && g.T == T && g.sample_bytes == sample_bytes) { e = &g; break; }
@@ -803,9 +848,9 @@ static int forward_maybe_graph(hfg_ctx* h, const float* mel, int nb, int T, char
     CUDA_TRY(h, cudaGraphLaunch(e->exec, h->stream));
     return HFG_OK;
   }
-  if (e->uses++ == 0) return run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->stream);   // first use: plain (also warms per-kernel attributes)
+  if (e->uses++ == 0) return run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->ws_bytes, h->stream);   // first use: plain (also warms per-kernel attributes)
   CUDA_TRY(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
-  int rc = run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->stream);
+  int rc = run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->ws_bytes, h->stream);
   cudaGraph_t graph = nullptr;
   cudaError_t ce = cudaStreamEndCapture(h->stream, &graph);
   if (rc || ce != cudaSuccess || !graph) {
@@ -813,11 +858,11 @@ static int forward_maybe_graph(hfg_ctx* h, const float* mel, int nb, int T, char
     cudaGetLastError();
     h->use_graphs = false;                               // capture unsupported here: stay on plain launches
     if (rc) return rc;
-    return run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->stream);
+    return run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->ws_bytes, h->stream);
   }
   ce = cudaGraphInstantiate(&e->exec, graph, 0);
   cudaGraphDestroy(graph);
-  if (ce != cudaSuccess) { e->exec = nullptr; cudaGetLastError(); h->use_graphs = false; return run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->stream); }
+  if (ce != cudaSuccess) { e->exec = nullptr; cudaGetLastError(); h->use_graphs = false; return run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->ws_bytes, h->stream); }
   e->launches = h->launches;
   CUDA_TRY(h, cudaGraphLaunch(e->exec, h->stream));
   return HFG_OK;
@@ -850,7 +895,10 @@ static int forward_host(hfg_handle h, const float* mel_host, int B, int T, void*
     for (int left = B; left > 0; left -= mb) parts.push_back(left < mb ? left : mb);
   }
   const size_t mel_elems = (size_t)T * h->cfg.num_mels, aud_elems = (size_t)T * h->total_up;
-  const size_t need_ws = workspace_layout(h, mb, T, nullptr, nullptr);
+  // every part lays out its own workspace (a small part may run its resblocks as concurrent chains with extra scratch
+  // while a larger one does not): size the allocation for the most demanding part
+  size_t need_ws = 0;
+  for (int nb : parts) need_ws = std::max(need_ws, workspace_layout(h, nb, T, nullptr, nullptr));
   if (need_ws > h->ws_bytes) {
     clear_graphs(h);
     if (h->ws) cudaFree(h->ws);
@@ -877,31 +925,56 @@ static int forward_host(hfg_handle h, const float* mel_host, int B, int T, void*
   if (!h->h2d_stream) CUDA_TRY(h, cudaStreamCreateWithFlags(&h->h2d_stream, cudaStreamNonBlocking));
   if (!h->d2h_stream) CUDA_TRY(h, cudaStreamCreateWithFlags(&h->d2h_stream, cudaStreamNonBlocking));
   const int n_mb = (int)parts.size();
-  while ((int)h->copy_events.size() < 2 * n_mb) {
+  while ((int)h->copy_events.size() < 3 * n_mb) {
     cudaEvent_t ev;
     CUDA_TRY(h, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     h->copy_events.push_back(ev);
   }
+  // Pageable caller memory: cudaMemcpyAsync would stage it synchronously inside the driver and serialise with the kernel
+  // launches.  It is staged here instead, one micro-batch at a time: the memcpy of part i+1's mels and of part i-1's
+  // waveforms run on the host while part i computes.
+  const bool in_direct = host_is_pinned(mel_host), out_direct = host_is_pinned(out_host);
+  if (!in_direct) { int rc = grow_pinned(h, &h->pin_in, &h->pin_in_bytes, (size_t)B * mel_elems * 4); if (rc) return rc; }
+  if (!out_direct) { int rc = grow_pinned(h, &h->pin_out, &h->pin_out_bytes, (size_t)B * aud_elems * sample_bytes); if (rc) return rc; }
+  const char* src_base = in_direct ? (const char*)mel_host : h->pin_in;
+  char* dst_base = out_direct ? (char*)out_host : h->pin_out;
+  auto drain = [&](int i, int b0) -> int {               // part i's waveforms: pinned staging -> the caller's pageable buffer
+    if (out_direct) return HFG_OK;
+    CUDA_TRY(h, cudaEventSynchronize(h->copy_events[3 * i + 2]));
+    const size_t off = (size_t)b0 * aud_elems * sample_bytes;
+    memcpy((char*)out_host + off, h->pin_out + off, (size_t)parts[i] * aud_elems * sample_bytes);
+    return HFG_OK;
+  };
+  auto upload = [&](int i, int b0) -> int {
+    const size_t off = (size_t)b0 * mel_elems * 4, bytes = (size_t)parts[i] * mel_elems * 4;
+    if (!in_direct) memcpy(h->pin_in + off, (const char*)mel_host + off, bytes);
+    CUDA_TRY(h, cudaMemcpyAsync((char*)h->d_mel + off, src_base + off, bytes, cudaMemcpyHostToDevice, h->h2d_stream));
+    CUDA_TRY(h, cudaEventRecord(h->copy_events[3 * i], h->h2d_stream));
+    return HFG_OK;
+  };
   long long launches = 0;
-  for (int i = 0, b0 = 0; i < n_mb; b0 += parts[i], ++i) {
-    const int nb = parts[i];
-    CUDA_TRY(h, cudaMemcpyAsync(h->d_mel + (size_t)b0 * mel_elems, mel_host + (size_t)b0 * mel_elems, (size_t)nb * mel_elems * 4,
-                                cudaMemcpyHostToDevice, h->h2d_stream));
-    CUDA_TRY(h, cudaEventRecord(h->copy_events[2 * i], h->h2d_stream));
-  }
-  for (int i = 0, b0 = 0; i < n_mb; b0 += parts[i], ++i) {
-    const int nb = parts[i];
+  std::vector<int> starts(n_mb, 0);
+  for (int i = 1; i < n_mb; ++i) starts[i] = starts[i - 1] + parts[i - 1];
+  if (in_direct) { for (int i = 0; i < n_mb; ++i) { int rc = upload(i, starts[i]); if (rc) return rc; } }
+  else { int rc = upload(0, 0); if (rc) return rc; }
+  for (int i = 0; i < n_mb; ++i) {
+    const int nb = parts[i], b0 = starts[i];
     char* dev_out = (char*)h->d_audio + (size_t)b0 * aud_elems * sample_bytes;
-    CUDA_TRY(h, cudaStreamWaitEvent(h->stream, h->copy_events[2 * i], 0));
+    CUDA_TRY(h, cudaStreamWaitEvent(h->stream, h->copy_events[3 * i], 0));
     int rc = forward_maybe_graph(h, h->d_mel + (size_t)b0 * mel_elems, nb, T, dev_out, sample_bytes);
     launches += h->launches; h->launches = 0;
     if (rc) { cudaStreamSynchronize(h->h2d_stream); cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->d2h_stream); return rc; }
-    CUDA_TRY(h, cudaEventRecord(h->copy_events[2 * i + 1], h->stream));
-    CUDA_TRY(h, cudaStreamWaitEvent(h->d2h_stream, h->copy_events[2 * i + 1], 0));
-    CUDA_TRY(h, cudaMemcpyAsync((char*)out_host + (size_t)b0 * aud_elems * sample_bytes, dev_out,
+    CUDA_TRY(h, cudaEventRecord(h->copy_events[3 * i + 1], h->stream));
+    CUDA_TRY(h, cudaStreamWaitEvent(h->d2h_stream, h->copy_events[3 * i + 1], 0));
+    CUDA_TRY(h, cudaMemcpyAsync(dst_base + (size_t)b0 * aud_elems * sample_bytes, dev_out,
                                 (size_t)nb * aud_elems * sample_bytes, cudaMemcpyDeviceToHost, h->d2h_stream));
+    CUDA_TRY(h, cudaEventRecord(h->copy_events[3 * i + 2], h->d2h_stream));
+    // while part i runs on the GPU: stage the next part's mels, hand the previous part's waveforms to the caller
+    if (!in_direct && i + 1 < n_mb) { rc = upload(i + 1, starts[i + 1]); if (rc) return rc; }
+    if (i > 0) { rc = drain(i - 1, starts[i - 1]); if (rc) return rc; }
   }
   h->launches = launches;
+  { int rc = drain(n_mb - 1, starts[n_mb - 1]); if (rc) return rc; }
   CUDA_TRY(h, cudaStreamSynchronize(h->d2h_stream));
   CUDA_TRY(h, cudaStreamSynchronize(h->stream));
   return HFG_OK;
@@ -1075,6 +1148,8 @@ void hfg_destroy(hfg_handle h) {
   for (Layer& L : h->layers) free_layer_device(L);
   for (auto& ev : h->events) cudaEventDestroy(ev);
   if (h->ws) cudaFree(h->ws);
+  if (h->pin_in) cudaFreeHost(h->pin_in);
+  if (h->pin_out) cudaFreeHost(h->pin_out);
   if (h->d_mel) cudaFree(h->d_mel);
   if (h->d_audio) cudaFree(h->d_audio);
   if (h->stream) cudaStreamDestroy(h->stream);

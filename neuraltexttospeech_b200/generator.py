@@ -69,6 +69,58 @@ def _config_from_hparams(h, compat: str) -> _lib.HfgConfig:
     return cfg
 
 
+class _PinnedBlock:
+    """One page-locked host allocation (hfg_host_alloc) exposed through the array interface.  A numpy array built on
+    it keeps it alive through `.base`; when the last view is dropped the block goes back to its pool, so a loop of
+    `audio = generator(mel)` calls reuses the same few pinned buffers instead of allocating (and page-faulting) a fresh
+    pageable array every call."""
+
+    def __init__(self, pool, ptr: int, nbytes: int, shape, typestr: str):
+        self._pool, self._ptr, self._nbytes = pool, ptr, nbytes
+        self.__array_interface__ = {"version": 3, "data": (ptr, False), "shape": tuple(shape), "typestr": typestr}
+
+    def __del__(self):
+        try:
+            self._pool.release(self._ptr, self._nbytes)
+        except Exception:
+            pass
+
+
+class _PinnedPool:
+    """Free lists of pinned host buffers by size (at most `keep` cached per size)."""
+
+    def __init__(self, lib, keep: int = 3):
+        self._lib, self._keep, self._free, self._closed = lib, keep, {}, False
+
+    def array(self, shape, dtype) -> np.ndarray:
+        dtype = np.dtype(dtype)
+        nbytes = int(np.prod(shape)) * dtype.itemsize
+        if nbytes == 0 or self._closed:
+            return np.empty(shape, dtype)
+        lst = self._free.get(nbytes)
+        if lst:
+            ptr = lst.pop()
+        else:
+            p = C.c_void_p()
+            _lib.check(self._lib.hfg_host_alloc(C.byref(p), nbytes), None, "hfg_host_alloc")
+            ptr = int(p.value)
+        return np.asarray(_PinnedBlock(self, ptr, nbytes, shape, dtype.str))
+
+    def release(self, ptr: int, nbytes: int) -> None:
+        lst = self._free.setdefault(nbytes, [])
+        if self._closed or len(lst) >= self._keep:
+            self._lib.hfg_host_free(C.c_void_p(ptr))
+        else:
+            lst.append(ptr)
+
+    def close(self) -> None:
+        self._closed = True
+        for lst in self._free.values():
+            for ptr in lst:
+                self._lib.hfg_host_free(C.c_void_p(ptr))
+        self._free = {}
+
+
 class Generator:
     def __init__(self, hparams, precision: str = "fp16", device: int = 0, compat: str = "reference"):
         self.hparams = coerce_hparams(hparams)
@@ -87,6 +139,7 @@ class Generator:
         _lib.check(self._lib.hfg_create(C.byref(cfg), self.device, C.byref(self._handle)), None, "hfg_create")
         self._weights_loaded = False
         self._ws = None           # torch workspace for the device-pointer path
+        self._pinned = _PinnedPool(self._lib)    # outputs of the host path (numpy in -> numpy out)
 
     # ------------------------------------------------------------------ weights
     def load_weights(self, weights: Union[str, Mapping[str, np.ndarray]]) -> "Generator":
@@ -160,7 +213,9 @@ class Generator:
         mel = np.ascontiguousarray(mel, dtype=np.float32)
         B, T = int(mel.shape[0]), int(mel.shape[1])
         if out is None:
-            out = np.empty((B, T * self._total_up, 1), dtype=np.float32)
+            # the result is an ordinary numpy array owned by the caller; its memory is page-locked and recycled through
+            # the generator's pool when the array is dropped, so the device->host copy runs asynchronously at link speed
+            out = self._pinned.array((B, T * self._total_up, 1), np.float32)
         _lib.check(self._lib.hfg_forward_host(self._handle, mel.ctypes.data_as(C.c_void_p), B, T,
                                               out.ctypes.data_as(C.c_void_p)), self._handle, "hfg_forward_host")
         return out
@@ -217,7 +272,7 @@ class Generator:
         self._check_shape(mel.shape)
         mel = np.ascontiguousarray(mel, dtype=np.float32)
         B, T = int(mel.shape[0]), int(mel.shape[1])
-        out = np.empty((B, T * self._total_up), dtype=np.int16)
+        out = self._pinned.array((B, T * self._total_up), np.int16)
         _lib.check(self._lib.hfg_forward_host_pcm16(self._handle, mel.ctypes.data_as(C.c_void_p), B, T,
                                                     out.ctypes.data_as(C.c_void_p)), self._handle, "hfg_forward_host_pcm16")
         return torch.from_numpy(out) if as_torch else out
@@ -308,6 +363,8 @@ class Generator:
             self._lib.hfg_destroy(self._handle)
             self._handle = C.c_void_p()
         self._ws = None
+        if getattr(self, "_pinned", None) is not None:
+            self._pinned.close()
 
     def __del__(self):
         try:

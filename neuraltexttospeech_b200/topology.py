@@ -58,6 +58,14 @@ def is_resblock1(h) -> bool:
     return h.resblock == "1"
 
 
+def used_dilations(h) -> List[List[int]]:
+    """The dilation entries the reference's resblocks consume: ResBlock1 reads dilation[0..2] (reference
+    HiFiGAN_TF/model.py:21-66), ResBlock2 dilation[0..1] (model.py:84-101).  Longer lists are truncated exactly like
+    the C engine does (generator._config_from_hparams); shorter ones are an error there."""
+    need = 3 if is_resblock1(h) else 2
+    return [[int(d) for d in list(ds)[:need]] for ds in h.resblock_dilation_sizes]
+
+
 def enumerate_layers(h) -> List[LayerSpec]:
     layers: List[LayerSpec] = []
     c0 = int(h.upsample_initial_channel)
@@ -68,7 +76,7 @@ def enumerate_layers(h) -> List[LayerSpec]:
     for i, (u, ku) in enumerate(zip(h.upsample_rates, h.upsample_kernel_sizes)):
         c = chans[i]
         layers.append(LayerSpec(f"ups.{i}", "convT", int(ku), c_prev, c, 1, int(u), "same"))
-        for j, (k, dils) in enumerate(zip(h.resblock_kernel_sizes, h.resblock_dilation_sizes)):
+        for j, (k, dils) in enumerate(zip(h.resblock_kernel_sizes, used_dilations(h))):
             n = i * nk + j
             if is_resblock1(h):
                 for m, d in enumerate(dils):

@@ -230,12 +230,19 @@ def _get(h, name):
     return h[name] if isinstance(h, dict) else getattr(h, name)
 
 
+def used_dilations(h):
+    """The dilation entries the reference's resblocks actually consume: ResBlock1 builds convs from dilation[0..2]
+    (reference HiFiGAN_TF/model.py:21-66), ResBlock2 from dilation[0..1] (model.py:84-101); longer lists are ignored."""
+    need = 3 if _get(h, "resblock") == "1" else 2
+    return [[int(d) for d in list(ds)[:need]] for ds in _get(h, "resblock_dilation_sizes")]
+
+
 def layer_names(h):
     """Weight-bearing layers in construction/call order -> (name, kind, k, dil, stride, cin, cout)."""
     c0 = int(_get(h, "upsample_initial_channel"))
     num_mels = int(h.get("num_mels", 80)) if isinstance(h, dict) else int(getattr(h, "num_mels", 80))
     rks = list(_get(h, "resblock_kernel_sizes"))
-    rds = list(_get(h, "resblock_dilation_sizes"))
+    rds = used_dilations(h)
     rb1 = _get(h, "resblock") == "1"
     out = [("conv_pre", "conv", 7, 1, 1, num_mels, c0)]
     cprev = c0
@@ -294,7 +301,7 @@ def generator_forward(h, weights, mel, backend="numpy64", compat="reference", ta
         return wt, bt
 
     rks = list(_get(h, "resblock_kernel_sizes"))
-    rds = list(_get(h, "resblock_dilation_sizes"))
+    rds = used_dilations(h)
     rates = list(_get(h, "upsample_rates"))
     rb1 = _get(h, "resblock") == "1"
     nk = len(rks)

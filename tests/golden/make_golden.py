@@ -18,6 +18,19 @@ Fixtures
                               fold axes, the MRF order and the residual wiring.  The two
                               reference quirks (causal k=3 convs, slope 0.3) are NOT covered
                               by any runnable reference code here: "parity unpinned" for them.
+  quirks_v{1,2,3}.npz         a SECOND, independently written derivation of the two reference quirks, run on
+                              the vendored torch modules themselves (not on the oracle's conv code):
+                              Q1 -- every ResBlock Conv1d for which the reference's own get_padding
+                              (HiFiGAN_TF/utils.py:29-37) answers "causal" is wrapped so that the vendored,
+                              symmetrically padded torch conv sees its input delayed by p = d(k-1)/2 samples
+                              (p zeros prepended, last p outputs dropped): y_sym[t - p] = sum_j x[t + j*d - 2p] W[j],
+                              which is Keras' causal Conv1D (left pad d(k-1), right pad 0);
+                              Q2 -- the module-level `F` of the vendored file is replaced by a shim whose
+                              leaky_relu default slope is Keras' LeakyReLU() default 0.3 (HiFiGAN_TF/model.py:152),
+                              so the vendored forward() runs unmodified.
+                              The oracle in compat="reference" must reproduce it (tests/test_oracle.py) and so
+                              must the CUDA fp32 mode (tests/test_generator_gpu.py).  TensorFlow itself is still
+                              not in the loop: the TF boundary stays "parity unpinned".
 """
 import os
 import sys
@@ -76,6 +89,7 @@ def _upstream_generator(h, keep_weight_norm=False):
                     rb.lrelu_slope = mod.LRELU_SLOPE
     if not keep_weight_norm:
         gen.remove_weight_norm()
+    gen._vendored_module = mod
     return gen.eval()
 
 
@@ -105,6 +119,53 @@ def _load_folded(gen, h, weights):
         else:
             for m in range(2):
                 put(rb.convs[m], f"resblocks.{n}.convs.{m}", "conv")
+
+
+def _reference_padding_string(k, d):
+    """reference HiFiGAN_TF/utils.py:29-37, restated here on purpose (this script must not lean on the oracle for Q1)."""
+    pad = int((k * d - d) / 2)
+    return "valid" if pad == 0 else ("causal" if pad == 1 else "same")
+
+
+def _apply_reference_quirks(gen, mod):
+    """Turn the vendored upstream torch generator into the reference's arithmetic without touching its forward()."""
+    import torch
+    import torch.nn.functional as TF
+
+    class DelayedInput(torch.nn.Module):          # symmetric conv on a delayed input == Keras causal conv
+        def __init__(self, conv):
+            super().__init__()
+            self.conv = conv
+            k, d = conv.kernel_size[0], conv.dilation[0]
+            self.p = d * (k - 1) // 2
+            assert conv.padding[0] == self.p and conv.stride[0] == 1
+
+        def forward(self, x):
+            n = x.shape[-1]
+            return self.conv(TF.pad(x, (self.p, 0)))[..., :n]
+
+    blocks = list(gen.resblocks)
+    if blocks and isinstance(blocks[0], torch.nn.Sequential):
+        blocks = [rb for group in blocks for rb in group]
+    n_wrapped = 0
+    for rb in blocks:
+        for lst in [getattr(rb, a) for a in ("convs1", "convs2", "convs") if hasattr(rb, a)]:
+            for m in range(len(lst)):
+                c = lst[m]
+                if _reference_padding_string(c.kernel_size[0], c.dilation[0]) == "causal":
+                    lst[m] = DelayedInput(c)
+                    n_wrapped += 1
+
+    class KerasDefaultsF:                          # `F` as the vendored file sees it
+        def __getattr__(self, name):
+            return getattr(TF, name)
+
+        @staticmethod
+        def leaky_relu(x, negative_slope=0.3):     # keras.layers.LeakyReLU() default alpha (model.py:152)
+            return TF.leaky_relu(x, negative_slope)
+
+    mod.F = KerasDefaultsF()
+    return n_wrapped
 
 
 def make_adjacent():
@@ -151,6 +212,21 @@ def main():
             print(f"v{v}: upstream torch vs oracle(compat=upstream) max-abs {err:.3e}; amp {np.abs(y).max():.3f}")
             assert err < 2e-5, err
             np.savez_compressed(os.path.join(HERE, f"upstream_v{v}.npz"), mel=mel, audio=y.astype(np.float32))
+            # second derivation of the reference quirks Q1/Q2 on the vendored modules (see the header)
+            gen = _upstream_generator(h)
+            _load_folded(gen, h, w)
+            nw = _apply_reference_quirks(gen, gen._vendored_module)
+            mel_q = synthetic_mel(B, 13, h.num_mels, seed=4321 + int(v))
+            with torch.no_grad():
+                yq = gen(torch.from_numpy(mel_q).permute(0, 2, 1).contiguous()).permute(0, 2, 1).contiguous().numpy()
+            mine = O.generator_forward(h, w, mel_q, "numpy64", "reference")
+            up = O.generator_forward(h, w, mel_q, "numpy64", "upstream")
+            err = float(np.abs(mine - yq).max())
+            print(f"v{v}: vendored torch + quirks ({nw} causal convs) vs oracle(compat=reference) max-abs {err:.3e}; "
+                  f"distance to compat=upstream {np.abs(up - yq).max():.3e}")
+            assert err < 2e-5, err
+            assert np.abs(up - yq).max() > 1e-3            # the quirks matter: the fixture tells the two modes apart
+            np.savez_compressed(os.path.join(HERE, f"quirks_v{v}.npz"), mel=mel_q, audio=yq.astype(np.float32), causal_convs=np.int64(nw))
 
 
 if __name__ == "__main__":

@@ -249,7 +249,98 @@ def test_cuda_array_interface_input(gens):
         g(Foreign(t.double()))
 
 
-@pytest.mark.parametrize("v,B", [("1", 3), ("3", 2)])
+@pytest.mark.parametrize("v", "123")
+def test_fp32_mode_matches_causalised_vendored_torch_fixture(v, gens, golden_dir):
+    """quirks_v*.npz: the reference's quirks (causal k=3/d=1 convs, final slope 0.3) derived a second time on the vendored
+    torch modules (tests/golden/make_golden.py) -- an output neither this library nor the oracle produced."""
+    z = np.load(os.path.join(golden_dir, f"quirks_v{v}.npz"))
+    out = gens(v, "fp32", "B")(z["mel"])
+    assert np.abs(out - z["audio"]).max() <= 2e-5
+    out16 = gens(v, "fp16", "B")(z["mel"])
+    assert np.abs(out16 - z["audio"]).max() <= TC_TOL and snr_db(z["audio"], out16) >= TC_SNR
+
+
+def test_micro_batch_of_config5_runs_as_one_forward(gens):
+    # BASELINE configs[4] (512 x 10 s on one GPU) is walked in micro-batches of hfg_auto_micro_batch(512, 862) = 76
+    # utterances: one forward of that batch size (B > 64), at a short T the CPU oracle finishes quickly
+    import torch
+    h = HParams.builtin("1")
+    g = gens("1", "fp16")
+    B = g.auto_micro_batch(512, 862)
+    assert B == 76
+    w = synthetic_weights(h, "B")
+    mel = synthetic_mel(B, 6, h.num_mels, seed=76)
+    ref = O.generator_forward(h, w, mel, "torch32")
+    out = g(torch.from_numpy(mel).cuda()).cpu().numpy()          # device path: the whole batch in one forward
+    assert out.shape == ref.shape
+    assert np.abs(out - ref).max() <= TC_TOL and snr_db(ref, out) >= TC_SNR
+    assert np.array_equal(g(mel), out)                            # host path (micro-batched) gives the same bits
+
+
+@pytest.mark.parametrize("v,B,T", [("1", 17, 228), ("3", 64, 100)])
+def test_host_path_parts_straddling_the_chain_threshold(v, B, T, gens):
+    """Round-1 advisor finding: the host path sized its workspace for the LARGEST micro-batch, but a smaller part of the
+    same call can fall below the concurrent-resblock threshold (B*T <= 2048 frames) and lay out MORE scratch than the
+    larger one (V1 17 x 228 -> parts 9 + 8; V3 64 x 100 -> 16 + 32 + 16).  The allocation now covers every part and
+    run_forward checks the layout against it; results must equal the device path on the whole batch."""
+    import torch
+    g = gens(v, "fp16")
+    mel = synthetic_mel(B, T, 80, seed=B)
+    host = g(mel)
+    dev = g(torch.from_numpy(mel).cuda()).cpu().numpy()
+    assert np.array_equal(host, dev)
+    h = HParams.builtin(v)
+    ref = O.generator_forward(h, synthetic_weights(h, "B"), mel[:2], "torch32")
+    assert np.abs(host[:2] - ref).max() <= TC_TOL
+
+
+def test_stage_with_a_conv_outside_the_tile_table_is_demoted_as_a_whole():
+    """Round-1 advisor finding: a non-stock config whose dilated conv exceeds the tcgen05 kernel's tap span (k=7, d=17:
+    span 102 > 96) used to leave ONE conv of the stage on the direct kernel while its neighbours kept the pre-activated
+    16-bit convention.  Stages are now uniform: the resblock convs of such a stage all run on the direct kernels."""
+    import dataclasses
+    h = dataclasses.replace(HParams.builtin("3"), resblock_kernel_sizes=[3, 7], resblock_dilation_sizes=[[1, 2], [2, 17]])
+    w = synthetic_weights(h, "B")
+    mel = synthetic_mel(2, 14, h.num_mels, seed=17)
+    ref = O.generator_forward(h, w, mel, "torch32")
+    g = Generator(h, precision="fp16").load_weights(w)
+    eng = g.layer_engines()
+    rb = {k: e for k, e in eng.items() if k.startswith("resblocks")}
+    assert set(rb.values()) == {"ffma"}, rb                       # span 102 in every stage -> every stage demoted
+    assert eng["ups.0"] == "tc" and eng["conv_pre"] == "tc"
+    out = g(mel)
+    g.close()
+    assert np.abs(out - ref).max() <= TC_TOL and snr_db(ref, out) >= TC_SNR
+
+
+def test_fp16_range_hot_trunk_and_saturation():
+    """fp16 storage has a 65504 ceiling (the north star names bf16/TF32; fp16 is this library's deviation).
+    leaky-relu is positively homogeneous, so a gain on conv_pre scales every activation of the trunk: with conv_pre's
+    g x 8 / x 64 and the hottest mel of the synthetic range (all +2.0) the 16-bit trunk and the raw 16-bit MRF running sum
+    must keep the north-star SNR (the waveform is 5x hotter and partly in tanh saturation, so the absolute bound is
+    scaled with it); with a gain that drives the trunk past 65504 the epilogue's saturating conversion must keep the
+    waveform finite (no inf -> NaN through the next MMA)."""
+    h = HParams.builtin("1")
+    w0 = dict(synthetic_weights(h, "B"))
+    mel = np.full((2, 24, h.num_mels), 2.0, np.float32)
+    mel += synthetic_mel(2, 24, h.num_mels, seed=5) * 0.05
+    g = Generator(h, precision="fp16")
+    for gain, lo, tol in ((8.0, 20.0, 1e-2), (64.0, 200.0, 5e-2)):
+        w = dict(w0); w["conv_pre.g"] = w0["conv_pre.g"] * gain
+        taps = {}
+        ref = O.generator_forward(h, w, mel, "torch32", taps=taps)
+        peak = max(float(np.abs(t).max()) for t in taps.values())
+        assert lo < peak < 2.0e4, peak                            # hot, but inside fp16 with room for the 3-way MRF sum
+        out = g.load_weights(w)(mel)
+        assert np.isfinite(out).all()
+        assert snr_db(ref, out) >= TC_SNR and np.abs(out - ref).max() <= tol, (gain, snr_db(ref, out), np.abs(out - ref).max())
+    w = dict(w0); w["conv_pre.g"] = w0["conv_pre.g"] * 65536.0    # trunk far beyond 65504
+    out = g.load_weights(w)(mel)
+    g.close()
+    assert np.isfinite(out).all() and np.abs(out).max() <= 1.0
+
+
+@pytest.mark.parametrize("v,B", [("1", 3), ("2", 2), ("3", 2)])
 def test_full_length_utterances_match_oracle(v, B, gens):
     """10-second utterances (862 frames): every stage has more tiles than SMs, so the full-height tile
     configurations, the CTA-pair kernels and the folded layers run at the bench's own shapes."""

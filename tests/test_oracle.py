@@ -25,6 +25,36 @@ def test_oracle_matches_upstream_torch_fixture(v, golden_dir):
 
 
 @pytest.mark.parametrize("v", "123")
+def test_oracle_reference_quirks_match_causalised_vendored_torch_fixture(v, golden_dir):
+    """quirks_v*.npz: the vendored upstream torch generator with the reference's two quirks derived a second time on
+    the torch modules themselves (delayed-input causal convs chosen by the reference's get_padding rule, Keras' 0.3
+    default slope) -- see tests/golden/make_golden.py.  Pins compat="reference" of the oracle to something it did not
+    produce itself (TensorFlow still is not in the loop)."""
+    z = np.load(os.path.join(golden_dir, f"quirks_v{v}.npz"))
+    h = HParams.builtin(v)
+    w = synthetic_weights(h, "B")
+    assert int(z["causal_convs"]) == sum(1 for (name, kind, k, d, s_, ci, co) in O.layer_names(h)
+                                         if kind == "conv" and name.startswith("resblocks") and O.padding_mode(k, d) == "causal")
+    for backend, tol in (("numpy64", 2e-5), ("torch32", 2e-5)):
+        y = O.generator_forward(h, w, z["mel"], backend, "reference")
+        assert y.shape == z["audio"].shape
+        assert np.abs(y - z["audio"]).max() < tol, backend
+    assert np.abs(O.generator_forward(h, w, z["mel"], "numpy64", "upstream") - z["audio"]).max() > 1e-3
+
+
+def test_dilation_lists_longer_than_the_reference_consumes_are_truncated():
+    # ResBlock1 reads dilation[0..2], ResBlock2 dilation[0..1] (reference model.py:21-66, 84-101)
+    from neuraltexttospeech_b200.topology import enumerate_layers
+    import dataclasses
+    for v, need in (("1", 3), ("3", 2)):
+        h = HParams.builtin(v)
+        longer = dataclasses.replace(h, resblock_dilation_sizes=[list(d) + [7, 9] for d in h.resblock_dilation_sizes])
+        assert [L.name for L in enumerate_layers(longer)] == [L.name for L in enumerate_layers(h)]
+        assert [n[0] for n in O.layer_names(longer)] == [n[0] for n in O.layer_names(h)]
+        assert all(len(d) == need for d in O.used_dilations(longer))
+
+
+@pytest.mark.parametrize("v", "123")
 @pytest.mark.parametrize("variant", "AB")
 def test_oracle_fp32_backends_match_fp64_fixture(v, variant, golden_dir):
     z = np.load(os.path.join(golden_dir, f"oracle_v{v}_{variant}.npz"))
