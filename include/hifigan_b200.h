@@ -108,7 +108,8 @@ int hfg_forward_pcm16(hfg_handle h, const float* mel_dev, int B, int T, int16_t*
 int hfg_forward_host_pcm16(hfg_handle h, const float* mel_host, int B, int T, int16_t* pcm_host);
 
 /* Options: "micro_batch" = utterances per forward of hfg_forward_host (0 = auto, the default: hfg_auto_micro_batch);
- * "stage_timing" 0/1; "cuda_graphs" 0/1 (default 1: launch-bound micro-batches of hfg_forward_host, <= 8192 frames,
+ * "stage_timing" 0/1; "fuse_resblocks" 0/1 (default 1: every
+ * ResBlock1 iteration of a stage with C <= 64 is one launch, needs a new hfg_finalize_weights); "cuda_graphs" 0/1 (default 1: launch-bound micro-batches of hfg_forward_host, <= 8192 frames,
  * are replayed from a CUDA graph captured on their second use); "concurrent_resblocks" = largest B*T in frames
  * (default 2048, 0 = never) for which the resblocks of a stage -- independent up to their last conv, reference
  * HiFiGAN_TF/model.py:161-166 -- run as concurrent chains on internal streams forked from and joined to the caller's
@@ -153,6 +154,18 @@ int hfg_op_tapped_conv(int act, int engine, const void* x_dev, int B, int x_rows
                        int out_stride, int out_off, float in_slope, const void* res_dev, float res_inv,
                        const void* res2_dev, float out_scale, float out_slope, float* acc_dev,
                        int mrf_mode, float mrf_div, void* out_dev, void* stream);
+
+/* Operator-level entry: ONE fused ResBlock1 iteration, xt = convs1[m](lrelu(x)); xt = convs2[m](lrelu(xt)); x = xt + x
+ * (reference model.py:71-80), as a single launch whose intermediate stays in shared memory; synchronous, for parity
+ * tests.  Kernel view of 64 channels per row (a [L, C] tensor with C < 64 is passed as [L/f, 64], f = 64/C, with
+ * block-Toeplitz weights); act: 1 fp16, 2 bf16; w1/w2 fp32 [ntaps][64][64], b1/b2 [64]; x is stored activated:
+ *   xt[q]  = lrelu(b1 + sum_j x[q + off1[j]] . W1_j, mid_slope), taken as 0 outside [0, rows)
+ *   v[q]   = b2 + sum_j xt[q + off2[j]] . W2_j + unact(x[q]) + res2[q]      unact(y) = y >= 0 ? y : y * res_inv
+ *   out[q] = lrelu(v * out_scale, out_slope)            res2 (running MRF sum, model.py:161-167) may be NULL */
+int hfg_op_resblock_fused(int act, const void* x_dev, int B, int rows, const float* w1_host, const float* b1_host, int ntaps1,
+                          const int* off1, const float* w2_host, const float* b2_host, int ntaps2, const int* off2,
+                          float mid_slope, float res_inv, const void* res2_dev, float out_scale, float out_slope,
+                          void* out_dev, void* stream);
 
 /* Pinned host memory helpers for callers without a CUDA runtime binding of their own. */
 int hfg_host_alloc(void** out, size_t bytes);

@@ -67,6 +67,9 @@ SIGNATURES = {
     "hfg_op_tapped_conv": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                      C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_float,
                                      C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_int, C.c_float, C.c_void_p, C.c_void_p]),
+    "hfg_op_resblock_fused": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int),
+                                        C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int), C.c_float, C.c_float, C.c_void_p,
+                                        C.c_float, C.c_float, C.c_void_p, C.c_void_p]),
     "hfg_host_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),
     "hfg_host_free": (C.c_int, [C.c_void_p]),
     "hfg_last_error": (C.c_char_p, [C.c_void_p]),

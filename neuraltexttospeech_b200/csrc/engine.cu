@@ -16,6 +16,7 @@
 #include <cstring>
 #include <map>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/hifigan_b200.h"
@@ -52,6 +53,14 @@ struct Layer {
   void* d_wpk = nullptr;
   bool use_tc = false;      // persistent tcgen05 kernel (conv_tc.cu): one launch per layer, phases = variants
   size_t wpk_bytes = 0;     // size of d_wpk (multiple of 256)
+  // convs1[m] of a ResBlock1 whose iteration (convs1[m] -> convs2[m] -> + x) runs as ONE launch of resblock_tc.cu
+  struct Fused {
+    bool on = false;
+    int fold = 1, cg = 2, ntaps1 = 0, ntaps2 = 0;
+    int off1[kMaxTaps], off2[kMaxTaps];
+    void* d_w1 = nullptr; void* d_w2 = nullptr;
+    float* d_b1 = nullptr; float* d_b2 = nullptr;
+  } fused;
 };
 
 thread_local std::string g_create_error;
@@ -98,6 +107,7 @@ struct hfg_ctx {
   void* d_audio = nullptr; size_t d_audio_bytes = 0;   // fp32 audio or 16-bit PCM
   bool force_ffma = false;
   bool auto_fold = true;       // per-layer fold factor from fold_cost (option "auto_fold")
+  bool fuse_resblocks = true;  // ResBlock1 iterations of the narrow stages (C <= 64) as one launch each (option "fuse_resblocks")
   bool need_acc = true, need_sum = false;
   // launch-bound forwards (B*T <= chain_frames): the resblocks of a stage are independent chains up to their last conv
   // (reference model.py:161-166 sums rb_j(x) over j), so chain j >= 1 runs on its own stream with its own scratch
@@ -310,6 +320,11 @@ void free_layer_device(Layer& L) {
   if (L.d_w32) cudaFree(L.d_w32);
   if (L.d_bias) cudaFree(L.d_bias);
   if (L.d_wpk) cudaFree(L.d_wpk);
+  if (L.fused.d_w1) cudaFree(L.fused.d_w1);
+  if (L.fused.d_w2) cudaFree(L.fused.d_w2);
+  if (L.fused.d_b1) cudaFree(L.fused.d_b1);
+  if (L.fused.d_b2) cudaFree(L.fused.d_b2);
+  L.fused = Layer::Fused();
   L.d_w32 = nullptr; L.d_bias = nullptr; L.d_wpk = nullptr;
 }
 
@@ -460,6 +475,20 @@ struct Runner {
     }
   }
 
+  // one ResBlock1 iteration (convs1[m] -> convs2[m] -> + x, reference model.py:71-80) as one launch of resblock_tc.cu
+  void resblock_fused(const Layer& c1, const void* x, int x_rows, void* out, const void* res2, float mid_slope,
+                      float out_scale, float out_slope) {
+    if (status != cudaSuccess) return;
+    const Layer::Fused& F = c1.fused;
+    RbArgs a{};
+    a.x = x; a.out = out; a.res2 = res2; a.bias1 = F.d_b1; a.bias2 = F.d_b2; a.w1 = F.d_w1; a.w2 = F.d_w2; a.cg = F.cg;
+    a.B = B; a.n_q = x_rows / F.fold; a.ntaps1 = F.ntaps1; a.ntaps2 = F.ntaps2;
+    memcpy(a.off1, F.off1, sizeof(int) * F.ntaps1); memcpy(a.off2, F.off2, sizeof(int) * F.ntaps2);
+    a.mid_slope = mid_slope; a.res_inv = 1.0f / slope_of_res; a.out_scale = out_scale; a.out_slope = out_slope;
+    status = launch_resblock_tc(a, h->act, s);
+    h->launches++;
+  }
+
   float slope_of_res = 1.0f;   // slope the residual tensor of the current stage was stored with (1 = raw)
 };
 
@@ -524,10 +553,20 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
         if (c.resblock == 1) {                                   // ResBlock1.call model.py:71-80
           const Layer& c1 = rb(n, m, 0);
           const Layer& c2 = rb(n, m, 1);
+          if (c1.fused.on) {                                     // the whole iteration in one launch; xt stays on chip
+            if (last && chains && j > 0) cu(cudaStreamWaitEvent(r.s, h->ev_sum[j - 1], 0));
+            const float os = next_tc ? next_slope : 1.0f;
+            if (!last) r.resblock_fused(c1, rcur, L, rnext, nullptr, kSlope, 1.0f, kSlope);
+            else if (nk == 1) r.resblock_fused(c1, rcur, L, rnext, nullptr, kSlope, 1.0f, os);
+            else if (j == 0) r.resblock_fused(c1, rcur, L, w.S, nullptr, kSlope, 1.0f, 1.0f);           // xs = rb_0(x)   (model.py:163-164)
+            else if (j < nk - 1) r.resblock_fused(c1, rcur, L, w.S, w.S, kSlope, 1.0f, 1.0f);           // xs += rb_j(x)  (model.py:165-166)
+            else r.resblock_fused(c1, rcur, L, rnext, w.S, kSlope, 1.0f / (float)nk, os);               // x = xs / num_kernels (model.py:167)
+          } else {
           r.conv(c1, rcur, L, Tj, kSlope, nullptr, kSlope, rb_tc);
           if (last && chains && j > 0) cu(cudaStreamWaitEvent(r.s, h->ev_sum[j - 1], 0));   // the running sum of chain j-1
           if (last) r.conv_mrf(c2, Tj, L, rnext, w.S, kSlope, rcur, w.ACC, j, nk, next_slope, next_tc);
           else r.conv(c2, Tj, L, rnext, kSlope, rcur, kSlope, rb_tc);
+          }
         } else {                                                 // ResBlock2.call model.py:106-112
           const Layer& c1 = rb(n, m, 0);
           if (last && chains && j > 0) cu(cudaStreamWaitEvent(r.s, h->ev_sum[j - 1], 0));
@@ -593,6 +632,7 @@ int hfg_create(const hfg_config* cfg, int device, hfg_handle* out) {
   h->cfg = *cfg; h->device = device;
   if (const char* e = getenv("HFG_AUTO_FOLD")) h->auto_fold = atoi(e) != 0;   // A/B knob
   if (const char* e = getenv("HFG_CHAIN_FRAMES")) h->chain_frames = atoll(e);  // A/B knob (option "concurrent_resblocks")
+  if (const char* e = getenv("HFG_FUSE")) h->fuse_resblocks = atoi(e) != 0;   // A/B knob (option "fuse_resblocks")
   build_layers(h);
   *out = h;
   return HFG_OK;
@@ -752,6 +792,54 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
   }
   if (!any) break;
   }
+  // Fused ResBlock1 iterations (resblock_tc.cu): both convs of an iteration on the tcgen05 path, C*f = 64 with
+  // f = 64/C dividing the stage's rows per frame, tap lists / spans that fit the fused kernel's shared-memory plan.
+  if (c.resblock == 1 && h->fuse_resblocks && h->act != ACT_F32 && !h->force_ffma) {
+    for (int n = 0; n < c.num_upsamples * c.num_kernels; ++n)
+      for (int m = 0; m < c.num_dilations[n % c.num_kernels]; ++m) {
+        const int i1 = h->i_rb[((size_t)n * HFG_MAX_DILATIONS + m) * 2], i2 = h->i_rb[((size_t)n * HFG_MAX_DILATIONS + m) * 2 + 1];
+        if (i1 < 0 || i2 < 0) continue;
+        Layer& A = h->layers[i1]; Layer& Bc = h->layers[i2];
+        if (!A.use_tc || !Bc.use_tc || A.cin != A.cout || A.cin > 64 || 64 % A.cin) continue;
+        const int f = 64 / A.cin;
+        if (A.in_rate % f) continue;
+        bool ok1, ok2;
+        const int pl1 = conv_pad_left(A.k, A.dil, c.compat, &ok1), pl2 = conv_pad_left(Bc.k, Bc.dil, c.compat, &ok2);
+        const KView V1 = build_view(A, fold_weight_norm(A), pl1, f, f, false), V2 = build_view(Bc, fold_weight_norm(Bc), pl2, f, f, false);
+        if (V1.off.size() != 1 || V2.off.size() != 1 || V1.max_taps() > kMaxTaps || V2.max_taps() > kMaxTaps) continue;
+        RbArgs ra{};
+        ra.ntaps1 = (int)V1.off[0].size(); ra.ntaps2 = (int)V2.off[0].size();
+        for (int t = 0; t < ra.ntaps1; ++t) ra.off1[t] = V1.off[0][t];
+        for (int t = 0; t < ra.ntaps2; ++t) ra.off2[t] = V2.off[0][t];
+        int cg = 2;
+        if (!rb_supported(ra, &cg)) continue;
+        Layer::Fused& F = A.fused;
+        F.fold = f; F.cg = cg; F.ntaps1 = ra.ntaps1; F.ntaps2 = ra.ntaps2;
+        memcpy(F.off1, ra.off1, sizeof(int) * ra.ntaps1); memcpy(F.off2, ra.off2, sizeof(int) * ra.ntaps2);
+        auto upload_w = [&](const KView& V, void** dptr) -> int {
+          const int nt = (int)V.off[0].size();
+          std::vector<float> w32((size_t)nt * 64 * 64);
+          for (int t = 0; t < nt; ++t) memcpy(&w32[(size_t)t * 4096], V.w[0][t].data(), sizeof(float) * 4096);
+          std::vector<char> pk(rb_packed_weight_bytes(nt));
+          rb_pack_weights(w32.data(), nt, cg, h->act, pk.data());
+          CUDA_TRY(h, cudaMalloc(dptr, pk.size()));
+          CUDA_TRY(h, cudaMemcpy(*dptr, pk.data(), pk.size(), cudaMemcpyHostToDevice));
+          return HFG_OK;
+        };
+        auto upload_b = [&](const Layer& L, float** dptr) -> int {
+          std::vector<float> bias(64);
+          for (int sidx = 0; sidx < f; ++sidx) memcpy(&bias[(size_t)sidx * L.cout], L.b.data(), sizeof(float) * L.cout);
+          CUDA_TRY(h, cudaMalloc((void**)dptr, 64 * sizeof(float)));
+          CUDA_TRY(h, cudaMemcpy(*dptr, bias.data(), 64 * sizeof(float), cudaMemcpyHostToDevice));
+          return HFG_OK;
+        };
+        int rc = upload_w(V1, &F.d_w1); if (rc) return rc;
+        rc = upload_w(V2, &F.d_w2); if (rc) return rc;
+        rc = upload_b(A, &F.d_b1); if (rc) return rc;
+        rc = upload_b(Bc, &F.d_b2); if (rc) return rc;
+        F.on = true;
+      }
+  }
   h->need_acc = false; h->need_sum = false;
   for (const Layer& L : h->layers)
     if (!L.transposed && L.name != "conv_pre" && L.name != "conv_post") { if (L.use_tc) h->need_sum = true; else h->need_acc = true; }
@@ -817,6 +905,25 @@ static bool host_is_pinned(const void* p) {
   cudaPointerAttributes at{};
   if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
   return at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged;
+}
+
+// host memcpy between pageable and pinned memory, split over a few threads (one thread moves ~6-10 GB/s, far below
+// the host link; the first upload and the last download of a call are exposed)
+static void staged_memcpy(char* dst, const char* src, size_t bytes) {
+  const size_t kChunk = size_t(2) << 20;
+  unsigned nt = std::thread::hardware_concurrency();
+  nt = nt == 0 ? 1 : (nt > 8 ? 8 : nt);
+  if (bytes < 2 * kChunk || nt == 1) { memcpy(dst, src, bytes); return; }
+  if ((size_t)nt > bytes / kChunk) nt = (unsigned)(bytes / kChunk);
+  const size_t per = (bytes / nt + 4095) & ~size_t(4095);
+  std::vector<std::thread> th;
+  for (unsigned t = 1; t < nt; ++t) {
+    const size_t off = (size_t)t * per;
+    if (off >= bytes) break;
+    th.emplace_back([=]() { memcpy(dst + off, src + off, std::min(per, bytes - off)); });
+  }
+  memcpy(dst, src, std::min(per, bytes));
+  for (auto& x : th) x.join();
 }
 
 static int grow_pinned(hfg_ctx* h, char** buf, size_t* have, size_t need) {
@@ -942,12 +1049,12 @@ static int forward_host(hfg_handle h, const float* mel_host, int B, int T, void*
     if (out_direct) return HFG_OK;
     CUDA_TRY(h, cudaEventSynchronize(h->copy_events[3 * i + 2]));
     const size_t off = (size_t)b0 * aud_elems * sample_bytes;
-    memcpy((char*)out_host + off, h->pin_out + off, (size_t)parts[i] * aud_elems * sample_bytes);
+    staged_memcpy((char*)out_host + off, h->pin_out + off, (size_t)parts[i] * aud_elems * sample_bytes);
     return HFG_OK;
   };
   auto upload = [&](int i, int b0) -> int {
     const size_t off = (size_t)b0 * mel_elems * 4, bytes = (size_t)parts[i] * mel_elems * 4;
-    if (!in_direct) memcpy(h->pin_in + off, (const char*)mel_host + off, bytes);
+    if (!in_direct) staged_memcpy(h->pin_in + off, (const char*)mel_host + off, bytes);
     CUDA_TRY(h, cudaMemcpyAsync((char*)h->d_mel + off, src_base + off, bytes, cudaMemcpyHostToDevice, h->h2d_stream));
     CUDA_TRY(h, cudaEventRecord(h->copy_events[3 * i], h->h2d_stream));
     return HFG_OK;
@@ -996,6 +1103,7 @@ int hfg_set_option(hfg_handle h, const char* key, long long value) {
   if (k == "force_ffma") { h->force_ffma = value != 0; h->finalized = false; return HFG_OK; }
   if (k == "cuda_graphs") { h->use_graphs = value != 0; if (!h->use_graphs) clear_graphs(h); return HFG_OK; }
   if (k == "auto_fold") { h->auto_fold = value != 0; h->finalized = false; return HFG_OK; }
+  if (k == "fuse_resblocks") { h->fuse_resblocks = value != 0; h->finalized = false; return HFG_OK; }
   if (k == "concurrent_resblocks") {      // largest B*T (frames) whose resblocks run as concurrent chains; 0 = never
     if (value < 0) return fail(h, HFG_ERR_INVALID, "concurrent_resblocks must be >= 0 (frames)");
     h->chain_frames = value; clear_graphs(h); return HFG_OK;
@@ -1120,6 +1228,42 @@ int hfg_op_tapped_conv(int act, int engine, const void* x_dev, int B, int x_rows
   if (e == cudaSuccess) e = cudaStreamSynchronize(s);
   cudaFree(d_bias); cudaFree(d_w);
   if (e != cudaSuccess) return fail(nullptr, HFG_ERR_CUDA, "tapped conv failed: %s", cudaGetErrorString(e));
+  return HFG_OK;
+}
+
+// One fused ResBlock1 iteration (resblock_tc.cu) on caller-provided device buffers; packs and uploads the weights on
+// every call -- operator-level parity tests only.
+int hfg_op_resblock_fused(int act, const void* x_dev, int B, int rows, const float* w1_host, const float* b1_host, int ntaps1,
+                          const int* off1, const float* w2_host, const float* b2_host, int ntaps2, const int* off2,
+                          float mid_slope, float res_inv, const void* res2_dev, float out_scale, float out_slope,
+                          void* out_dev, void* stream) {
+  if ((act != ACT_F16 && act != ACT_BF16) || !x_dev || !out_dev || !w1_host || !w2_host || !b1_host || !b2_host || !off1 || !off2 ||
+      ntaps1 < 1 || ntaps2 < 1 || ntaps1 > kMaxTaps || ntaps2 > kMaxTaps)
+    return fail(nullptr, HFG_ERR_INVALID, "hfg_op_resblock_fused: bad argument");
+  RbArgs a{};
+  a.x = x_dev; a.out = out_dev; a.res2 = res2_dev; a.B = B; a.n_q = rows; a.ntaps1 = ntaps1; a.ntaps2 = ntaps2;
+  memcpy(a.off1, off1, sizeof(int) * ntaps1); memcpy(a.off2, off2, sizeof(int) * ntaps2);
+  a.mid_slope = mid_slope; a.res_inv = res_inv; a.out_scale = out_scale; a.out_slope = out_slope;
+  int cg = 2;
+  if (!rb_supported(a, &cg)) return fail(nullptr, HFG_ERR_UNSUPPORTED, "fused resblock kernel does not cover these taps");
+  a.cg = cg;
+  cudaStream_t s = (cudaStream_t)stream;
+  void* d_w[2] = {nullptr, nullptr}; float* d_b[2] = {nullptr, nullptr};
+  const float* wh[2] = {w1_host, w2_host}; const float* bh[2] = {b1_host, b2_host}; const int nt[2] = {ntaps1, ntaps2};
+  cudaError_t e = cudaSuccess;
+  for (int c = 0; c < 2 && e == cudaSuccess; ++c) {
+    std::vector<char> pk(rb_packed_weight_bytes(nt[c]));
+    rb_pack_weights(wh[c], nt[c], cg, (ActType)act, pk.data());
+    e = cudaMalloc(&d_w[c], pk.size());
+    if (e == cudaSuccess) e = cudaMemcpy(d_w[c], pk.data(), pk.size(), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&d_b[c], 64 * sizeof(float));
+    if (e == cudaSuccess) e = cudaMemcpy(d_b[c], bh[c], 64 * sizeof(float), cudaMemcpyHostToDevice);
+  }
+  a.w1 = d_w[0]; a.w2 = d_w[1]; a.bias1 = d_b[0]; a.bias2 = d_b[1];
+  if (e == cudaSuccess) e = launch_resblock_tc(a, (ActType)act, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  for (int c = 0; c < 2; ++c) { cudaFree(d_w[c]); cudaFree(d_b[c]); }
+  if (e != cudaSuccess) return fail(nullptr, HFG_ERR_CUDA, "fused resblock failed: %s", cudaGetErrorString(e));
   return HFG_OK;
 }
 

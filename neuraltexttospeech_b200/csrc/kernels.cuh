@@ -121,4 +121,27 @@ void tc_pack_weights(const float* w, int ntaps, int c_in, int c_out, int span, A
 cudaError_t launch_conv_tc(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out);
 void tc_set_trace(long long* dev);   // debug builds (-DHFG_TC_TRACE): device buffer of [6][64][8] clock stamps, see conv_tc.cu
 
+// ---------------------------------------------------------------- fused ResBlock1 iteration (resblock_tc.cu)
+// One launch = conv1 (dilated) -> lrelu -> conv2 -> + x (reference model.py:71-80), 64 kernel-view channels per row
+// (C*fold = 64), both convs given as tap lists over kernel-view rows with 64x64 (block-Toeplitz when folded) weights:
+//   xt[q]  = lrelu(b1 + sum_j x[q + off1[j]] . W1_j, mid_slope), 0 outside [0, n_q)      x stored activated
+//   v[q]   = b2 + sum_j xt[q + off2[j]] . W2_j + unact(x[q]) + res2[q]                    unact(y) = y >= 0 ? y : y * res_inv
+//   out[q] = lrelu(v * out_scale, out_slope)
+struct RbArgs {
+  const void* x;        // [B, n_q, 64] 16-bit, stored activated (slope 1/res_inv)
+  void* out;            // [B, n_q, 64]
+  const void* res2;     // running raw MRF sum, indexed like out, or nullptr
+  const float* bias1; const float* bias2;   // [64] each (kernel view: the layer's bias replicated per fold slot)
+  const void* w1; const void* w2;           // rb_pack_weights images (256-byte aligned)
+  int cg;               // CTA grouping the weights were packed for (rb_supported)
+  int B, n_q;
+  int ntaps1, ntaps2;
+  int off1[kMaxTaps], off2[kMaxTaps];
+  float mid_slope, res_inv, out_scale, out_slope;
+};
+bool rb_supported(const RbArgs& a, int* cg_out);          // needs ntaps / offsets only
+size_t rb_packed_weight_bytes(int ntaps);
+void rb_pack_weights(const float* w, int ntaps, int cg, ActType act, void* dst_host);   // w: fp32 [ntaps][64][64]
+cudaError_t launch_resblock_tc(const RbArgs& a, ActType act, cudaStream_t s);
+
 }  // namespace hfg

@@ -208,10 +208,12 @@ def test_host_path_cuda_graph_replay_is_bit_identical():
     mel = synthetic_mel(2, 16, h.num_mels)
     g.set_option("cuda_graphs", 0)
     plain = g(mel).copy()
+    n_plain = g.last_launch_count()
+    assert n_plain == 61              # cast_pad + 78 convs, minus one launch per fused ResBlock1 iteration of stages 2-3 (18)
     g.set_option("cuda_graphs", 1)
     outs = [g(mel).copy() for _ in range(4)]                    # plain, capture, replay, replay
     assert all((o == plain).all() for o in outs)
-    assert g.last_launch_count() == 79
+    assert g.last_launch_count() == n_plain
     mel2 = synthetic_mel(2, 16, h.num_mels, seed=7)             # same shape, new data: the graph reads the same device buffer
     g.set_option("cuda_graphs", 0)
     plain2 = g(mel2).copy()
@@ -305,8 +307,11 @@ def test_stage_with_a_conv_outside_the_tile_table_is_demoted_as_a_whole():
     ref = O.generator_forward(h, w, mel, "torch32")
     g = Generator(h, precision="fp16").load_weights(w)
     eng = g.layer_engines()
-    rb = {k: e for k, e in eng.items() if k.startswith("resblocks")}
-    assert set(rb.values()) == {"ffma"}, rb                       # span 102 in every stage -> every stage demoted
+    nk = len(h.resblock_kernel_sizes)
+    per_stage = [{e for k, e in eng.items() if k.startswith("resblocks.") and int(k.split(".")[1]) // nk == i}
+                 for i in range(len(h.upsample_rates))]
+    assert all(len(s_) == 1 for s_ in per_stage), per_stage      # every stage is uniform ...
+    assert per_stage[0] == {"ffma"}, per_stage                    # ... and the 128-channel stage (span 102, no fold) is demoted as a whole
     assert eng["ups.0"] == "tc" and eng["conv_pre"] == "tc"
     out = g(mel)
     g.close()
@@ -353,12 +358,36 @@ def test_full_length_utterances_match_oracle(v, B, gens):
     assert np.abs(out - ref).max() <= TC_TOL and snr_db(ref, out) >= TC_SNR
 
 
+def test_fused_resblock_iterations_cover_the_narrow_stages_and_keep_parity():
+    """Every ResBlock1 iteration of a stage with C <= 64 is ONE launch (resblock_tc.cu: conv1 -> lrelu -> conv2 -> + x,
+    the intermediate stays in shared memory).  Launch counts say which path ran; results with the fusion on and off
+    must both meet the tolerance (they differ in rounding only: the fused kernel adds the residual in fp32 before
+    conv2's accumulation instead of after it)."""
+    for v, fused_iters in (("1", 18), ("2", 36)):
+        h = HParams.builtin(v)
+        w = synthetic_weights(h, "B")
+        mel = synthetic_mel(2, 50, h.num_mels, seed=21)
+        ref = O.generator_forward(h, w, mel, "torch32")
+        g = Generator(h, precision="fp16").load_weights(w)
+        on = g(mel)
+        n_on = g.last_launch_count()
+        g.set_option("fuse_resblocks", 0)
+        g.load_weights(w)
+        off = g(mel)
+        n_off = g.last_launch_count()
+        g.close()
+        assert n_off == 79 and n_off - n_on == fused_iters, (n_on, n_off)
+        for out in (on, off):
+            assert np.abs(out - ref).max() <= TC_TOL and snr_db(ref, out) >= TC_SNR
+
+
 def test_launch_path_knobs_off_in_a_subprocess():
-    """The half-height tiles, programmatic dependent launch and per-layer folds are chosen per process (environment
-    knobs read once): re-run the golden / seeded parity tests with all three off so the other code paths stay covered."""
+    """The half-height tiles, programmatic dependent launch, per-layer folds and the fused ResBlock launches are chosen per
+    process (environment knobs read once): re-run the golden / seeded parity tests with all of them off so the other code
+    paths stay covered."""
     import subprocess
     import sys
-    env = dict(os.environ, HFG_TC_SMALL="0", HFG_PDL="0", HFG_AUTO_FOLD="0")
+    env = dict(os.environ, HFG_TC_SMALL="0", HFG_PDL="0", HFG_AUTO_FOLD="0", HFG_FUSE="0")
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_generator_gpu.py"), "-q", "-x", "-m", "gpu",
                         "-k", "golden or seeded or batch_independence"], env=env, cwd=root, capture_output=True, text=True, timeout=600)

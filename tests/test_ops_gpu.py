@@ -135,3 +135,73 @@ def test_ffma_mrf_modes():
     xq = x.cpu().numpy()
     tot = sum(ref_tapped_conv(xq, w, bias, taps) for w in ws) / 3
     assert np.abs(fin.cpu().numpy() - lrelu(tot, 0.3)).max() <= 2e-5
+
+
+# ---------------------------------------------------------------- fused ResBlock1 iteration (resblock_tc.cu)
+def ref_resblock_fused(xq, w1, b1, off1, w2, b2, off2, mid_slope, res_inv, res2, out_scale, out_slope, mid_dtype):
+    """numpy fp64 restatement of kernels.cuh RbArgs semantics on the SAME 16-bit inputs; the intermediate is rounded to
+    the storage type like the kernel's shared-memory tile."""
+    import torch
+    xt = ref_tapped_conv(xq, w1, b1, off1)                                        # conv1 on the stored (activated) x
+    xt = np.where(xt >= 0, xt, xt * mid_slope)
+    xt = torch.from_numpy(xt.astype(np.float32)).to(mid_dtype).float().numpy()    # 16-bit xt tile
+    v = ref_tapped_conv(xt, w2, b2, off2)
+    v += np.where(xq >= 0, xq, xq * np.float32(res_inv))                          # skip connection on the un-activated x
+    if res2 is not None:
+        v += res2
+    v *= out_scale
+    return np.where(v >= 0, v, v * out_slope)
+
+
+def folded_taps(k, d, pad_left, f):
+    return sorted({(s + j * d - pad_left) // f for s in range(f) for j in range(k)})
+
+
+RB_CASES = [  # (k, dilation, fold, B, rows): the ResBlock1 iterations of V1 / V2 stages with C*fold = 64
+    (3, 1, 1, 2, 700),      # causal conv1 AND causal conv2 (reference quirk Q1): taps [-2,-1,0]
+    (3, 3, 1, 1, 1500),
+    (7, 5, 1, 2, 900),
+    (11, 5, 1, 1, 2100),    # k = 11: resident weights leave room for one xt tile only / one block per tile
+    (11, 1, 2, 2, 640),     # C = 32 folded by 2
+    (11, 5, 2, 1, 1111),    # 17 + 7 kernel-view taps
+    (7, 3, 8, 3, 130),      # C = 8 folded by 8 (V2 stage 3); utterance shorter than a tile
+    (3, 5, 4, 2, 257),
+]
+
+
+@pytest.mark.parametrize("k,d,f,B,rows", RB_CASES)
+@pytest.mark.parametrize("dtype", ["float16", "bfloat16"])
+def test_resblock_fused_matches_two_convs(k, d, f, B, rows, dtype):
+    import torch
+    from neuraltexttospeech_b200.ops import resblock_fused
+    from neuraltexttospeech_b200.utils import get_padding
+    rng = np.random.default_rng(k * 100 + d * 10 + f)
+    tdt = getattr(torch, dtype)
+
+    def pad_left(kk, dd):                       # reference HiFiGAN_TF/utils.py:29-37 -> keras padding mode
+        return dd * (kk - 1) if get_padding(kk, dd) == "causal" else dd * (kk - 1) // 2
+
+    off1, off2 = folded_taps(k, d, pad_left(k, d), f), folded_taps(k, 1, pad_left(k, 1), f)
+    x = rng.standard_normal((B, rows, 64)).astype(np.float32)
+    xt = torch.from_numpy(lrelu(x, 0.1)).cuda().to(tdt)
+    xq = xt.float().cpu().numpy()
+    w1 = (rng.standard_normal((len(off1), 64, 64)) / np.sqrt(64 * len(off1))).astype(np.float32)
+    w2 = (rng.standard_normal((len(off2), 64, 64)) / np.sqrt(64 * len(off2))).astype(np.float32)
+    b1 = rng.uniform(-0.1, 0.1, 64).astype(np.float32); b2 = rng.uniform(-0.1, 0.1, 64).astype(np.float32)
+    w1q = torch.from_numpy(w1).to(tdt).float().numpy(); w2q = torch.from_numpy(w2).to(tdt).float().numpy()
+    tol = {"float16": 6e-3, "bfloat16": 5e-2}[dtype]
+    # plain iteration: output stored activated with 0.1
+    ref = ref_resblock_fused(xq, w1q, b1, off1, w2q, b2, off2, 0.1, 10.0, None, 1.0, 0.1, tdt)
+    out = resblock_fused(xt, w1, b1, off1, w2, b2, off2).float().cpu().numpy()
+    err = np.abs(out - ref)
+    assert err.max() <= tol, (err.max(), np.unravel_index(err.argmax(), err.shape))
+    # last iteration of the last resblock: + running MRF sum, / num_kernels, stored for conv_post (slope 0.3)
+    s2 = torch.from_numpy(rng.standard_normal((B, rows, 64)).astype(np.float32)).cuda().to(tdt)
+    ref = ref_resblock_fused(xq, w1q, b1, off1, w2q, b2, off2, 0.1, 10.0, s2.float().cpu().numpy(), 1.0 / 3, 0.3, tdt)
+    out = resblock_fused(xt, w1, b1, off1, w2, b2, off2, res2=s2, out_scale=1.0 / 3, out_slope=0.3).float().cpu().numpy()
+    assert np.abs(out - ref).max() <= tol
+    # in place on the sum buffer (xs += rb_j(x)), raw output
+    s2b = s2.clone()
+    resblock_fused(xt, w1, b1, off1, w2, b2, off2, res2=s2b, out_slope=1.0, out=s2b)
+    ref = ref_resblock_fused(xq, w1q, b1, off1, w2q, b2, off2, 0.1, 10.0, s2.float().cpu().numpy(), 1.0, 1.0, tdt)
+    assert np.abs(s2b.float().cpu().numpy() - ref).max() <= 2 * tol

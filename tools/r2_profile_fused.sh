@@ -1,0 +1,13 @@
+#!/bin/bash
+# tests, then launch list + ncu --set full of the 18 fused ResBlock launches of one V1 forward (16 utterances)
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/pytest_gpu.log
+python tools/profile_forward.py > gpurun_out/plain_profile.log 2>&1 && \
+ncu --metrics gpu__time_duration.sum --clock-control none -s 61 -c 61 --csv --log-file gpurun_out/launches_fwd_b16.csv python tools/profile_forward.py > gpurun_out/ncu_launches.log 2>&1
+echo "launch list rc=$?"
+python tools/profile_forward.py > gpurun_out/plain_profile2.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:resblock_tc_kernel -s 18 -c 18 -f -o gpurun_out/prof_fused python tools/profile_forward.py > gpurun_out/ncu_fused.log 2>&1
+echo "ncu fused rc=$?"
+ncu -i gpurun_out/prof_fused.ncu-rep --page raw --csv > gpurun_out/prof_fused_raw.csv 2>/dev/null
+ncu -i gpurun_out/prof_fused.ncu-rep --page source --csv > gpurun_out/prof_fused_source.csv 2>/dev/null
+ls -la gpurun_out
