@@ -282,6 +282,7 @@ def main():
     dev_ms = max_over_ranks(e0.elapsed_time(e1)) / args.steps
     clocks = clk.summary()
     stage_ms = gen.stage_times_ms()          # per forward of `mb` utterances, averaged over the timed forwards
+    stage_launches = gen.stage_launches()    # kernels per stage as launched (a fused ResBlock iteration is ONE launch)
     gen.set_option("stage_timing", 0)
 
     # ---------------- end-to-end through Generator.call on pinned host buffers ("e2e")
@@ -355,18 +356,19 @@ def main():
         p_tensor, bw = pk["tflops_sustained"] * 1e12, pk["hbm_gbs"] * 1e9
         # per-stage roofline: t_roof = max(F / P_tensor, B / BW_hbm) per forward of `mb` utterances
         stages, t_roof_sum = [], 0.0
-        for w, ms in zip(per_stage_work(h, act_b), stage_ms):
+        for w, ms, nl in zip(per_stage_work(h, act_b), stage_ms, stage_launches):
+            w["launches"] = nl
             f_st, b_st = 2.0 * w["macs"] * T * mean_fwd_batch, float(w["bytes"]) * T * mean_fwd_batch
             t_t, t_h = f_st / p_tensor * 1e3, b_st / bw * 1e3
             t_roof = max(t_t, t_h) if tensor_bound else t_h
             t_roof_sum += t_roof
-            stages.append({"label": w["label"], "ms": round(ms, 4), "launches": w["launches"], "bound": "tensor" if (tensor_bound and t_t >= t_h) else "hbm",
+            stages.append({"label": w["label"], "ms": round(ms, 4), "launches": nl, "bound": "tensor" if (tensor_bound and t_t >= t_h) else "hbm",
                            "roof_ms": round(t_roof, 4), "frac": round(t_roof / ms, 4) if ms > 0 else None,
                            "tflops": round(f_st / (ms * 1e-3) / 1e12, 1) if ms > 0 else None,
                            "gbs": round(b_st / (ms * 1e-3) / 1e9, 1) if ms > 0 else None})
         # dominant kernel: the stage with the largest measured time; all of its launches are conv_tc_kernel instances
         dom = max(range(len(stages)), key=lambda i: stages[i]["ms"])
-        dw, dst = per_stage_work(h, act_b)[dom], stages[dom]
+        dw, dst = dict(per_stage_work(h, act_b)[dom], launches=stage_launches[dom]), stages[dom]
         dom_flops_launch = 2.0 * dw["macs"] * T * mean_fwd_batch / dw["launches"]
         dom_ms_launch = dst["ms"] / dw["launches"]
         dom_bytes_launch = float(dw["bytes"]) * T * mean_fwd_batch / dw["launches"]
@@ -387,7 +389,9 @@ def main():
             "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps), "clocks": clocks,
             "roofline": {"bound": "tensor" if dom_tensor else "hbm", "achieved": achieved, "peak": dom_peak,
                          "unit": "TFLOP/s" if dom_tensor else "GB/s", "frac": achieved / dom_peak, "traffic": traffic,
-                         "kernel": f"conv_tc_kernel (tcgen05 implicit GEMM), {dst['label']}: {dw['launches']} launches per forward of {mb} utterances",
+                         "kernel": (f"resblock_tc_kernel (fused ResBlock1 iterations, tcgen05) + conv_tc_kernel (ups), {dst['label']}: "
+                                    if stage_launches[dom] < per_stage_work(h, act_b)[dom]["launches"] else
+                                    f"conv_tc_kernel (tcgen05 implicit GEMM), {dst['label']}: ") + f"{dw['launches']} launches per forward of {mb} utterances",
                          "flops_per_launch": dom_flops_launch, "bytes_per_launch": dom_bytes_launch, "ms_per_launch": dom_ms_launch,
                          "timing": "CUDA events on the launch stream around the stage, inside the timed region, averaged over its forwards",
                          "peak_source": pk["source"] + (" bf16 sustained (fp16 runs at the same tcgen05 rate; kernel timed inside a long step)" if dom_tensor

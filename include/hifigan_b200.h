@@ -89,7 +89,10 @@ int hfg_workspace_bytes(hfg_handle h, int B, int T, size_t* out);
  *   mel_dev   : device, fp32, [B, T, num_mels] C-contiguous (channels-last, like the reference)
  *   audio_dev : device, fp32, [B, T*prod(rates), 1]
  *   workspace : device, >= hfg_workspace_bytes, 256-byte aligned; caller-owned
- *   stream    : cudaStream_t (NULL = legacy default stream) */
+ *   stream    : cudaStream_t (NULL = legacy default stream)
+ * Asynchronous on `stream`.  Launch-bound forwards (B*T <= 8192 frames, option "cuda_graphs" on, `stream` not being
+ * captured by the caller) are replayed from a CUDA graph captured on the second call with the same
+ * (mel_dev, audio_dev, workspace_dev, B, T): the graph is captured on an internal stream and launched into `stream`. */
 int hfg_forward(hfg_handle h, const float* mel_dev, int B, int T, float* audio_dev,
                 void* workspace_dev, size_t workspace_bytes, void* stream);
 
@@ -138,6 +141,10 @@ int hfg_last_launch_count(hfg_handle h, long long* out);
  * out[0]=conv_pre, out[1+i]=stage i (ups[i] + its resblocks), out[1+n]=conv_post. Returns count via n. */
 int hfg_stage_times_ms(hfg_handle h, float* out, int* n);
 
+/* Kernels launched per measurement stage by the last forward (same indexing as hfg_stage_times_ms; the mel cast of
+ * the 16-bit path counts towards conv_pre): what one "launch" of a stage's roofline row means. */
+int hfg_stage_launches(hfg_handle h, int* out, int* n);
+
 /* Operator-level entry: ONE tapped convolution (the building block of every layer above); synchronous, for
  * parity tests.  A dilated Conv1D (reference model.py:26-66) is out_stride=1, tap_off[j] = j*d - pad_left; one
  * phase p of a Conv1DTranspose (model.py:131-136) is out_stride=u, out_off=p.  act: 0 fp32, 1 fp16, 2 bf16
@@ -161,8 +168,11 @@ int hfg_op_tapped_conv(int act, int engine, const void* x_dev, int B, int x_rows
  * block-Toeplitz weights); act: 1 fp16, 2 bf16; w1/w2 fp32 [ntaps][64][64], b1/b2 [64]; x is stored activated:
  *   xt[q]  = lrelu(b1 + sum_j x[q + off1[j]] . W1_j, mid_slope), taken as 0 outside [0, rows)
  *   v[q]   = b2 + sum_j xt[q + off2[j]] . W2_j + unact(x[q]) + res2[q]      unact(y) = y >= 0 ? y : y * res_inv
- *   out[q] = lrelu(v * out_scale, out_slope)            res2 (running MRF sum, model.py:161-167) may be NULL */
-int hfg_op_resblock_fused(int act, const void* x_dev, int B, int rows, const float* w1_host, const float* b1_host, int ntaps1,
+ *   out[q] = lrelu(v * out_scale, out_slope)            res2 (running MRF sum, model.py:161-167) may be NULL
+ * mode 1 is that iteration; mode 2 is a whole ResBlock2 (model.py:106-112), where both convs carry their own skip:
+ *   x1[q]  = b1 + sum_j x[q + off1[j]] . W1_j + unact(x[q]);  xt = lrelu(x1, mid_slope) (16-bit), 0 outside [0, rows)
+ *   v[q]   = b2 + sum_j xt[q + off2[j]] . W2_j + unact_mid(xt[q]) + res2[q] */
+int hfg_op_resblock_fused(int act, int mode, const void* x_dev, int B, int rows, const float* w1_host, const float* b1_host, int ntaps1,
                           const int* off1, const float* w2_host, const float* b2_host, int ntaps2, const int* off2,
                           float mid_slope, float res_inv, const void* res2_dev, float out_scale, float out_slope,
                           void* out_dev, void* stream);

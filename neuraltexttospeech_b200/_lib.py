@@ -64,10 +64,11 @@ SIGNATURES = {
     "hfg_layer_folds": (C.c_int, [C.c_void_p, C.c_char_p, C.c_size_t]),
     "hfg_last_launch_count": (C.c_int, [C.c_void_p, C.POINTER(C.c_longlong)]),
     "hfg_stage_times_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int)]),
+    "hfg_stage_launches": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "hfg_op_tapped_conv": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                      C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_float,
                                      C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_int, C.c_float, C.c_void_p, C.c_void_p]),
-    "hfg_op_resblock_fused": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int),
+    "hfg_op_resblock_fused": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int),
                                         C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int), C.c_float, C.c_float, C.c_void_p,
                                         C.c_float, C.c_float, C.c_void_p, C.c_void_p]),
     "hfg_host_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),

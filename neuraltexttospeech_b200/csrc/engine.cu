@@ -88,9 +88,11 @@ struct hfg_ctx {
   int marks_per_fwd = 0;
   long long timed_forwards = 0;      // forwards stamped since the last hfg_stage_times_ms
   int n_stage_marks = 0;
+  std::vector<long long> stage_launches;   // kernels launched between consecutive stage marks of the last forward
   // host-buffer path
   int micro_batch = 0;         // host path: utterances per forward; 0 = auto (auto_micro_batch)
   cudaStream_t stream = nullptr;
+  cudaStream_t cap_stream = nullptr;                          // device path: graphs are captured here, launched on the caller's stream
   cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;   // host path: copies overlap the forward of the neighbouring micro-batch
   std::vector<cudaEvent_t> copy_events;                      // 2 per micro-batch (mel landed, audio ready)
   // host path, small forwards (launch-bound): the launch sequence of one micro-batch is captured into a CUDA graph on
@@ -482,6 +484,7 @@ struct Runner {
     const Layer::Fused& F = c1.fused;
     RbArgs a{};
     a.x = x; a.out = out; a.res2 = res2; a.bias1 = F.d_b1; a.bias2 = F.d_b2; a.w1 = F.d_w1; a.w2 = F.d_w2; a.cg = F.cg;
+    a.mode = h->cfg.resblock == 1 ? 1 : 2;
     a.B = B; a.n_q = x_rows / F.fold; a.ntaps1 = F.ntaps1; a.ntaps2 = F.ntaps2;
     memcpy(a.off1, F.off1, sizeof(int) * F.ntaps1); memcpy(a.off2, F.off2, sizeof(int) * F.ntaps2);
     a.mid_slope = mid_slope; a.res_inv = 1.0f / slope_of_res; a.out_scale = out_scale; a.out_slope = out_slope;
@@ -507,8 +510,13 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
   const float kFinalSlope = c.compat == 0 ? 0.3f : 0.01f;       // keras LeakyReLU() default, model.py:152
   int mark = 0;
   const int slot = (int)(h->timed_forwards % kTimingSlots);
+  long long launches_at_mark = h->launches;
+  h->stage_launches.clear();
   auto stamp = [&]() {
-    if (h->stage_timing && mark < h->marks_per_fwd) cudaEventRecord(h->events[(size_t)slot * h->marks_per_fwd + mark++], s);
+    if (mark > 0) h->stage_launches.push_back(h->launches - launches_at_mark);   // mark 0 opens conv_pre
+    launches_at_mark = h->launches;
+    if (h->stage_timing && mark < h->marks_per_fwd) cudaEventRecord(h->events[(size_t)slot * h->marks_per_fwd + mark], s);
+    ++mark;
   };
   auto rb = [&](int n, int m, int which) -> const Layer& { return h->layers[h->i_rb[((size_t)n * HFG_MAX_DILATIONS + m) * 2 + which]]; };
   auto up_layer = [&](int i) -> const Layer& { return h->layers[h->i_ups[i]]; };
@@ -569,6 +577,18 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
           }
         } else {                                                 // ResBlock2.call model.py:106-112
           const Layer& c1 = rb(n, m, 0);
+          if (m == 0 && c1.fused.on) {                           // the whole ResBlock2 (both convs, both skips) in one launch
+            if (chains && j > 0) cu(cudaStreamWaitEvent(r.s, h->ev_sum[j - 1], 0));
+            rnext = (rcur == P) ? Q : P;
+            if (j == nk - 1) next_x = rnext;
+            const float os = next_tc ? next_slope : 1.0f;
+            if (nk == 1) r.resblock_fused(c1, rcur, L, rnext, nullptr, kSlope, 1.0f, os);
+            else if (j == 0) r.resblock_fused(c1, rcur, L, w.S, nullptr, kSlope, 1.0f, 1.0f);
+            else if (j < nk - 1) r.resblock_fused(c1, rcur, L, w.S, w.S, kSlope, 1.0f, 1.0f);
+            else r.resblock_fused(c1, rcur, L, rnext, w.S, kSlope, 1.0f / (float)nk, os);
+            if (chains && j < nk - 1) cu(cudaEventRecord(h->ev_sum[j], r.s));
+            break;
+          }
           if (last && chains && j > 0) cu(cudaStreamWaitEvent(r.s, h->ev_sum[j - 1], 0));
           if (last) r.conv_mrf(c1, rcur, L, rnext, w.S, kSlope, rcur, w.ACC, j, nk, next_slope, next_tc);
           else r.conv(c1, rcur, L, rnext, kSlope, rcur, kSlope, rb_tc);
@@ -594,7 +614,7 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
     r.conv_tc(post, x, L, w.T, nullptr, 1.0f, nullptr, 1.0f, 1.0f, audio_dev, pcm_dev);
     if (r.status != cudaSuccess) return fail(h, HFG_ERR_CUDA, "conv_post launch failed: %s", cudaGetErrorString(r.status));
     stamp();
-    h->n_stage_marks = mark;
+    h->n_stage_marks = std::min(mark, h->marks_per_fwd);
     if (h->stage_timing) h->timed_forwards++;
     return HFG_OK;
   }
@@ -606,7 +626,7 @@ int run_forward(hfg_ctx* h, const float* mel_dev, int B, int T, float* audio_dev
   h->launches++;
   if (e != cudaSuccess) return fail(h, HFG_ERR_CUDA, "conv_post launch failed: %s", cudaGetErrorString(e));
   stamp();
-  h->n_stage_marks = mark;
+  h->n_stage_marks = std::min(mark, h->marks_per_fwd);
   if (h->stage_timing) h->timed_forwards++;
   return HFG_OK;
 }
@@ -794,10 +814,16 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
   }
   // Fused ResBlock1 iterations (resblock_tc.cu): both convs of an iteration on the tcgen05 path, C*f = 64 with
   // f = 64/C dividing the stage's rows per frame, tap lists / spans that fit the fused kernel's shared-memory plan.
-  if (c.resblock == 1 && h->fuse_resblocks && h->act != ACT_F32 && !h->force_ffma) {
+  if (h->fuse_resblocks && h->act != ACT_F32 && !h->force_ffma) {
     for (int n = 0; n < c.num_upsamples * c.num_kernels; ++n)
       for (int m = 0; m < c.num_dilations[n % c.num_kernels]; ++m) {
-        const int i1 = h->i_rb[((size_t)n * HFG_MAX_DILATIONS + m) * 2], i2 = h->i_rb[((size_t)n * HFG_MAX_DILATIONS + m) * 2 + 1];
+        // ResBlock1: (convs1[m], convs2[m]) of iteration m; ResBlock2: (convs[0], convs[1]) = the whole block, once
+        int i1, i2;
+        if (c.resblock == 1) { i1 = h->i_rb[((size_t)n * HFG_MAX_DILATIONS + m) * 2]; i2 = h->i_rb[((size_t)n * HFG_MAX_DILATIONS + m) * 2 + 1]; }
+        else {
+          if (m != 0 || c.num_dilations[n % c.num_kernels] != 2) continue;
+          i1 = h->i_rb[((size_t)n * HFG_MAX_DILATIONS + 0) * 2]; i2 = h->i_rb[((size_t)n * HFG_MAX_DILATIONS + 1) * 2];
+        }
         if (i1 < 0 || i2 < 0) continue;
         Layer& A = h->layers[i1]; Layer& Bc = h->layers[i2];
         if (!A.use_tc || !Bc.use_tc || A.cin != A.cout || A.cin > 64 || 64 % A.cin) continue;
@@ -808,6 +834,7 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
         const KView V1 = build_view(A, fold_weight_norm(A), pl1, f, f, false), V2 = build_view(Bc, fold_weight_norm(Bc), pl2, f, f, false);
         if (V1.off.size() != 1 || V2.off.size() != 1 || V1.max_taps() > kMaxTaps || V2.max_taps() > kMaxTaps) continue;
         RbArgs ra{};
+        ra.mode = c.resblock == 1 ? 1 : 2;
         ra.ntaps1 = (int)V1.off[0].size(); ra.ntaps2 = (int)V2.off[0].size();
         for (int t = 0; t < ra.ntaps1; ++t) ra.off1[t] = V1.off[0][t];
         for (int t = 0; t < ra.ntaps2; ++t) ra.off2[t] = V2.off[0][t];
@@ -872,6 +899,59 @@ int hfg_workspace_bytes(hfg_handle h, int B, int T, size_t* out) {
   return HFG_OK;
 }
 
+// One micro-batch of the host path on h->stream.  Launch-bound forwards (few frames) are replayed from a CUDA graph
+// captured on the second use of the same (buffers, shape): 79 launches + 230 tensor-map encodes become one graph launch.
+static int forward_maybe_graph(hfg_ctx* h, const float* mel, int nb, int T, char* dev_out, int sample_bytes, char* ws, size_t ws_bytes,
+                               cudaStream_t launch) {
+  float* audio = sample_bytes == 4 ? (float*)dev_out : nullptr;
+  int16_t* pcm = sample_bytes == 2 ? (int16_t*)dev_out : nullptr;
+  bool eligible = h->use_graphs && !h->stage_timing && (long long)nb * T <= 8192;
+  if (eligible && launch != h->stream) {               // a caller's stream: leave it alone while the caller captures it
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(launch, &st) != cudaSuccess) { cudaGetLastError(); eligible = false; }
+    else if (st != cudaStreamCaptureStatusNone) eligible = false;
+  }
+  if (!eligible) return run_forward(h, mel, nb, T, audio, pcm, ws, ws_bytes, launch);
+  hfg_ctx::GraphEntry* e = nullptr;
+  for (auto& g : h->graphs)
+    if (g.mel == mel && g.out == dev_out && g.ws == ws && g.B == nb && g.T == T && g.sample_bytes == sample_bytes) { e = &g; break; }
+  if (!e) {
+    if (h->graphs.size() >= 16) { if (h->graphs.front().exec) cudaGraphExecDestroy(h->graphs.front().exec); h->graphs.erase(h->graphs.begin()); }
+    h->graphs.push_back({mel, dev_out, ws, nb, T, sample_bytes, 0, 0, nullptr});
+    e = &h->graphs.back();
+  }
+  if (e->exec) {
+    h->launches = e->launches;
+    CUDA_TRY(h, cudaGraphLaunch(e->exec, launch));
+    return HFG_OK;
+  }
+  if (e->uses++ == 0) return run_forward(h, mel, nb, T, audio, pcm, ws, ws_bytes, launch);   // first use: plain (also warms per-kernel attributes)
+  // capture on an internal stream (a caller's stream may be the legacy default stream, which cannot be captured);
+  // the instantiated graph is then launched into the caller's stream like any other work
+  cudaStream_t cap = launch;
+  if (launch != h->stream) {
+    if (!h->cap_stream) CUDA_TRY(h, cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
+    cap = h->cap_stream;
+  }
+  CUDA_TRY(h, cudaStreamBeginCapture(cap, cudaStreamCaptureModeThreadLocal));
+  int rc = run_forward(h, mel, nb, T, audio, pcm, ws, ws_bytes, cap);
+  cudaGraph_t graph = nullptr;
+  cudaError_t ce = cudaStreamEndCapture(cap, &graph);
+  if (rc || ce != cudaSuccess || !graph) {
+    if (graph) cudaGraphDestroy(graph);
+    cudaGetLastError();
+    h->use_graphs = false;                               // capture unsupported here: stay on plain launches
+    if (rc) return rc;
+    return run_forward(h, mel, nb, T, audio, pcm, ws, ws_bytes, launch);
+  }
+  ce = cudaGraphInstantiate(&e->exec, graph, 0);
+  cudaGraphDestroy(graph);
+  if (ce != cudaSuccess) { e->exec = nullptr; cudaGetLastError(); h->use_graphs = false; return run_forward(h, mel, nb, T, audio, pcm, ws, ws_bytes, launch); }
+  e->launches = h->launches;
+  CUDA_TRY(h, cudaGraphLaunch(e->exec, launch));
+  return HFG_OK;
+}
+
 static int forward_device(hfg_handle h, const float* mel_dev, int B, int T, float* audio_dev, int16_t* pcm_dev,
                           void* workspace_dev, size_t workspace_bytes, void* stream, const char* fn) {
   if (!h) return HFG_ERR_INVALID;
@@ -887,7 +967,10 @@ static int forward_device(hfg_handle h, const float* mel_dev, int B, int T, floa
   if ((size_t)(ws - (char*)workspace_dev) + need > workspace_bytes)
     return fail(h, HFG_ERR_NOMEM, "workspace too small: need %zu bytes, got %zu", need + 256, workspace_bytes);
   CUDA_TRY(h, cudaSetDevice(h->device));
-  return run_forward(h, mel_dev, B, T, audio_dev, pcm_dev, ws, workspace_bytes - (size_t)(ws - (char*)workspace_dev), (cudaStream_t)stream);
+  // launch-bound forwards are replayed from a CUDA graph captured on the second call with the same buffers and shape
+  // (tensor-map encodes and ~60-80 launches become one graph launch into the caller's stream)
+  return forward_maybe_graph(h, mel_dev, B, T, audio_dev ? (char*)audio_dev : (char*)pcm_dev, audio_dev ? 4 : 2, ws,
+                             workspace_bytes - (size_t)(ws - (char*)workspace_dev), (cudaStream_t)stream);
 }
 
 int hfg_forward(hfg_handle h, const float* mel_dev, int B, int T, float* audio_dev, void* workspace_dev,
@@ -932,46 +1015,6 @@ static int grow_pinned(hfg_ctx* h, char** buf, size_t* have, size_t need) {
   *buf = nullptr; *have = 0;
   CUDA_TRY(h, cudaHostAlloc((void**)buf, need, cudaHostAllocDefault));
   *have = need;
-  return HFG_OK;
-}
-
-// One micro-batch of the host path on h->stream.  Launch-bound forwards (few frames) are replayed from a CUDA graph
-// captured on the second use of the same (buffers, shape): 79 launches + 230 tensor-map encodes become one graph launch.
-static int forward_maybe_graph(hfg_ctx* h, const float* mel, int nb, int T, char* dev_out, int sample_bytes) {
-  float* audio = sample_bytes == 4 ? (float*)dev_out : nullptr;
-  int16_t* pcm = sample_bytes == 2 ? (int16_t*)dev_out : nullptr;
-  const bool eligible = h->use_graphs && !h->stage_timing && (long long)nb * T <= 8192;
-  if (!eligible) return run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->ws_bytes, h->stream);
-  hfg_ctx::GraphEntry* e = nullptr;
-  for (auto& g : h->graphs)
-    if (g.mel == mel && g.out == dev_out && g.ws == h->ws && g.B == nb && g.T == T && g.sample_bytes == sample_bytes) { e = &g; break; }
-  if (!e) {
-    if (h->graphs.size() >= 16) { if (h->graphs.front().exec) cudaGraphExecDestroy(h->graphs.front().exec); h->graphs.erase(h->graphs.begin()); }
-    h->graphs.push_back({mel, dev_out, h->ws, nb, T, sample_bytes, 0, 0, nullptr});
-    e = &h->graphs.back();
-  }
-  if (e->exec) {
-    h->launches = e->launches;
-    CUDA_TRY(h, cudaGraphLaunch(e->exec, h->stream));
-    return HFG_OK;
-  }
-  if (e->uses++ == 0) return run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->ws_bytes, h->stream);   // first use: plain (also warms per-kernel attributes)
-  CUDA_TRY(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
-  int rc = run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->ws_bytes, h->stream);
-  cudaGraph_t graph = nullptr;
-  cudaError_t ce = cudaStreamEndCapture(h->stream, &graph);
-  if (rc || ce != cudaSuccess || !graph) {
-    if (graph) cudaGraphDestroy(graph);
-    cudaGetLastError();
-    h->use_graphs = false;                               // capture unsupported here: stay on plain launches
-    if (rc) return rc;
-    return run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->ws_bytes, h->stream);
-  }
-  ce = cudaGraphInstantiate(&e->exec, graph, 0);
-  cudaGraphDestroy(graph);
-  if (ce != cudaSuccess) { e->exec = nullptr; cudaGetLastError(); h->use_graphs = false; return run_forward(h, mel, nb, T, audio, pcm, (char*)h->ws, h->ws_bytes, h->stream); }
-  e->launches = h->launches;
-  CUDA_TRY(h, cudaGraphLaunch(e->exec, h->stream));
   return HFG_OK;
 }
 
@@ -1068,7 +1111,7 @@ static int forward_host(hfg_handle h, const float* mel_host, int B, int T, void*
     const int nb = parts[i], b0 = starts[i];
     char* dev_out = (char*)h->d_audio + (size_t)b0 * aud_elems * sample_bytes;
     CUDA_TRY(h, cudaStreamWaitEvent(h->stream, h->copy_events[3 * i], 0));
-    int rc = forward_maybe_graph(h, h->d_mel + (size_t)b0 * mel_elems, nb, T, dev_out, sample_bytes);
+    int rc = forward_maybe_graph(h, h->d_mel + (size_t)b0 * mel_elems, nb, T, dev_out, sample_bytes, (char*)h->ws, h->ws_bytes, h->stream);
     launches += h->launches; h->launches = 0;
     if (rc) { cudaStreamSynchronize(h->h2d_stream); cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->d2h_stream); return rc; }
     CUDA_TRY(h, cudaEventRecord(h->copy_events[3 * i + 1], h->stream));
@@ -1147,6 +1190,16 @@ int hfg_layer_folds(hfg_handle h, char* buf, size_t cap) {
 int hfg_last_launch_count(hfg_handle h, long long* out) {
   if (!h || !out) return HFG_ERR_INVALID;
   *out = h->launches;
+  return HFG_OK;
+}
+
+int hfg_stage_launches(hfg_handle h, int* out, int* n) {
+  if (!h || !out || !n) return HFG_ERR_INVALID;
+  const int cnt = (int)h->stage_launches.size();
+  if (cnt == 0) return fail(h, HFG_ERR_STATE, "no forward ran on this handle");
+  if (*n < cnt) return fail(h, HFG_ERR_INVALID, "need room for %d ints", cnt);
+  for (int i = 0; i < cnt; ++i) out[i] = (int)h->stage_launches[i];
+  *n = cnt;
   return HFG_OK;
 }
 
@@ -1233,7 +1286,7 @@ int hfg_op_tapped_conv(int act, int engine, const void* x_dev, int B, int x_rows
 
 // One fused ResBlock1 iteration (resblock_tc.cu) on caller-provided device buffers; packs and uploads the weights on
 // every call -- operator-level parity tests only.
-int hfg_op_resblock_fused(int act, const void* x_dev, int B, int rows, const float* w1_host, const float* b1_host, int ntaps1,
+int hfg_op_resblock_fused(int act, int mode, const void* x_dev, int B, int rows, const float* w1_host, const float* b1_host, int ntaps1,
                           const int* off1, const float* w2_host, const float* b2_host, int ntaps2, const int* off2,
                           float mid_slope, float res_inv, const void* res2_dev, float out_scale, float out_slope,
                           void* out_dev, void* stream) {
@@ -1241,6 +1294,7 @@ int hfg_op_resblock_fused(int act, const void* x_dev, int B, int rows, const flo
       ntaps1 < 1 || ntaps2 < 1 || ntaps1 > kMaxTaps || ntaps2 > kMaxTaps)
     return fail(nullptr, HFG_ERR_INVALID, "hfg_op_resblock_fused: bad argument");
   RbArgs a{};
+  a.mode = mode;
   a.x = x_dev; a.out = out_dev; a.res2 = res2_dev; a.B = B; a.n_q = rows; a.ntaps1 = ntaps1; a.ntaps2 = ntaps2;
   memcpy(a.off1, off1, sizeof(int) * ntaps1); memcpy(a.off2, off2, sizeof(int) * ntaps2);
   a.mid_slope = mid_slope; a.res_inv = res_inv; a.out_scale = out_scale; a.out_slope = out_slope;
@@ -1297,6 +1351,7 @@ void hfg_destroy(hfg_handle h) {
   if (h->d_mel) cudaFree(h->d_mel);
   if (h->d_audio) cudaFree(h->d_audio);
   if (h->stream) cudaStreamDestroy(h->stream);
+  if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
   if (h->h2d_stream) cudaStreamDestroy(h->h2d_stream);
   if (h->d2h_stream) cudaStreamDestroy(h->d2h_stream);
   for (auto& ev : h->copy_events) cudaEventDestroy(ev);

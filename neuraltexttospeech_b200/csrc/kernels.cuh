@@ -134,6 +134,8 @@ struct RbArgs {
   const float* bias1; const float* bias2;   // [64] each (kernel view: the layer's bias replicated per fold slot)
   const void* w1; const void* w2;           // rb_pack_weights images (256-byte aligned)
   int cg;               // CTA grouping the weights were packed for (rb_supported)
+  int mode;             // 1: ResBlock1 iteration (above); 2: whole ResBlock2 (model.py:106-112), both convs with their own skip:
+                        //    x1 = b1 + conv1(x) + unact(x); xt = lrelu(x1); v = b2 + conv2(xt) + x1 (as stored in xt) + res2
   int B, n_q;
   int ntaps1, ntaps2;
   int off1[kMaxTaps], off2[kMaxTaps];

@@ -21,6 +21,10 @@
 //   fin    acc2 -> (+ running MRF sum, * 1/num_kernels on the last resblock: model.py:161-167) -> lrelu for the consumer
 //          -> 16-bit, in place in the (now dead) xt tile -> TMA store.  The last span2 rows of a tile are not valid
 //          (their taps read past the xt rows computed here) and are not stored: the last block uses a shorter box.
+// MODE 2 is a whole ResBlock2 (model.py:106-112: x1 = c_a(lrelu(x)) + x; x2 = c_b(lrelu(x1)) + x1): the mid epilogue adds
+// the first skip connection before activating (xt = lrelu(x1)), conv2 starts from zero, and the fin epilogue recovers x1
+// from the 16-bit xt tile (exactly what the unfused path reads back from HBM) for the second one.  The xt tile then has
+// `lead` spare rows on top so that output row r and its x1 share one shared-memory row at a 1024-byte-aligned block start.
 // Roles: warp 0 slab producer, warp 1 weight producer (both convs' weights stay resident), warp 2 MMA issuer (order
 // c1(i+1), c2(i): the tensor core works on the next tile's conv1 while the mid epilogue of this one runs), warps 4-15
 // three epilogue groups taking mid / fin passes round-robin, warp 16 store issuer.  CG = 2 runs CTA pairs
@@ -52,10 +56,10 @@ struct RbPlan {
   int off_xt, off_w, off_bias, off_bar, total;
 };
 
-__host__ __device__ inline RbPlan rb_plan(int mb, int cg, int slab_rows, int span2, int ntaps, int nsl, int nxt) {
+__host__ __device__ inline RbPlan rb_plan(int mb, int cg, int slab_rows, int span2, int ntaps, int nsl, int nxt, int lead = 0) {
   RbPlan p;
   p.slab_bytes = slab_rows * kRbRowB;                         // slab_rows % 8 == 0 -> every slot 1024-byte aligned
-  p.xt_rows = mb * 128 + ((span2 + 7) & ~7);
+  p.xt_rows = mb * 128 + ((lead + span2 + 7) & ~7);
   p.xt_bytes = p.xt_rows * kRbRowB;
   p.w_bytes = ntaps * (kRbC / cg) * kRbRowB;                  // both convs; a CTA of a pair holds half of the weight rows
   int off = nsl * p.slab_bytes;
@@ -79,10 +83,11 @@ struct RbKArgs {
   int tiles_q, total_tiles;            // per utterance / in total (CG == 2: PAIR tiles of 2*r2 rows)
   int box_rows, nbox;                  // slab = nbox TMA boxes of box_rows rows
   int nsl, nxt;                        // ring depths (slab slots, xt tiles)
-  float mid_slope, res_inv, out_scale, out_slope;
+  int lead;                            // MODE 2: spare rows on top of the xt tile (0 in MODE 1)
+  float mid_slope, xt_inv, res_inv, out_scale, out_slope;   // xt_inv = 1 / mid_slope
 };
 
-template <typename T, int MB, int CG>
+template <typename T, int MB, int CG, int MODE>
 __global__ void __launch_bounds__(kRbThreads, 1)
 resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_out,
                    const __grid_constant__ CUtensorMap tm_out_last, const __grid_constant__ CUtensorMap tm_w1,
@@ -94,7 +99,8 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
   constexpr int EG = kRbEpiGroups;
   const int nsl = ka.nsl, nxt = ka.nxt;
   const int ntaps = ka.ntaps1 + ka.ntaps2;
-  const RbPlan pl = rb_plan(MB, CG, ka.nbox * ka.box_rows, ka.span2, ntaps, nsl, nxt);
+  const RbPlan pl = rb_plan(MB, CG, ka.nbox * ka.box_rows, ka.span2, ntaps, nsl, nxt, ka.lead);
+  const int lead = MODE == 2 ? ka.lead : 0;
 
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* slab = smem;
@@ -192,7 +198,7 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
       // ===================== MMA issuer (pair: leader only) =====================
       if (rank == 0 && my_tiles > 0) {
         const uint32_t slab_addr = smem_u32(slab), xt_addr = smem_u32(xt), w_addr = smem_u32(wsm);
-        auto issue = [&](uint32_t a_base, uint32_t w_base, const int* offs, int mn, int nt, uint32_t tacc, bool fresh) {
+        auto issue = [&](uint32_t a_base, uint32_t w_base, const int* offs, int mn, int nt, uint32_t tacc, bool fresh) {   // mn: offset of smem row 0
           if (elect_one()) {
 #pragma unroll 1
             for (int mb = 0; mb < MB; ++mb) {
@@ -228,8 +234,8 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
         auto conv2 = [&](int i) {
           mbar_wait(&mid_done[i & 1], (i >> 1) & 1);      // xt tile written, acc2 pre-loaded with the residual, acc1 drained
           tc_fence_after();
-          issue(xt_addr + (i % nxt) * pl.xt_bytes, w_addr + ka.ntaps1 * TAP_BYTES, ka.off2, ka.min2, ka.ntaps2,
-                tmem_base + (2 * MB + (i & 1) * MB) * kRbC, false);
+          issue(xt_addr + (i % nxt) * pl.xt_bytes, w_addr + ka.ntaps1 * TAP_BYTES, ka.off2, ka.min2 - lead, ka.ntaps2,
+                tmem_base + (2 * MB + (i & 1) * MB) * kRbC, MODE == 2);
           commit(&acc2_full[i & 1]);
         };
         mbar_wait(&w_full[0], 0);
@@ -248,6 +254,7 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
     if (warp == kRbStoreWarp) {
       // ===================== store issuer =====================
       // one bulk group per tile
+      const int out_row0 = MODE == 2 ? lead - ka.min2 : 0;    // xt row holding output row 0 (multiple of 8)
       for (int i = 0; i < my_tiles; ++i) {
         int b; const int q0 = tile_q0(tile0 + i * tile_step, b);
         const int buf = i % nxt;
@@ -255,7 +262,7 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
           mbar_wait(&out_done[2 * buf + mb], (i / nxt) & 1);
           if (elect_one()) {
             const int q = q0 + mb * 128;
-            if (q < ka.n_q) tma_store_3d(mb == MB - 1 ? &tm_out_last : &tm_out, xt + buf * pl.xt_bytes + mb * 128 * kRbRowB, 0, q, b);
+            if (q < ka.n_q) tma_store_3d(mb == MB - 1 ? &tm_out_last : &tm_out, xt + buf * pl.xt_bytes + (mb * 128 + out_row0) * kRbRowB, 0, q, b);
           }
           __syncwarp();
         }
@@ -300,8 +307,11 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
           const int r = mb * 128 + er;                                // row of the CTA tile
           const int g = q0 + ka.min2 + r;                             // kernel-view row of this xt row (xt row 0 = q0 - h2)
           const bool inside = g >= 0 && g < ka.n_q;
-          const int sr = r + halo;                                    // slab row holding x of output row r
-          uint8_t* xrow = xt + xbuf * pl.xt_bytes + r * kRbRowB;
+          // MODE 1: slab row of OUTPUT row r (skip connection of the iteration, goes into acc2);
+          // MODE 2: slab row of XT row r (skip connection of the first conv, added before the activation)
+          const int sr = MODE == 2 ? r - ka.min1 : r + halo;
+          const int xr = r + lead;                                    // shared-memory row of xt row r
+          uint8_t* xrow = xt + xbuf * pl.xt_bytes + xr * kRbRowB;
           const uint8_t* srow = slab + sbuf * pl.slab_bytes + sr * kRbRowB;
           const uint32_t t1 = tmem_base + lane_base + ((i & 1) * MB + mb) * kRbC;
           const uint32_t t2 = tmem_base + lane_base + (2 * MB + (i & 1) * MB + mb) * kRbC;
@@ -323,26 +333,36 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                 v[4 * e + 0] = __uint_as_float(acc[8 * k + 4 * e + 0]) + bb.x; v[4 * e + 1] = __uint_as_float(acc[8 * k + 4 * e + 1]) + bb.y;
                 v[4 * e + 2] = __uint_as_float(acc[8 * k + 4 * e + 2]) + bb.z; v[4 * e + 3] = __uint_as_float(acc[8 * k + 4 * e + 3]) + bb.w;
               }
+              if (MODE == 2) {                                        // x1 = c_a(lrelu(x)) + x   (model.py:108-111)
+                float2 f;
+                f = H2<T>::up(rr[k].x); v[0] += lrelu_ge1(f.x, res_inv); v[1] += lrelu_ge1(f.y, res_inv);
+                f = H2<T>::up(rr[k].y); v[2] += lrelu_ge1(f.x, res_inv); v[3] += lrelu_ge1(f.y, res_inv);
+                f = H2<T>::up(rr[k].z); v[4] += lrelu_ge1(f.x, res_inv); v[5] += lrelu_ge1(f.y, res_inv);
+                f = H2<T>::up(rr[k].w); v[6] += lrelu_ge1(f.x, res_inv); v[7] += lrelu_ge1(f.y, res_inv);
+              }
 #pragma unroll
-              for (int e = 0; e < 8; ++e) v[e] = inside ? lrelu_le1(v[e], mid_slope) : 0.f;
+              for (int e = 0; e < 8; ++e) v[e] = lrelu_le1(v[e], mid_slope);
               uint4 u;
               u.x = H2<T>::down(v[0], v[1]); u.y = H2<T>::down(v[2], v[3]); u.z = H2<T>::down(v[4], v[5]); u.w = H2<T>::down(v[6], v[7]);
-              *reinterpret_cast<uint4*>(xrow + (((c0 / 8 + k) ^ (r & 7)) * 16)) = u;
+              if (!inside) u = make_uint4(0u, 0u, 0u, 0u);           // conv2 sees zero padding outside the utterance
+              *reinterpret_cast<uint4*>(xrow + (((c0 / 8 + k) ^ (xr & 7)) * 16)) = u;
             }
-            // skip connection (model.py:79): x is stored activated; acc2 starts from unact(x) + b2
-            uint32_t init[32];
-            const float4* c4 = reinterpret_cast<const float4*>(bias_s + kRbC + c0);
+            if (MODE == 1) {
+              // skip connection (model.py:79): x is stored activated; acc2 starts from unact(x) + b2
+              uint32_t init[32];
+              const float4* c4 = reinterpret_cast<const float4*>(bias_s + kRbC + c0);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              float2 f; const float4 ba = c4[2 * k], bb = c4[2 * k + 1];
-              f = H2<T>::up(rr[k].x); init[8 * k + 0] = __float_as_uint(lrelu_ge1(f.x, res_inv) + ba.x); init[8 * k + 1] = __float_as_uint(lrelu_ge1(f.y, res_inv) + ba.y);
-              f = H2<T>::up(rr[k].y); init[8 * k + 2] = __float_as_uint(lrelu_ge1(f.x, res_inv) + ba.z); init[8 * k + 3] = __float_as_uint(lrelu_ge1(f.y, res_inv) + ba.w);
-              f = H2<T>::up(rr[k].z); init[8 * k + 4] = __float_as_uint(lrelu_ge1(f.x, res_inv) + bb.x); init[8 * k + 5] = __float_as_uint(lrelu_ge1(f.y, res_inv) + bb.y);
-              f = H2<T>::up(rr[k].w); init[8 * k + 6] = __float_as_uint(lrelu_ge1(f.x, res_inv) + bb.z); init[8 * k + 7] = __float_as_uint(lrelu_ge1(f.y, res_inv) + bb.w);
+              for (int k = 0; k < 4; ++k) {
+                float2 f; const float4 ba = c4[2 * k], bb = c4[2 * k + 1];
+                f = H2<T>::up(rr[k].x); init[8 * k + 0] = __float_as_uint(lrelu_ge1(f.x, res_inv) + ba.x); init[8 * k + 1] = __float_as_uint(lrelu_ge1(f.y, res_inv) + ba.y);
+                f = H2<T>::up(rr[k].y); init[8 * k + 2] = __float_as_uint(lrelu_ge1(f.x, res_inv) + ba.z); init[8 * k + 3] = __float_as_uint(lrelu_ge1(f.y, res_inv) + ba.w);
+                f = H2<T>::up(rr[k].z); init[8 * k + 4] = __float_as_uint(lrelu_ge1(f.x, res_inv) + bb.x); init[8 * k + 5] = __float_as_uint(lrelu_ge1(f.y, res_inv) + bb.y);
+                f = H2<T>::up(rr[k].w); init[8 * k + 6] = __float_as_uint(lrelu_ge1(f.x, res_inv) + bb.z); init[8 * k + 7] = __float_as_uint(lrelu_ge1(f.y, res_inv) + bb.w);
+              }
+              tmem_st32(t2 + c0, init);
             }
-            tmem_st32(t2 + c0, init);
           }
-          tmem_st_wait();
+          if (MODE == 1) tmem_st_wait();
           tc_fence_before();
           fence_proxy_async();                                        // xt rows -> visible to the tensor core (async proxy)
           __syncwarp();
@@ -366,7 +386,8 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
           const int r = mb * 128 + er;
           const int q = q0 + r;
           const bool has_res2 = ka.res2 != nullptr && r < ka.r2 && q < ka.n_q;
-          uint8_t* orow = xt + xbuf * pl.xt_bytes + r * kRbRowB;
+          const int orr = MODE == 2 ? r + lead - ka.min2 : r;        // MODE 2: the row of x1 (second skip connection), reused for the output
+          uint8_t* orow = xt + xbuf * pl.xt_bytes + orr * kRbRowB;
           const uint32_t t2 = tmem_base + lane_base + (2 * MB + (i & 1) * MB + mb) * kRbC;
 #pragma unroll
           for (int c0 = 0; c0 < kRbC; c0 += 32) {
@@ -378,12 +399,26 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
 #pragma unroll
               for (int k = 0; k < 4; ++k) rr2[k] = rp[k];
             }
+            uint4 rx[4];
+            if (MODE == 2) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k) rx[k] = *reinterpret_cast<const uint4*>(orow + (((c0 / 8 + k) ^ (orr & 7)) * 16));
+            }
             tmem_ld_wait();
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               float v[8];
 #pragma unroll
               for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(acc[8 * k + e]);
+              if (MODE == 2) {                                        // x2 = c_b(lrelu(x1)) + x1, x1 recovered from the 16-bit xt tile
+                const float4 ba = *reinterpret_cast<const float4*>(bias_s + kRbC + c0 + 8 * k), bb = *reinterpret_cast<const float4*>(bias_s + kRbC + c0 + 8 * k + 4);
+                const float xi = ka.xt_inv;
+                float2 f;
+                f = H2<T>::up(rx[k].x); v[0] += lrelu_ge1(f.x, xi) + ba.x; v[1] += lrelu_ge1(f.y, xi) + ba.y;
+                f = H2<T>::up(rx[k].y); v[2] += lrelu_ge1(f.x, xi) + ba.z; v[3] += lrelu_ge1(f.y, xi) + ba.w;
+                f = H2<T>::up(rx[k].z); v[4] += lrelu_ge1(f.x, xi) + bb.x; v[5] += lrelu_ge1(f.y, xi) + bb.y;
+                f = H2<T>::up(rx[k].w); v[6] += lrelu_ge1(f.x, xi) + bb.z; v[7] += lrelu_ge1(f.y, xi) + bb.w;
+              }
               if (has_res2) {
                 float2 f;
                 f = H2<T>::up(rr2[k].x); v[0] += f.x; v[1] += f.y;
@@ -399,7 +434,7 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
               for (int e = 0; e < 8; ++e) v[e] = lrelu_le1(v[e], osl);
               uint4 u;
               u.x = H2<T>::down(v[0], v[1]); u.y = H2<T>::down(v[2], v[3]); u.z = H2<T>::down(v[4], v[5]); u.w = H2<T>::down(v[6], v[7]);
-              *reinterpret_cast<uint4*>(orow + (((c0 / 8 + k) ^ (r & 7)) * 16)) = u;
+              *reinterpret_cast<uint4*>(orow + (((c0 / 8 + k) ^ (orr & 7)) * 16)) = u;
             }
           }
           tc_fence_before();
@@ -465,7 +500,7 @@ int rb_env_int(const char* name, int dflt) { const char* e = getenv(name); retur
 
 void rb_boxes(int rows, int* box_rows, int* nbox) {
   int best_br = 256, best_pad = 1 << 30;
-  for (int br = 256; br >= 8; br >>= 1) {               // fewest padded rows with at most 24 boxes; ties -> larger box
+  for (int br = 256; br >= 32; br >>= 1) {              // fewest padded rows with boxes of >= 4 KB; ties -> larger box
     const int nb = (rows + br - 1) / br;
     if (nb > 24) break;
     if (nb * br < best_pad) { best_pad = nb * br; best_br = br; }
@@ -473,7 +508,7 @@ void rb_boxes(int rows, int* box_rows, int* nbox) {
   *box_rows = best_br; *nbox = (rows + best_br - 1) / best_br;
 }
 
-struct RbShape { int mb, cg, nsl, nxt, box_rows, nbox, min1, min2, span1, span2; };
+struct RbShape { int mb, cg, nsl, nxt, box_rows, nbox, min1, min2, span1, span2, lead; };
 
 void rb_minmax(const int* off, int n, int* mn, int* mx) {
   *mn = off[0]; *mx = off[0];
@@ -491,7 +526,9 @@ bool rb_choose(const RbArgs& a, RbShape* out) {
   rb_minmax(a.off2, a.ntaps2, &s.min2, &mx2);
   if (s.min1 > 0 || s.min2 > 0 || mx1 < 0 || mx2 < 0) return false;      // both convs see their own row (zero offset inside the taps' hull)
   s.span1 = mx1 - s.min1; s.span2 = mx2 - s.min2;
-  if (s.span2 >= 64) return false;
+  if (s.span2 >= 100) return false;                      // the last block of a tile must keep some valid rows
+  if (a.mode != 1 && a.mode != 2) return false;
+  s.lead = a.mode == 2 ? (8 - ((-s.min2) % 8)) % 8 : 0;     // MODE 2: output row 0 / its x1 sit on an 8-row boundary of the xt tile
   static const int force_mb = rb_env_int("HFG_RB_MB", 0), force_cg = rb_env_int("HFG_RB_CG", 0), force_nxt = rb_env_int("HFG_RB_NXT", 0);
   const int ntaps = a.ntaps1 + a.ntaps2;
   struct Try { int mb, nxt_min; };
@@ -501,14 +538,14 @@ bool rb_choose(const RbArgs& a, RbShape* out) {
     for (const Try& t : order) {
       if (force_mb && t.mb != force_mb) continue;
       const int halo = -(s.min1 + s.min2);
-      const int need = t.mb * 128 + (s.span1 > halo ? s.span1 : halo);
+      const int need = t.mb * 128 + (a.mode == 2 ? s.span1 : (s.span1 > halo ? s.span1 : halo));
       int br, nb; rb_boxes(need, &br, &nb);
       int nsl = 2, nxt = t.nxt_min;
       if (force_nxt) { if (force_nxt < t.nxt_min) continue; nxt = force_nxt; }
-      if ((size_t)rb_plan(t.mb, cg, br * nb, s.span2, ntaps, nsl, nxt).total > kRbMaxSmem) continue;
+      if ((size_t)rb_plan(t.mb, cg, br * nb, s.span2, ntaps, nsl, nxt, s.lead).total > kRbMaxSmem) continue;
       // spend what is left on a third xt tile, then a third slab slot
-      if (!force_nxt && nxt < kRbMaxXt && nxt >= 2 && (size_t)rb_plan(t.mb, cg, br * nb, s.span2, ntaps, nsl, nxt + 1).total <= kRbMaxSmem) ++nxt;
-      if (nsl < kRbMaxSl && (size_t)rb_plan(t.mb, cg, br * nb, s.span2, ntaps, nsl + 1, nxt).total <= kRbMaxSmem) ++nsl;
+      if (!force_nxt && nxt < kRbMaxXt && nxt >= 2 && (size_t)rb_plan(t.mb, cg, br * nb, s.span2, ntaps, nsl, nxt + 1, s.lead).total <= kRbMaxSmem) ++nxt;
+      if (nsl < kRbMaxSl && (size_t)rb_plan(t.mb, cg, br * nb, s.span2, ntaps, nsl + 1, nxt, s.lead).total <= kRbMaxSmem) ++nsl;
       s.mb = t.mb; s.cg = cg; s.nsl = nsl; s.nxt = nxt; s.box_rows = br; s.nbox = nb;
       *out = s;
       return true;
@@ -517,7 +554,7 @@ bool rb_choose(const RbArgs& a, RbShape* out) {
   return false;
 }
 
-template <typename T, int MB, int CG>
+template <typename T, int MB, int CG, int MODE>
 cudaError_t rb_launch_t(const RbArgs& a, const RbShape& sh, ActType act, cudaStream_t st) {
   RbKArgs ka{};
   ka.bias1 = a.bias1; ka.bias2 = a.bias2; ka.res2 = a.res2; ka.w1 = a.w1; ka.w2 = a.w2;
@@ -528,10 +565,11 @@ cudaError_t rb_launch_t(const RbArgs& a, const RbShape& sh, ActType act, cudaStr
   ka.r2 = MB * 128 - sh.span2;
   ka.tiles_q = (a.n_q + CG * ka.r2 - 1) / (CG * ka.r2);
   ka.total_tiles = a.B * ka.tiles_q;
-  ka.box_rows = sh.box_rows; ka.nbox = sh.nbox; ka.nsl = sh.nsl; ka.nxt = sh.nxt;
+  ka.box_rows = sh.box_rows; ka.nbox = sh.nbox; ka.nsl = sh.nsl; ka.nxt = sh.nxt; ka.lead = sh.lead;
+  ka.xt_inv = 1.0f / a.mid_slope;
   ka.mid_slope = a.mid_slope; ka.res_inv = a.res_inv; ka.out_scale = a.out_scale; ka.out_slope = a.out_slope;
   if (!(a.mid_slope > 0.f && a.mid_slope <= 1.f) || !(a.out_slope > 0.f && a.out_slope <= 1.f) || !(a.res_inv >= 1.f)) return cudaErrorInvalidValue;
-  const RbPlan pl = rb_plan(MB, CG, sh.nbox * sh.box_rows, sh.span2, a.ntaps1 + a.ntaps2, sh.nsl, sh.nxt);
+  const RbPlan pl = rb_plan(MB, CG, sh.nbox * sh.box_rows, sh.span2, a.ntaps1 + a.ntaps2, sh.nsl, sh.nxt, sh.lead);
   if ((size_t)pl.total > kRbMaxSmem) return cudaErrorInvalidConfiguration;
   CUtensorMap tm_x, tm_out, tm_last, tm_w1, tm_w2;
   if (!rb_map3(&tm_x, act, a.x, a.n_q, a.B, sh.box_rows)) return cudaErrorNotSupported;
@@ -544,7 +582,7 @@ cudaError_t rb_launch_t(const RbArgs& a, const RbShape& sh, ActType act, cudaStr
     if (!rb_map_w(&tm_w1, a.w1, (size_t)a.ntaps1 * kRbC * kRbRowB, box)) return cudaErrorNotSupported;
     if (!rb_map_w(&tm_w2, a.w2, (size_t)a.ntaps2 * kRbC * kRbRowB, box)) return cudaErrorNotSupported;
   } else { tm_w1 = tm_out; tm_w2 = tm_out; }
-  auto kern = resblock_tc_kernel<T, MB, CG>;
+  auto kern = resblock_tc_kernel<T, MB, CG, MODE>;
   constexpr int kMaxDev = 32;
   static int configured_dev[kMaxDev] = {0};
   int dev = 0; cudaGetDevice(&dev);
@@ -609,13 +647,15 @@ cudaError_t launch_resblock_tc(const RbArgs& a, ActType act, cudaStream_t s) {
   RbShape sh;
   if (!rb_choose(a, &sh)) return cudaErrorInvalidValue;
   if (sh.cg != a.cg) return cudaErrorInvalidValue;          // weights were packed for the other CTA grouping
-#define RB_DISPATCH(TT)                                                              \
-  if (sh.mb == 2 && sh.cg == 2) return rb_launch_t<TT, 2, 2>(a, sh, act, s);         \
-  if (sh.mb == 1 && sh.cg == 2) return rb_launch_t<TT, 1, 2>(a, sh, act, s);         \
-  if (sh.mb == 2 && sh.cg == 1) return rb_launch_t<TT, 2, 1>(a, sh, act, s);         \
-  if (sh.mb == 1 && sh.cg == 1) return rb_launch_t<TT, 1, 1>(a, sh, act, s);
-  if (act == ACT_F16) { RB_DISPATCH(__half) }
-  if (act == ACT_BF16) { RB_DISPATCH(__nv_bfloat16) }
+#define RB_DISPATCH(TT, MODE)                                                              \
+  if (sh.mb == 2 && sh.cg == 2) return rb_launch_t<TT, 2, 2, MODE>(a, sh, act, s);         \
+  if (sh.mb == 1 && sh.cg == 2) return rb_launch_t<TT, 1, 2, MODE>(a, sh, act, s);         \
+  if (sh.mb == 2 && sh.cg == 1) return rb_launch_t<TT, 2, 1, MODE>(a, sh, act, s);         \
+  if (sh.mb == 1 && sh.cg == 1) return rb_launch_t<TT, 1, 1, MODE>(a, sh, act, s);
+  if (act == ACT_F16 && a.mode == 1) { RB_DISPATCH(__half, 1) }
+  if (act == ACT_F16 && a.mode == 2) { RB_DISPATCH(__half, 2) }
+  if (act == ACT_BF16 && a.mode == 1) { RB_DISPATCH(__nv_bfloat16, 1) }
+  if (act == ACT_BF16 && a.mode == 2) { RB_DISPATCH(__nv_bfloat16, 2) }
 #undef RB_DISPATCH
   return cudaErrorInvalidValue;
 }

@@ -347,6 +347,13 @@ class Generator:
         _lib.check(self._lib.hfg_stage_times_ms(self._handle, buf, C.byref(n)), self._handle)
         return [float(buf[i]) for i in range(n.value)]
 
+    def stage_launches(self):
+        """Kernels launched per measurement stage ([conv_pre, stage 0.., conv_post]) by the last forward."""
+        buf = (C.c_int * 16)()
+        n = C.c_int(16)
+        _lib.check(self._lib.hfg_stage_launches(self._handle, buf, C.byref(n)), self._handle)
+        return [int(buf[i]) for i in range(n.value)]
+
     def summary(self, print_fn=print) -> None:
         """Layer table (the Keras `.summary()` surface touched by reference gan.py:192)."""
         print_fn(f"Generator(resblock={self.hparams.resblock!r}, precision={self.precision}, compat={self.compat})")

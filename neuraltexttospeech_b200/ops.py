@@ -43,9 +43,10 @@ def tapped_conv(x, w: np.ndarray, bias: np.ndarray, tap_off: Sequence[int], *, e
 
 
 def resblock_fused(x, w1: np.ndarray, b1: np.ndarray, off1: Sequence[int], w2: np.ndarray, b2: np.ndarray, off2: Sequence[int], *,
-                   mid_slope: float = 0.1, res_inv: float = 10.0, res2=None, out_scale: float = 1.0, out_slope: float = 0.1, out=None):
-    """One fused ResBlock1 iteration (hfg_op_resblock_fused): x torch CUDA [B, rows, 64] float16 / bfloat16 stored
-    activated; w1 / w2 fp32 [ntaps, 64, 64]."""
+                   mode: int = 1, mid_slope: float = 0.1, res_inv: float = 10.0, res2=None, out_scale: float = 1.0,
+                   out_slope: float = 0.1, out=None):
+    """One fused ResBlock1 iteration (mode 1) or whole ResBlock2 (mode 2) (hfg_op_resblock_fused): x torch CUDA
+    [B, rows, 64] float16 / bfloat16 stored activated; w1 / w2 fp32 [ntaps, 64, 64]."""
     import torch
     lib = _lib.load()
     act = {torch.float16: 1, torch.bfloat16: 2}[x.dtype]
@@ -59,7 +60,7 @@ def resblock_fused(x, w1: np.ndarray, b1: np.ndarray, off1: Sequence[int], w2: n
         out = torch.zeros_like(x)
     o1 = (C.c_int * len(off1))(*[int(t) for t in off1]); o2 = (C.c_int * len(off2))(*[int(t) for t in off2])
     ptr = lambda t: C.c_void_p(t.data_ptr()) if t is not None else None
-    rc = lib.hfg_op_resblock_fused(act, ptr(x), B, rows, w1.ctypes.data_as(C.c_void_p), b1.ctypes.data_as(C.c_void_p), len(off1), o1,
+    rc = lib.hfg_op_resblock_fused(act, int(mode), ptr(x), B, rows, w1.ctypes.data_as(C.c_void_p), b1.ctypes.data_as(C.c_void_p), len(off1), o1,
                                    w2.ctypes.data_as(C.c_void_p), b2.ctypes.data_as(C.c_void_p), len(off2), o2,
                                    float(mid_slope), float(res_inv), ptr(res2), float(out_scale), float(out_slope), ptr(out),
                                    C.c_void_p(torch.cuda.current_stream(x.device).cuda_stream))

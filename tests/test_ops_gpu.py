@@ -205,3 +205,50 @@ def test_resblock_fused_matches_two_convs(k, d, f, B, rows, dtype):
     resblock_fused(xt, w1, b1, off1, w2, b2, off2, res2=s2b, out_slope=1.0, out=s2b)
     ref = ref_resblock_fused(xq, w1q, b1, off1, w2q, b2, off2, 0.1, 10.0, s2.float().cpu().numpy(), 1.0, 1.0, tdt)
     assert np.abs(s2b.float().cpu().numpy() - ref).max() <= 2 * tol
+
+
+RB2_CASES = [  # (k, (d_a, d_b), fold, B, rows): the ResBlock2s of V3 stages 1-2 (C*fold = 64)
+    (3, (1, 2), 1, 2, 700),      # causal c_a (k=3, d=1), "same" c_b
+    (5, (2, 6), 1, 1, 1500),
+    (7, (3, 12), 1, 2, 900),     # span of c_b = 72 rows: 184 valid rows per 256-row tile
+    (7, (3, 12), 2, 1, 1111),    # C = 32 folded by 2
+    (3, (1, 2), 2, 3, 130),
+]
+
+
+@pytest.mark.parametrize("k,ds,f,B,rows", RB2_CASES)
+def test_resblock2_fused_matches_two_convs_with_skips(k, ds, f, B, rows):
+    """mode 2 of the fused kernel = a whole ResBlock2 (reference model.py:106-112)."""
+    import torch
+    from neuraltexttospeech_b200.ops import resblock_fused
+    from neuraltexttospeech_b200.utils import get_padding
+    rng = np.random.default_rng(k * 100 + ds[1] * 10 + f)
+    tdt = torch.float16
+
+    def pad_left(kk, dd):
+        return dd * (kk - 1) if get_padding(kk, dd) == "causal" else dd * (kk - 1) // 2
+
+    off1, off2 = folded_taps(k, ds[0], pad_left(k, ds[0]), f), folded_taps(k, ds[1], pad_left(k, ds[1]), f)
+    x = rng.standard_normal((B, rows, 64)).astype(np.float32)
+    xt = torch.from_numpy(lrelu(x, 0.1)).cuda().to(tdt)
+    xq = xt.float().cpu().numpy()
+    w1 = (rng.standard_normal((len(off1), 64, 64)) / np.sqrt(64 * len(off1))).astype(np.float32)
+    w2 = (rng.standard_normal((len(off2), 64, 64)) / np.sqrt(64 * len(off2))).astype(np.float32)
+    b1 = rng.uniform(-0.1, 0.1, 64).astype(np.float32); b2 = rng.uniform(-0.1, 0.1, 64).astype(np.float32)
+    w1q = torch.from_numpy(w1).to(tdt).float().numpy(); w2q = torch.from_numpy(w2).to(tdt).float().numpy()
+    s2 = torch.from_numpy(rng.standard_normal((B, rows, 64)).astype(np.float32)).cuda().to(tdt)
+
+    def ref(res2, out_scale, out_slope):
+        x1 = ref_tapped_conv(xq, w1q, b1, off1) + np.where(xq >= 0, xq, xq * np.float32(10.0))
+        a1 = torch.from_numpy(np.where(x1 >= 0, x1, x1 * 0.1).astype(np.float32)).to(tdt).float().numpy()   # 16-bit xt tile
+        v = ref_tapped_conv(a1, w2q, b2, off2) + np.where(a1 >= 0, a1, a1 * np.float32(10.0))              # x1 as stored in the tile
+        if res2 is not None:
+            v += res2
+        v *= out_scale
+        return np.where(v >= 0, v, v * out_slope)
+
+    out = resblock_fused(xt, w1, b1, off1, w2, b2, off2, mode=2).float().cpu().numpy()
+    err = np.abs(out - ref(None, 1.0, 0.1))
+    assert err.max() <= 8e-3, (err.max(), np.unravel_index(err.argmax(), err.shape))
+    out = resblock_fused(xt, w1, b1, off1, w2, b2, off2, mode=2, res2=s2, out_scale=1.0 / 3, out_slope=0.3).float().cpu().numpy()
+    assert np.abs(out - ref(s2.float().cpu().numpy(), 1.0 / 3, 0.3)).max() <= 8e-3
