@@ -192,7 +192,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="v1_b64x10s", choices=sorted(CONFIGS))
-    ap.add_argument("--precision", default="fp16", choices=["fp32", "fp16", "bf16"])
+    ap.add_argument("--precision", default="fp16", choices=["fp32", "fp16", "bf16", "tf32"])
     ap.add_argument("--micro-batch", type=int, default=0, help="utterances per forward; 0 = the library's own rule")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -349,11 +349,14 @@ def main():
 
     if rank == 0:
         pk = peaks()
-        act_b = 2 if args.precision != "fp32" else 4
+        act_b = 2 if args.precision in ("fp16", "bf16") else 4
         flops = 2.0 * count_macs_per_frame(h) * T * B
         bytes_boundary = boundary_bytes_per_frame(h, act_b) * T * B
         tensor_bound = args.precision != "fp32"
         p_tensor, bw = pk["tflops_sustained"] * 1e12, pk["hbm_gbs"] * 1e9
+        if args.precision == "tf32":          # no measured TF32 GEMM peak on this pool: half of the measured bf16 peak (the nominal ratio)
+            p_tensor *= 0.5
+            pk = dict(pk, tflops_sustained=pk["tflops_sustained"] * 0.5, source=pk["source"] + "; TF32 = 0.5 x measured bf16 (nominal ratio, not measured)")
         # per-stage roofline: t_roof = max(F / P_tensor, B / BW_hbm) per forward of `mb` utterances
         stages, t_roof_sum = [], 0.0
         for w, ms, nl in zip(per_stage_work(h, act_b), stage_ms, stage_launches):
@@ -380,7 +383,8 @@ def main():
             "metric": metric_name(version), "value": world * audio_s_per_step / (dev_ms / 1000), "unit": "audio-s/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms, "higher_is_better": True,
             "scaling": "strong" if strong else "weak", "vs_baseline": None,
-            "dtype": {"fp16": "fp16 (fp32 accumulate)", "bf16": "bf16 (fp32 accumulate)", "fp32": "fp32"}[args.precision],
+            "dtype": {"fp16": "fp16 (fp32 accumulate)", "bf16": "bf16 (fp32 accumulate)", "fp32": "fp32",
+                      "tf32": "tf32 operands, fp32 storage (fp32 accumulate)"}[args.precision],
             "data": "synthetic",
             "config": {"workload": args.config, "generator": f"config_v{version}.json", "per_gpu_batch": B, "frames": T,
                        "samples_per_utterance": L, "micro_batch": mb, "weights": "random-init (Glorot-uniform v, g=||v||, b=0)",

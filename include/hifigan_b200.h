@@ -41,7 +41,9 @@ typedef enum {
 typedef enum {
   HFG_PRECISION_FP32 = 0, /* fp32 FFMA validation mode: <=1e-5 of the fp32 reference    */
   HFG_PRECISION_FP16 = 1, /* tcgen05 kind::f16, fp16 operands+storage, fp32 accumulate  */
-  HFG_PRECISION_BF16 = 2  /* tcgen05 kind::f16, bf16 operands+storage, fp32 accumulate  */
+  HFG_PRECISION_BF16 = 2, /* tcgen05 kind::f16, bf16 operands+storage, fp32 accumulate  */
+  HFG_PRECISION_TF32 = 3  /* tcgen05 kind::tf32, fp32 storage (operands rounded to TF32), fp32 accumulate: fp32 range,
+                             meets the tensor-core tolerance (<= 2e-3 max-abs, >= 40 dB) like fp16      */
 } hfg_precision;
 
 /* POD mirror of the hparams fields Generator.__init__ reads

@@ -15,7 +15,7 @@ HFG_MAX_KERNELS = 8
 HFG_MAX_DILATIONS = 4
 
 HFG_ERR_INVALID, HFG_ERR_STATE, HFG_ERR_CUDA, HFG_ERR_NOMEM, HFG_ERR_UNSUPPORTED = -1, -2, -3, -4, -5
-PRECISIONS = {"fp32": 0, "fp16": 1, "bf16": 2}
+PRECISIONS = {"fp32": 0, "fp16": 1, "bf16": 2, "tf32": 3}
 
 
 class HfgConfig(C.Structure):
@@ -96,6 +96,15 @@ def load():
     # file lock, the other ranks of a torchrun launch wait for it.  Without nvcc (a box that only received the prebuilt
     # library) the existing binary is used as shipped.  There is never a fallback to another implementation.
     from . import build as _build
+    alt = os.environ.get("HFG_LIB")          # A/B experiments: a library built elsewhere (tools/build_variant.py); same ABI, no digest check
+    if alt:
+        lib = C.CDLL(alt)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+        return lib
     stale = not os.path.exists(LIB_PATH)
     if not stale and _build.have_nvcc():
         stale = not _build.is_current()

@@ -80,6 +80,7 @@ struct hfg_ctx {
   int total_up = 1;
   bool finalized = false;
   int precision = HFG_PRECISION_FP32;
+  bool tf32 = false;            // precision "tf32": fp32 storage (act == ACT_F32), layers on the kind::tf32 tensor-core kernel
   ActType act = ACT_F32;
   std::string err;
   long long launches = 0;
@@ -411,7 +412,7 @@ struct Runner {
   // persistent tcgen05 kernel: the whole layer (all phases of a transposed conv) in one launch; x is
   // stored already activated (conv_tc.cu), res is stored activated with slope 1/res_inv
   void conv_tc(const Layer& L, const void* x, int x_rows, void* out, const void* res, float res_inv,
-               const void* res2, float out_scale, float out_slope, float* post_out = nullptr, int16_t* post_pcm = nullptr) {
+               const void* res2, float out_scale, float out_slope, float* post_out = nullptr, int16_t* post_pcm = nullptr, bool raw_out = false) {
     if (status != cudaSuccess) return;
     const int u = L.u_k, rows = x_rows / L.fold_in;      // kernel-view rows (time folding, see Layer)
     TcArgs a{};
@@ -427,7 +428,8 @@ struct Runner {
       a.var[p].ntaps = ph.ntaps; a.var[p].out_off = p;
       for (int j = 0; j < ph.ntaps; ++j) a.var[p].tap_off[j] = ph.tap_off[j];
     }
-    status = launch_conv_tc(a, h->act, s, nullptr);
+    a.raw_out = raw_out ? 1 : 0;
+    status = h->tf32 ? launch_conv_tf32(a, s) : launch_conv_tc(a, h->act, s, nullptr);
     h->launches++;
   }
 
@@ -468,8 +470,8 @@ struct Runner {
     if (L.use_tc) {
       const float ri = 1.0f / slope_of_res;
       if (nk == 1) conv_tc(L, x, x_rows, out, res, ri, nullptr, 1.0f, os);
-      else if (j == 0) conv_tc(L, x, x_rows, sum, res, ri, nullptr, 1.0f, 1.0f);
-      else if (j < nk - 1) conv_tc(L, x, x_rows, sum, res, ri, sum, 1.0f, 1.0f);
+      else if (j == 0) conv_tc(L, x, x_rows, sum, res, ri, nullptr, 1.0f, 1.0f, nullptr, nullptr, true);
+      else if (j < nk - 1) conv_tc(L, x, x_rows, sum, res, ri, sum, 1.0f, 1.0f, nullptr, nullptr, true);
       else conv_tc(L, x, x_rows, out, res, ri, sum, 1.0f / (float)nk, os);
     } else {
       const int mode = nk == 1 ? MRF_NONE : (j == 0 ? MRF_FIRST : (j == nk - 1 ? MRF_FINAL : MRF_ADD));
@@ -692,13 +694,14 @@ int hfg_set_weight(hfg_handle h, const char* name, const float* host, const int6
 
 int hfg_finalize_weights(hfg_handle h, int precision) {
   if (!h) return HFG_ERR_INVALID;
-  if (precision < 0 || precision > 2) return fail(h, HFG_ERR_INVALID, "precision must be 0 (fp32), 1 (fp16) or 2 (bf16)");
+  if (precision < 0 || precision > 3) return fail(h, HFG_ERR_INVALID, "precision must be 0 (fp32), 1 (fp16), 2 (bf16) or 3 (tf32)");
   for (const Layer& L : h->layers)
     if (!L.has_v || !L.has_g || !L.has_b) return fail(h, HFG_ERR_STATE, "layer '%s' is missing %s", L.name.c_str(), !L.has_v ? "v" : (!L.has_g ? "g" : "b"));
   CUDA_TRY(h, cudaSetDevice(h->device));
   clear_graphs(h);                                     // weight pointers are baked into captured launches
   h->precision = precision;
-  h->act = precision == HFG_PRECISION_FP32 ? ACT_F32 : (precision == HFG_PRECISION_FP16 ? ACT_F16 : ACT_BF16);
+  h->tf32 = precision == HFG_PRECISION_TF32;
+  h->act = (precision == HFG_PRECISION_FP32 || h->tf32) ? ACT_F32 : (precision == HFG_PRECISION_FP16 ? ACT_F16 : ACT_BF16);
   const hfg_config& c = h->cfg;
   // run_forward treats the resblock convs of a stage as one engine (pre-activated 16-bit storage and the 16-bit running
   // MRF sum on the tcgen05 path, raw storage and the fp32 accumulator on the direct path).  A non-stock config can have
@@ -713,12 +716,13 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
     const bool is_post = (L.name == "conv_post"), is_pre = (L.name == "conv_pre");
     bool ok;
     const int pl = (is_pre || is_post) ? (L.dil * (L.k - 1)) / 2 : (L.transposed ? 0 : conv_pad_left(L.k, L.dil, c.compat, &ok));
-    const bool tc_mode = h->act != ACT_F32 && !h->force_ffma && !demote[li];
+    const bool tf32 = h->tf32;
+    const bool tc_mode = (h->act != ACT_F32 || tf32) && !h->force_ffma && !demote[li];
     // fold factor of a [rows, C] tensor on the tcgen05 path: C*f = 16 when C < 16 and the row count is divisible
     auto fold_of = [&](int C, int rate) { return (tc_mode && C < 16 && 16 % C == 0 && rate % (16 / C) == 0) ? 16 / C : 1; };
     // conv_post rides the tcgen05 kernel (16-column tile, tanh/fp32 epilogue) when its input is stored pre-activated,
     // i.e. when the last stage's resblocks run on the tcgen05 kernel too (layers are finalised in call order)
-    const bool post_tc = is_post && tc_mode && li > 0 && h->layers[li - 1].use_tc;
+    const bool post_tc = is_post && tc_mode && !tf32 && li > 0 && h->layers[li - 1].use_tc;   // TF32: conv_post stays on its direct kernel
     KView V;
     L.use_tc = false;
     if (tc_mode && (!is_post || post_tc)) {
@@ -743,7 +747,7 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
         }
         fi = fo = best_f;
       }
-      if (!L.transposed && !is_pre && !is_post && L.cin == L.cout && h->auto_fold) {
+      if (!L.transposed && !is_pre && !is_post && L.cin == L.cout && h->auto_fold && !tf32) {
         // ResBlock convs: folding is free in memory (bit-identical tensor), so pick the fold factor with the lowest
         // modelled MMA + operand-staging time per output row (see fold_cost)
         double best = fold_cost(L, pl, fi, nullptr);
@@ -755,8 +759,9 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
         }
       }
       V = build_view(L, w, pl, fi, fo, post_tc);
-      const int cin_mma = is_pre ? (int)align_up((size_t)V.cin_k, 64) : V.cin_k;
-      L.use_tc = (int)V.off.size() <= kMaxVariants && V.max_taps() <= kMaxTaps && tc_supported(cin_mma, V.cout_k, V.max_taps(), V.span());
+      const int cin_mma = is_pre ? (int)align_up((size_t)V.cin_k, tf32 ? 32 : 64) : V.cin_k;
+      L.use_tc = (int)V.off.size() <= kMaxVariants && V.max_taps() <= kMaxTaps &&
+                 (tf32 ? tf32_supported(cin_mma, V.cout_k, V.max_taps(), V.span()) : tc_supported(cin_mma, V.cout_k, V.max_taps(), V.span()));
       if (L.use_tc) { L.cin_pad = cin_mma; L.fold_in = fi; L.fold_out = fo; }
     }
     if (!L.use_tc) {                                     // direct kernels: unfolded view
@@ -779,9 +784,15 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
     if (L.use_tc) {
       const int span = V.span();
       size_t total = 0;
-      for (Phase& ph : L.phases) { ph.wpk_off = total; total += align_up(tc_packed_weight_bytes(L.cin_pad, L.cout_k, ph.ntaps), 256); }
+      for (Phase& ph : L.phases) {
+        ph.wpk_off = total;
+        total += align_up(tf32 ? tf32_packed_weight_bytes(L.cin_pad, L.cout_k, ph.ntaps) : tc_packed_weight_bytes(L.cin_pad, L.cout_k, ph.ntaps), 256);
+      }
       std::vector<char> pk(total);
-      for (Phase& ph : L.phases) tc_pack_weights(&w32[ph.w32_off], ph.ntaps, L.cin_pad, L.cout_k, span, h->act, pk.data() + ph.wpk_off);
+      for (Phase& ph : L.phases) {
+        if (tf32) tf32_pack_weights(&w32[ph.w32_off], ph.ntaps, L.cin_pad, L.cout_k, pk.data() + ph.wpk_off);
+        else tc_pack_weights(&w32[ph.w32_off], ph.ntaps, L.cin_pad, L.cout_k, span, h->act, pk.data() + ph.wpk_off);
+      }
       L.wpk_bytes = total;
       CUDA_TRY(h, cudaMalloc(&L.d_wpk, total));
       CUDA_TRY(h, cudaMemcpy(L.d_wpk, pk.data(), total, cudaMemcpyHostToDevice));
@@ -902,11 +913,11 @@ int hfg_workspace_bytes(hfg_handle h, int B, int T, size_t* out) {
 // One micro-batch of the host path on h->stream.  Launch-bound forwards (few frames) are replayed from a CUDA graph
 // captured on the second use of the same (buffers, shape): 79 launches + 230 tensor-map encodes become one graph launch.
 static int forward_maybe_graph(hfg_ctx* h, const float* mel, int nb, int T, char* dev_out, int sample_bytes, char* ws, size_t ws_bytes,
-                               cudaStream_t launch) {
+                               cudaStream_t launch, bool own_stream) {
   float* audio = sample_bytes == 4 ? (float*)dev_out : nullptr;
   int16_t* pcm = sample_bytes == 2 ? (int16_t*)dev_out : nullptr;
   bool eligible = h->use_graphs && !h->stage_timing && (long long)nb * T <= 8192;
-  if (eligible && launch != h->stream) {               // a caller's stream: leave it alone while the caller captures it
+  if (eligible && !own_stream) {                       // a caller's stream: leave it alone while the caller captures it
     cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(launch, &st) != cudaSuccess) { cudaGetLastError(); eligible = false; }
     else if (st != cudaStreamCaptureStatusNone) eligible = false;
@@ -929,7 +940,7 @@ static int forward_maybe_graph(hfg_ctx* h, const float* mel, int nb, int T, char
   // capture on an internal stream (a caller's stream may be the legacy default stream, which cannot be captured);
   // the instantiated graph is then launched into the caller's stream like any other work
   cudaStream_t cap = launch;
-  if (launch != h->stream) {
+  if (!own_stream) {
     if (!h->cap_stream) CUDA_TRY(h, cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
     cap = h->cap_stream;
   }
@@ -970,7 +981,7 @@ static int forward_device(hfg_handle h, const float* mel_dev, int B, int T, floa
   // launch-bound forwards are replayed from a CUDA graph captured on the second call with the same buffers and shape
   // (tensor-map encodes and ~60-80 launches become one graph launch into the caller's stream)
   return forward_maybe_graph(h, mel_dev, B, T, audio_dev ? (char*)audio_dev : (char*)pcm_dev, audio_dev ? 4 : 2, ws,
-                             workspace_bytes - (size_t)(ws - (char*)workspace_dev), (cudaStream_t)stream);
+                             workspace_bytes - (size_t)(ws - (char*)workspace_dev), (cudaStream_t)stream, false);
 }
 
 int hfg_forward(hfg_handle h, const float* mel_dev, int B, int T, float* audio_dev, void* workspace_dev,
@@ -1111,7 +1122,7 @@ static int forward_host(hfg_handle h, const float* mel_host, int B, int T, void*
     const int nb = parts[i], b0 = starts[i];
     char* dev_out = (char*)h->d_audio + (size_t)b0 * aud_elems * sample_bytes;
     CUDA_TRY(h, cudaStreamWaitEvent(h->stream, h->copy_events[3 * i], 0));
-    int rc = forward_maybe_graph(h, h->d_mel + (size_t)b0 * mel_elems, nb, T, dev_out, sample_bytes, (char*)h->ws, h->ws_bytes, h->stream);
+    int rc = forward_maybe_graph(h, h->d_mel + (size_t)b0 * mel_elems, nb, T, dev_out, sample_bytes, (char*)h->ws, h->ws_bytes, h->stream, true);
     launches += h->launches; h->launches = 0;
     if (rc) { cudaStreamSynchronize(h->h2d_stream); cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->d2h_stream); return rc; }
     CUDA_TRY(h, cudaEventRecord(h->copy_events[3 * i + 1], h->stream));
@@ -1245,7 +1256,24 @@ int hfg_op_tapped_conv(int act, int engine, const void* x_dev, int B, int x_rows
   CUDA_TRY(nullptr, cudaMalloc((void**)&d_bias, bias.size() * 4));
   CUDA_TRY(nullptr, cudaMemcpy(d_bias, bias.data(), bias.size() * 4, cudaMemcpyHostToDevice));
   cudaError_t e;
-  if (engine == 1) {
+  if (engine == 2) {                                   // TF32 tensor-core kernel (fp32 storage)
+    if (act != ACT_F32 || in_slope != 1.0f || mrf_mode != MRF_NONE || !tf32_supported(c_in, c_out, ntaps, mx - mn)) {
+      cudaFree(d_bias);
+      return fail(nullptr, HFG_ERR_UNSUPPORTED, "tf32 kernel does not cover c_in=%d c_out=%d ntaps=%d span=%d act=%d", c_in, c_out, ntaps, mx - mn, act);
+    }
+    const size_t nb = align_up(tf32_packed_weight_bytes(c_in, c_out, ntaps), 256);
+    std::vector<char> pk(nb);
+    tf32_pack_weights(w_host, ntaps, c_in, c_out, pk.data());
+    CUDA_TRY(nullptr, cudaMalloc(&d_w, nb));
+    CUDA_TRY(nullptr, cudaMemcpy(d_w, pk.data(), nb, cudaMemcpyHostToDevice));
+    TcArgs t{};
+    t.x = x_dev; t.out = out_dev; t.res = res_dev; t.res2 = res2_dev; t.bias = d_bias;
+    t.B = B; t.x_rows = x_rows; t.n_q = x_rows; t.out_rows = x_rows * out_stride; t.out_stride = out_stride;
+    t.c_in = c_in; t.c_out = c_out; t.res_inv = res_inv; t.out_scale = out_scale; t.out_slope = out_slope;
+    t.nvar = 1; t.var[0].w = d_w; t.var[0].ntaps = ntaps; t.var[0].out_off = out_off;
+    for (int j = 0; j < ntaps; ++j) t.var[0].tap_off[j] = tap_off[j];
+    e = launch_conv_tf32(t, s);
+  } else if (engine == 1) {
     if (act == ACT_F32 || in_slope != 1.0f || mrf_mode != MRF_NONE || !tc_supported(c_in, c_out, ntaps, mx - mn)) {
       cudaFree(d_bias);
       return fail(nullptr, HFG_ERR_UNSUPPORTED, "tcgen05 kernel does not cover c_in=%d c_out=%d ntaps=%d span=%d act=%d in_slope=%g mrf_mode=%d",
@@ -1323,7 +1351,7 @@ int hfg_op_resblock_fused(int act, int mode, const void* x_dev, int B, int rows,
 
 #ifdef HFG_TC_TRACE
 // debug builds only (tools/trace_layer.py); not part of the C ABI
-void hfgdbg_set_trace(void* dev) { tc_set_trace((long long*)dev); }
+void hfgdbg_set_trace(void* dev) { tc_set_trace((long long*)dev); rb_set_trace((long long*)dev); }
 #endif
 
 int hfg_host_alloc(void** out, size_t bytes) {

@@ -106,6 +106,7 @@ struct TcArgs {
   float* post_out;      // conv_post mode (may be NULL): fp32 [B, n_q*post_f]; `out` is then only a scratch
                         // buffer of >= B*n_q*c_out 16-bit elements for the (unused) output tensor map
   int16_t* post_pcm;    // conv_post mode, when non-NULL: 16-bit PCM [B, n_q*post_f] instead of post_out
+  int raw_out;          // TF32 kernel only: 1 = store the result unrounded (the running MRF sum is never an MMA operand)
   const void* w_base;   // allocation holding every variant's packed weights (256-byte aligned; the CTA-pair
   size_t w_bytes;       // configurations read it through one TMA map), and its size (multiple of 256)
 };
@@ -120,6 +121,14 @@ void tc_pack_weights(const float* w, int ntaps, int c_in, int c_out, int span, A
 // returns cudaSuccess or an error; *msg (optional) receives a static description on failure
 cudaError_t launch_conv_tc(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out);
 void tc_set_trace(long long* dev);   // debug builds (-DHFG_TC_TRACE): device buffer of [6][64][8] clock stamps, see conv_tc.cu
+
+// ---------------------------------------------------------------- TF32 tensor-core kernel (conv_tf32.cu)
+// Same contract as launch_conv_tc (TcArgs; x / out / res / res2 are fp32, stored activated like the 16-bit path; no
+// conv_post mode): tcgen05.mma.kind::tf32, fp32 storage with stored activations rounded to TF32.
+bool tf32_supported(int c_in, int c_out, int ntaps, int span);
+size_t tf32_packed_weight_bytes(int c_in, int c_out, int ntaps);
+void tf32_pack_weights(const float* w, int ntaps, int c_in, int c_out, void* dst_host);
+cudaError_t launch_conv_tf32(const TcArgs& a, cudaStream_t s);
 
 // ---------------------------------------------------------------- fused ResBlock1 iteration (resblock_tc.cu)
 // One launch = conv1 (dilated) -> lrelu -> conv2 -> + x (reference model.py:71-80), 64 kernel-view channels per row
@@ -145,5 +154,6 @@ bool rb_supported(const RbArgs& a, int* cg_out);          // needs ntaps / offse
 size_t rb_packed_weight_bytes(int ntaps);
 void rb_pack_weights(const float* w, int ntaps, int cg, ActType act, void* dst_host);   // w: fp32 [ntaps][64][64]
 cudaError_t launch_resblock_tc(const RbArgs& a, ActType act, cudaStream_t s);
+void rb_set_trace(long long* dev);     // debug builds (-DHFG_TC_TRACE): [7 roles][64 tiles][8 events] clock stamps
 
 }  // namespace hfg

@@ -299,7 +299,6 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
         for (int mb = 0; mb < MB; ++mb, ++pcnt) {
           if ((int)(pcnt % (uint32_t)EG) != grp) continue;
           mbar_wait(&acc1_full[i & 1], (i >> 1) & 1);                 // conv1 of the tile complete (hence its slab landed)
-          if (rank == 0) mbar_wait(&slab_full[sbuf], (i / nsl) & 1);  // (already complete; the peer's bytes arrive on the leader's barrier)
           tc_fence_after();
           mbar_wait(&xt_free[xbuf], ((i / nxt) & 1) ^ 1);            // the tile's previous tenant has been stored
           mbar_wait(&acc2_free[i & 1], ((i >> 1) & 1) ^ 1);          // fin(i-2) has read acc2[i&1]
@@ -307,6 +306,7 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
           const int r = mb * 128 + er;                                // row of the CTA tile
           const int g = q0 + ka.min2 + r;                             // kernel-view row of this xt row (xt row 0 = q0 - h2)
           const bool inside = g >= 0 && g < ka.n_q;
+          const bool tile_inside = q0 + ka.min2 >= 0 && q0 + ka.min2 + MB * 128 <= ka.n_q;   // warp-uniform: no row of the tile needs zeroing
           // MODE 1: slab row of OUTPUT row r (skip connection of the iteration, goes into acc2);
           // MODE 2: slab row of XT row r (skip connection of the first conv, added before the activation)
           const int sr = MODE == 2 ? r - ka.min1 : r + halo;
@@ -344,7 +344,7 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
               for (int e = 0; e < 8; ++e) v[e] = lrelu_le1(v[e], mid_slope);
               uint4 u;
               u.x = H2<T>::down(v[0], v[1]); u.y = H2<T>::down(v[2], v[3]); u.z = H2<T>::down(v[4], v[5]); u.w = H2<T>::down(v[6], v[7]);
-              if (!inside) u = make_uint4(0u, 0u, 0u, 0u);           // conv2 sees zero padding outside the utterance
+              if (!tile_inside) { if (!inside) u = make_uint4(0u, 0u, 0u, 0u); }   // conv2 sees zero padding outside the utterance (edge tiles only)
               *reinterpret_cast<uint4*>(xrow + (((c0 / 8 + k) ^ (xr & 7)) * 16)) = u;
             }
             if (MODE == 1) {
@@ -381,11 +381,18 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
 #pragma unroll 1
         for (int mb = 0; mb < MB; ++mb, ++pcnt) {
           if ((int)(pcnt % (uint32_t)EG) != grp) continue;
-          mbar_wait(&acc2_full[i & 1], (i >> 1) & 1);                 // conv2 of the whole tile complete: xt rows are dead
-          tc_fence_after();
           const int r = mb * 128 + er;
           const int q = q0 + r;
           const bool has_res2 = ka.res2 != nullptr && r < ka.r2 && q < ka.n_q;
+          // the running MRF sum comes from global memory: request it before waiting for the accumulator
+          uint4 rr2[8];
+          if (has_res2) {
+            const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(ka.res2) + ((size_t)b * ka.n_q + q) * kRbC);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) rr2[k] = rp[k];
+          }
+          mbar_wait(&acc2_full[i & 1], (i >> 1) & 1);                 // conv2 of the whole tile complete: xt rows are dead
+          tc_fence_after();
           const int orr = MODE == 2 ? r + lead - ka.min2 : r;        // MODE 2: the row of x1 (second skip connection), reused for the output
           uint8_t* orow = xt + xbuf * pl.xt_bytes + orr * kRbRowB;
           const uint32_t t2 = tmem_base + lane_base + (2 * MB + (i & 1) * MB + mb) * kRbC;
@@ -393,12 +400,6 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
           for (int c0 = 0; c0 < kRbC; c0 += 32) {
             uint32_t acc[32];
             tmem_ld32(t2 + c0, acc);
-            uint4 rr2[4];
-            if (has_res2) {
-              const uint4* rp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(ka.res2) + ((size_t)b * ka.n_q + q) * kRbC + c0);
-#pragma unroll
-              for (int k = 0; k < 4; ++k) rr2[k] = rp[k];
-            }
             uint4 rx[4];
             if (MODE == 2) {
 #pragma unroll
@@ -421,10 +422,11 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
               }
               if (has_res2) {
                 float2 f;
-                f = H2<T>::up(rr2[k].x); v[0] += f.x; v[1] += f.y;
-                f = H2<T>::up(rr2[k].y); v[2] += f.x; v[3] += f.y;
-                f = H2<T>::up(rr2[k].z); v[4] += f.x; v[5] += f.y;
-                f = H2<T>::up(rr2[k].w); v[6] += f.x; v[7] += f.y;
+                const uint4 s4 = rr2[c0 / 8 + k];
+                f = H2<T>::up(s4.x); v[0] += f.x; v[1] += f.y;
+                f = H2<T>::up(s4.y); v[2] += f.x; v[3] += f.y;
+                f = H2<T>::up(s4.z); v[4] += f.x; v[5] += f.y;
+                f = H2<T>::up(s4.w); v[6] += f.x; v[7] += f.y;
               }
               if (osc != 1.0f) {
 #pragma unroll
@@ -612,6 +614,8 @@ cudaError_t rb_launch_t(const RbArgs& a, const RbShape& sh, ActType act, cudaStr
 }
 
 }  // namespace
+
+void rb_set_trace(long long*) {}      // (role tracing lives in the experiment branch of this file; see profiles/r2b_*)
 
 bool rb_supported(const RbArgs& a, int* cg_out) {
   RbShape s;

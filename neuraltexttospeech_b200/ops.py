@@ -33,7 +33,7 @@ def tapped_conv(x, w: np.ndarray, bias: np.ndarray, tap_off: Sequence[int], *, e
         out = torch.zeros((B, rows * out_stride, c_out), dtype=x.dtype, device=x.device)
     taps = (C.c_int * ntaps)(*[int(t) for t in tap_off])
     ptr = lambda t: C.c_void_p(t.data_ptr()) if t is not None else None
-    rc = lib.hfg_op_tapped_conv(act, {"ffma": 0, "tc": 1}[engine], ptr(x), B, rows, c_in,
+    rc = lib.hfg_op_tapped_conv(act, {"ffma": 0, "tc": 1, "tf32": 2}[engine], ptr(x), B, rows, c_in,
                                 w.ctypes.data_as(C.c_void_p), bias.ctypes.data_as(C.c_void_p), c_out, ntaps, taps,
                                 out_stride, out_off, float(in_slope), ptr(res), float(res_inv), ptr(res2),
                                 float(out_scale), float(out_slope), ptr(acc), int(mrf_mode), float(mrf_div), ptr(out),

@@ -252,3 +252,39 @@ def test_resblock2_fused_matches_two_convs_with_skips(k, ds, f, B, rows):
     assert err.max() <= 8e-3, (err.max(), np.unravel_index(err.argmax(), err.shape))
     out = resblock_fused(xt, w1, b1, off1, w2, b2, off2, mode=2, res2=s2, out_scale=1.0 / 3, out_slope=0.3).float().cpu().numpy()
     assert np.abs(out - ref(s2.float().cpu().numpy(), 1.0 / 3, 0.3)).max() <= 8e-3
+
+
+# ---------------------------------------------------------------- TF32 tensor-core kernel (conv_tf32.cu)
+def tf32_round(a):
+    u = np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+    u = (u + np.uint32(0x0FFF) + ((u >> np.uint32(13)) & np.uint32(1))) & np.uint32(0xFFFFE000)
+    return u.view(np.float32)
+
+
+TF32_SHAPES = [  # (c_in, c_out, taps, B, rows)
+    (32, 32, [-2, -1, 0], 2, 700),
+    (64, 64, [3 * j - 9 for j in range(7)], 2, 520),
+    (128, 128, [5 * j - 25 for j in range(11)], 1, 300),
+    (512, 256, [-1, 0], 1, 140),                         # one phase of ups[0], two N tiles
+    (96, 512, [j - 3 for j in range(7)], 1, 130),        # conv_pre: 80 mel channels padded to 96
+    (16, 16, [-1, 0, 1], 3, 260),                        # 64-byte swizzle rows
+    (8, 16, [0, 1], 2, 300),                             # 32-byte swizzle rows, K = 8 (one MMA per tap)
+    (128, 64, [-1, 0], 1, 600),
+]
+
+
+@pytest.mark.parametrize("cin,cout,taps,B,rows", TF32_SHAPES)
+def test_tapped_conv_tf32(cin, cout, taps, B, rows):
+    import torch
+    from neuraltexttospeech_b200.ops import tapped_conv
+    rng = np.random.default_rng(cin * 1000 + cout + len(taps))
+    x = tf32_round(lrelu(rng.standard_normal((B, rows, cin)).astype(np.float32), 0.1))     # stored activated, TF32-rounded
+    w = (rng.standard_normal((len(taps), cin, cout)) / np.sqrt(cin * len(taps))).astype(np.float32)
+    bias = rng.uniform(-0.1, 0.1, cout).astype(np.float32)
+    res = lrelu(rng.standard_normal((B, rows, cout)).astype(np.float32), 0.1)
+    res_raw = np.where(res >= 0, res, res * np.float32(10.0))
+    ref = lrelu(ref_tapped_conv(x, tf32_round(w), bias, taps, in_slope=1.0, res=res_raw), 0.3)
+    out = tapped_conv(torch.from_numpy(x).cuda(), w, bias, taps, engine="tf32", res=torch.from_numpy(res).cuda(), res_inv=10.0,
+                      out_slope=0.3).cpu().numpy()
+    assert np.abs(out - ref).max() <= 3e-3            # fp32 accumulate of exact TF32 products; the stored output is TF32-rounded
+    assert np.array_equal(out, tf32_round(out))       # ... to 10 mantissa bits
