@@ -13,9 +13,11 @@
 // A tile = (utterance b, R2 = MB*128 - span2 output rows).  Per tile:
 //   slab   x rows [q0 - h1 - h2, ...) (MB*128 + span1 rows; h = left halo, OOB rows zero = TF padding)  TMA -> smem ring
 //   c1     acc1[mb] (TMEM) = sum_taps slab[mb*128 + off1_j ..] . W1_j           tcgen05.mma, M = 128 (256 for a CTA pair)
-//   mid    acc1 -> +b1 -> zero outside the utterance (conv2 pads xt with zeros) -> lrelu -> 16-bit -> xt tile in smem,
+//   (both convs end with a "bias tap": one K = 16 MMA of a constant ones tile with the bias as hi + lo 16-bit rows, so the
+//    epilogues below carry no bias adds)
+//   mid    acc1 -> zero outside the utterance (conv2 pads xt with zeros) -> lrelu -> 16-bit -> xt tile in smem,
 //          written in the swizzled K-major layout the MMA reads (it is conv2's A operand);
-//          the skip connection: slab row -> unactivate -> +b2 -> fp32 -> tcgen05.st into acc2 (the accumulator of conv2
+//          the skip connection: slab row -> unactivate -> fp32 -> tcgen05.st into acc2 (the accumulator of conv2
 //          starts from the residual, so the slab slot is free again before conv2 even starts)
 //   c2     acc2[mb] += sum_taps xt[mb*128 + off2_j ..] . W2_j
 //   fin    acc2 -> (+ running MRF sum, * 1/num_kernels on the last resblock: model.py:161-167) -> lrelu for the consumer
@@ -65,7 +67,7 @@ __host__ __device__ inline RbPlan rb_plan(int mb, int cg, int slab_rows, int spa
   int off = nsl * p.slab_bytes;
   p.off_xt = off; off += nxt * p.xt_bytes;
   p.off_w = off; off += p.w_bytes;
-  p.off_bias = off; off += 2 * kRbC * 4;
+  p.off_bias = off; off += 4096 + 2 * (2 * (kRbC / cg) * 16);   // "ones" A tile [2 K-chunks][128 rows][16 B] + per conv a bias B tile [2][64/cg rows][16 B]
   p.off_bar = off; off += (2 * kRbMaxSl + 2 + 8 + kRbMaxXt + kRbMaxXt * 2) * 8 + 16;
   p.total = off;
   return p;
@@ -106,7 +108,11 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
   uint8_t* slab = smem;
   uint8_t* xt = smem + pl.off_xt;
   uint8_t* wsm = smem + pl.off_w;
-  float* bias_s = reinterpret_cast<float*>(smem + pl.off_bias);          // [0,64) conv1, [64,128) conv2
+  // Biases ride the tensor core: one extra K = 16 MMA per conv and block multiplies a constant A tile whose first two K
+  // columns are 1 with a B tile whose first two K rows hold the bias as hi + lo 16-bit parts (exact to ~2^-22): the
+  // epilogues carry no bias adds (64 FADD + 16 shared loads per 32 columns before).
+  uint8_t* ones_s = smem + pl.off_bias;
+  uint8_t* biasb_s = ones_s + 4096;                                      // conv1 tile, then conv2 tile (2 * NB * 16 bytes each)
   uint64_t* slab_full = reinterpret_cast<uint64_t*>(smem + pl.off_bar);
   uint64_t* slab_empty = slab_full + kRbMaxSl;
   uint64_t* w_full = slab_empty + kRbMaxSl;            // [2]: conv1 / conv2 weights landed
@@ -136,7 +142,25 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
     if (CG == 2) { tma_prefetch_desc(&tm_w1); tma_prefetch_desc(&tm_w2); }
   }
   if (warp == 2) { if (CG == 2) tmem_alloc2(tmem_slot, TMEM_COLS); else tmem_alloc(tmem_slot, TMEM_COLS); }
-  if (tid < 2 * kRbC) bias_s[tid] = tid < kRbC ? ka.bias1[tid] : ka.bias2[tid - kRbC];
+  {
+    // ones tile: element (row r, k) at chunk (k / 8) * 2048 + r * 16 + (k % 8) * 2; k = 0, 1 -> 1.0, everything else 0
+    const uint32_t one2 = std::is_same<T, __nv_bfloat16>::value ? 0x3F803F80u : 0x3C003C00u;
+    if (tid < 256) *reinterpret_cast<uint4*>(ones_s + tid * 16) = make_uint4(tid < 128 ? one2 : 0u, 0u, 0u, 0u);
+    // bias tiles: this CTA's NB output channels; element (k, n) at chunk (k / 8) * NB * 16 + n * 16 + (k % 8) * 2
+    if (tid >= 256 && tid < 256 + 2 * 2 * NB) {
+      const int e = tid - 256, c = e / (2 * NB), rem = e % (2 * NB), chunk = rem / NB, n = rem % NB;
+      uint4 u = make_uint4(0u, 0u, 0u, 0u);
+      if (chunk == 0) {
+        const float bv = (c == 0 ? ka.bias1 : ka.bias2)[(int)rank * NB + n];
+        float hi, lo;
+        if (std::is_same<T, __nv_bfloat16>::value) { hi = __bfloat162float(__float2bfloat16_rn(bv)); lo = bv - hi; }
+        else { hi = __half2float(__float2half_rn(bv)); lo = bv - hi; }
+        u.x = H2<T>::down(hi, lo);
+      }
+      *reinterpret_cast<uint4*>(biasb_s + c * (2 * NB * 16) + chunk * NB * 16 + n * 16) = u;
+    }
+    fence_proxy_async();                                                 // generic writes -> visible to the tensor core
+  }
   tc_fence_before();
   if (CG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
@@ -198,7 +222,7 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
       // ===================== MMA issuer (pair: leader only) =====================
       if (rank == 0 && my_tiles > 0) {
         const uint32_t slab_addr = smem_u32(slab), xt_addr = smem_u32(xt), w_addr = smem_u32(wsm);
-        auto issue = [&](uint32_t a_base, uint32_t w_base, const int* offs, int mn, int nt, uint32_t tacc, bool fresh) {   // mn: offset of smem row 0
+        auto issue = [&](uint32_t a_base, uint32_t w_base, const int* offs, int mn, int nt, uint32_t tacc, bool fresh, int bias_idx) {   // mn: offset of smem row 0
           if (elect_one()) {
 #pragma unroll 1
             for (int mb = 0; mb < MB; ++mb) {
@@ -216,6 +240,11 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
                 }
                 first = 0;
               }
+              // bias tap: acc += ones[128 x 16] . biasB[16 x 64]
+              const uint64_t oa = make_desc(smem_u32(ones_s), 2048u, 128u);
+              const uint64_t ob = make_desc(smem_u32(biasb_s) + (uint32_t)bias_idx * (2 * NB * 16), NB * 16, 128u);
+              if (CG == 2) umma_f16_2cta(tacc + mb * kRbC, oa, ob, IDESC, first ? 0u : 1u);
+              else umma_f16(tacc + mb * kRbC, oa, ob, IDESC, first ? 0u : 1u);
             }
           }
           __syncwarp();
@@ -228,14 +257,14 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
           const int pos = i % nsl;
           mbar_wait(&slab_full[pos], (i / nsl) & 1);
           tc_fence_after();
-          issue(slab_addr + pos * pl.slab_bytes, w_addr, ka.off1, ka.min1, ka.ntaps1, tmem_base + (i & 1) * (MB * kRbC), true);
+          issue(slab_addr + pos * pl.slab_bytes, w_addr, ka.off1, ka.min1, ka.ntaps1, tmem_base + (i & 1) * (MB * kRbC), true, 0);
           commit(&acc1_full[i & 1]);
         };
         auto conv2 = [&](int i) {
           mbar_wait(&mid_done[i & 1], (i >> 1) & 1);      // xt tile written, acc2 pre-loaded with the residual, acc1 drained
           tc_fence_after();
           issue(xt_addr + (i % nxt) * pl.xt_bytes, w_addr + ka.ntaps1 * TAP_BYTES, ka.off2, ka.min2 - lead, ka.ntaps2,
-                tmem_base + (2 * MB + (i & 1) * MB) * kRbC, MODE == 2);
+                tmem_base + (2 * MB + (i & 1) * MB) * kRbC, MODE == 2, 1);
           commit(&acc2_full[i & 1]);
         };
         mbar_wait(&w_full[0], 0);
@@ -323,16 +352,11 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
 #pragma unroll
             for (int k = 0; k < 4; ++k) rr[k] = *reinterpret_cast<const uint4*>(srow + (((c0 / 8 + k) ^ (sr & 7)) * 16));
             tmem_ld_wait();
-            const float4* b4 = reinterpret_cast<const float4*>(bias_s + c0);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               float v[8];
 #pragma unroll
-              for (int e = 0; e < 2; ++e) {
-                const float4 bb = b4[2 * k + e];
-                v[4 * e + 0] = __uint_as_float(acc[8 * k + 4 * e + 0]) + bb.x; v[4 * e + 1] = __uint_as_float(acc[8 * k + 4 * e + 1]) + bb.y;
-                v[4 * e + 2] = __uint_as_float(acc[8 * k + 4 * e + 2]) + bb.z; v[4 * e + 3] = __uint_as_float(acc[8 * k + 4 * e + 3]) + bb.w;
-              }
+              for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(acc[8 * k + e]);
               if (MODE == 2) {                                        // x1 = c_a(lrelu(x)) + x   (model.py:108-111)
                 float2 f;
                 f = H2<T>::up(rr[k].x); v[0] += lrelu_ge1(f.x, res_inv); v[1] += lrelu_ge1(f.y, res_inv);
@@ -350,14 +374,13 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
             if (MODE == 1) {
               // skip connection (model.py:79): x is stored activated; acc2 starts from unact(x) + b2
               uint32_t init[32];
-              const float4* c4 = reinterpret_cast<const float4*>(bias_s + kRbC + c0);
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
-                float2 f; const float4 ba = c4[2 * k], bb = c4[2 * k + 1];
-                f = H2<T>::up(rr[k].x); init[8 * k + 0] = __float_as_uint(lrelu_ge1(f.x, res_inv) + ba.x); init[8 * k + 1] = __float_as_uint(lrelu_ge1(f.y, res_inv) + ba.y);
-                f = H2<T>::up(rr[k].y); init[8 * k + 2] = __float_as_uint(lrelu_ge1(f.x, res_inv) + ba.z); init[8 * k + 3] = __float_as_uint(lrelu_ge1(f.y, res_inv) + ba.w);
-                f = H2<T>::up(rr[k].z); init[8 * k + 4] = __float_as_uint(lrelu_ge1(f.x, res_inv) + bb.x); init[8 * k + 5] = __float_as_uint(lrelu_ge1(f.y, res_inv) + bb.y);
-                f = H2<T>::up(rr[k].w); init[8 * k + 6] = __float_as_uint(lrelu_ge1(f.x, res_inv) + bb.z); init[8 * k + 7] = __float_as_uint(lrelu_ge1(f.y, res_inv) + bb.w);
+                float2 f;
+                f = H2<T>::up(rr[k].x); init[8 * k + 0] = __float_as_uint(lrelu_ge1(f.x, res_inv)); init[8 * k + 1] = __float_as_uint(lrelu_ge1(f.y, res_inv));
+                f = H2<T>::up(rr[k].y); init[8 * k + 2] = __float_as_uint(lrelu_ge1(f.x, res_inv)); init[8 * k + 3] = __float_as_uint(lrelu_ge1(f.y, res_inv));
+                f = H2<T>::up(rr[k].z); init[8 * k + 4] = __float_as_uint(lrelu_ge1(f.x, res_inv)); init[8 * k + 5] = __float_as_uint(lrelu_ge1(f.y, res_inv));
+                f = H2<T>::up(rr[k].w); init[8 * k + 6] = __float_as_uint(lrelu_ge1(f.x, res_inv)); init[8 * k + 7] = __float_as_uint(lrelu_ge1(f.y, res_inv));
               }
               tmem_st32(t2 + c0, init);
             }
@@ -412,13 +435,12 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
 #pragma unroll
               for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(acc[8 * k + e]);
               if (MODE == 2) {                                        // x2 = c_b(lrelu(x1)) + x1, x1 recovered from the 16-bit xt tile
-                const float4 ba = *reinterpret_cast<const float4*>(bias_s + kRbC + c0 + 8 * k), bb = *reinterpret_cast<const float4*>(bias_s + kRbC + c0 + 8 * k + 4);
                 const float xi = ka.xt_inv;
                 float2 f;
-                f = H2<T>::up(rx[k].x); v[0] += lrelu_ge1(f.x, xi) + ba.x; v[1] += lrelu_ge1(f.y, xi) + ba.y;
-                f = H2<T>::up(rx[k].y); v[2] += lrelu_ge1(f.x, xi) + ba.z; v[3] += lrelu_ge1(f.y, xi) + ba.w;
-                f = H2<T>::up(rx[k].z); v[4] += lrelu_ge1(f.x, xi) + bb.x; v[5] += lrelu_ge1(f.y, xi) + bb.y;
-                f = H2<T>::up(rx[k].w); v[6] += lrelu_ge1(f.x, xi) + bb.z; v[7] += lrelu_ge1(f.y, xi) + bb.w;
+                f = H2<T>::up(rx[k].x); v[0] += lrelu_ge1(f.x, xi); v[1] += lrelu_ge1(f.y, xi);
+                f = H2<T>::up(rx[k].y); v[2] += lrelu_ge1(f.x, xi); v[3] += lrelu_ge1(f.y, xi);
+                f = H2<T>::up(rx[k].z); v[4] += lrelu_ge1(f.x, xi); v[5] += lrelu_ge1(f.y, xi);
+                f = H2<T>::up(rx[k].w); v[6] += lrelu_ge1(f.x, xi); v[7] += lrelu_ge1(f.y, xi);
               }
               if (has_res2) {
                 float2 f;

@@ -500,3 +500,66 @@ def test_host_path_tapered_micro_batches_are_bit_identical(gens):
     finally:
         g.set_option("micro_batch", 0)
     assert np.array_equal(g.synthesize_pcm16(mel), g.synthesize_pcm16(torch.from_numpy(mel).cuda()).cpu().numpy())
+
+
+@pytest.mark.parametrize("v", "123")
+@pytest.mark.parametrize("precision", ["fp16", "tf32", "fp32"])
+def test_guard_bands_around_caller_buffers_stay_intact(v, precision):
+    """compute-sanitizer is closed on this GPU pool (profiles/r2b_sanitizer_closed.txt), so out-of-bounds WRITES are caught
+    here instead: mel, audio / PCM and workspace live inside larger allocations whose margins hold a sentinel; after the
+    forward (device-pointer path, a batch / length that leaves ragged last tiles in every stage) the margins must be intact
+    and the result must equal the ordinary call."""
+    import ctypes as C
+    import torch
+    from neuraltexttospeech_b200 import _lib
+    h = HParams.builtin(v)
+    g = Generator(h, precision=precision).load_weights(synthetic_weights(h, "B"))
+    B, T = 3, 19
+    mel = synthetic_mel(B, T, h.num_mels, seed=int(v))
+    want = g(torch.from_numpy(mel).cuda()).cpu().numpy()
+    want_pcm = g.synthesize_pcm16(torch.from_numpy(mel).cuda()).cpu().numpy()
+    G = 1 << 18                                                   # guard band: 256 Ki elements on either side
+    L = T * 256
+
+    def guarded(n, dtype, fill):
+        buf = torch.full((n + 2 * G,), fill, dtype=dtype, device="cuda")
+        return buf, buf[G:G + n]
+
+    ws_bytes = g.workspace_bytes(B, T)
+    mel_buf, mel_in = guarded(B * T * h.num_mels, torch.float32, 7.0)
+    mel_in.copy_(torch.from_numpy(mel).reshape(-1))
+    out_buf, out = guarded(B * L, torch.float32, 123.0)
+    pcm_buf, pcm = guarded(B * L, torch.int16, 12345)
+    ws_buf, ws = guarded(ws_bytes, torch.uint8, 0xA5)
+    stream = torch.cuda.current_stream().cuda_stream
+    lib = g._lib
+    _lib.check(lib.hfg_forward(g._handle, C.c_void_p(mel_in.data_ptr()), B, T, C.c_void_p(out.data_ptr()), C.c_void_p(ws.data_ptr()),
+                               ws_bytes, C.c_void_p(stream)), g._handle)
+    _lib.check(lib.hfg_forward_pcm16(g._handle, C.c_void_p(mel_in.data_ptr()), B, T, C.c_void_p(pcm.data_ptr()), C.c_void_p(ws.data_ptr()),
+                                     ws_bytes, C.c_void_p(stream)), g._handle)
+    torch.cuda.synchronize()
+    g.close()
+    for buf, fill, n in ((mel_buf, 7.0, B * T * h.num_mels), (out_buf, 123.0, B * L), (pcm_buf, 12345, B * L), (ws_buf, 0xA5, ws_bytes)):
+        assert bool((buf[:G] == fill).all()) and bool((buf[G + n:] == fill).all())
+    assert np.array_equal(mel_in.cpu().numpy().reshape(B, T, -1), mel)            # the input is never written
+    assert np.array_equal(out.cpu().numpy().reshape(B, L, 1), want)
+    assert np.array_equal(pcm.cpu().numpy().reshape(B, L), want_pcm)
+
+
+@pytest.mark.parametrize("v,precision", [("1", "fp16"), ("2", "fp16"), ("3", "fp16"), ("1", "tf32")])
+def test_repeated_forwards_are_bit_identical(v, precision):
+    """A stand-in for racecheck: every forward of the same input -- plain launches, graph capture, graph replay, with the
+    resblocks as concurrent chains and at a size that runs the CTA-pair and fused kernels over many tiles -- returns the
+    same bits."""
+    import torch
+    h = HParams.builtin(v)
+    g = Generator(h, precision=precision).load_weights(synthetic_weights(h, "B"))
+    for B, T in ((2, 30), (3, 300)):
+        mel = synthetic_mel(B, T, h.num_mels, seed=B + T)
+        mel_dev = torch.from_numpy(mel).cuda()
+        first = g(mel).copy()
+        for _ in range(5):
+            assert np.array_equal(g(mel), first)
+        for _ in range(3):
+            assert np.array_equal(g(mel_dev).cpu().numpy(), first)
+    g.close()
