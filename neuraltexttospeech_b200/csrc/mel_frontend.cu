@@ -329,6 +329,12 @@ int hfg_mel_create(const hfg_mel_config* cfg, int device, hfg_mel_handle* out) {
   if (c.fft_length != 256 && c.fft_length != 1024 && c.fft_length != 4096)
     return mfail(nullptr, HFG_ERR_UNSUPPORTED, "fft_length must be 256, 1024 or 4096 (radix-4 kernel), got %d", c.fft_length);
   if (c.frame_length < 1 || c.frame_length > c.fft_length) return mfail(nullptr, HFG_ERR_INVALID, "frame_length must be in [1, fft_length]");
+  // The reference sizes its filterbank with frame_length // 2 + 1 spectrogram bins while tf.signal.stft returns
+  // fft_length // 2 + 1 (HiFiGAN_TF/common/audio_processing_tf.py:53-59, 85-97): with frame_length != filter_length its matmul
+  // has mismatched inner dimensions and raises.  The drop-in refuses the same constructor arguments instead of inventing a result.
+  if (c.frame_length != c.fft_length)
+    return mfail(nullptr, HFG_ERR_INVALID, "frame_length (%d) != filter_length (%d): the reference's mel filterbank has frame_length//2+1 bins "
+                 "and its matmul with the fft_length//2+1-bin spectrogram fails (audio_processing_tf.py:55,85-97)", c.frame_length, c.fft_length);
   if (c.frame_step < 1) return mfail(nullptr, HFG_ERR_INVALID, "frame_step must be >= 1");
   if (c.n_mel_channels < 1 || c.sampling_rate < 1 || c.mel_fmin < 0 || c.mel_fmax <= c.mel_fmin || c.mel_fmax > c.sampling_rate / 2.0f)
     return mfail(nullptr, HFG_ERR_INVALID, "bad mel filterbank parameters (need 0 <= fmin < fmax <= sampling_rate/2)");

@@ -61,6 +61,11 @@ def num_frames(n_samples, frame_length=1024, frame_step=256):
 def mel_spectrogram(wav, frame_length=1024, frame_step=256, fft_length=1024, n_mel_channels=80, sampling_rate=22050,
                     mel_fmin=0.0, mel_fmax=8000.0, dtype=np.float64):
     """wav [B, N] (or [N]) -> log-mel [B, T, n_mel_channels], T = num_frames(N) (audio_processing_tf.py:62-104)."""
+    if frame_length != fft_length:
+        # the reference builds the filterbank for frame_length // 2 + 1 bins (audio_processing_tf.py:55) but the STFT has
+        # fft_length // 2 + 1: its matmul raises for these arguments, and so does this restatement
+        raise ValueError(f"frame_length ({frame_length}) != filter_length ({fft_length}): the reference's "
+                         "spectrogram @ mel_filterbank has mismatched inner dimensions")
     x = np.asarray(wav, dtype=dtype)
     squeeze = x.ndim == 1
     if squeeze:
@@ -70,6 +75,6 @@ def mel_spectrogram(wav, frame_length=1024, frame_step=256, fft_length=1024, n_m
     frames = x[:, idx] * hann_periodic(frame_length).astype(dtype)[None, None, :]
     spec = np.fft.rfft(frames, n=fft_length, axis=-1)
     power = (np.abs(spec) ** 2).astype(dtype)
-    mel = power @ mel_weight_matrix(n_mel_channels, fft_length // 2 + 1, sampling_rate, mel_fmin, mel_fmax).astype(dtype)
+    mel = power @ mel_weight_matrix(n_mel_channels, frame_length // 2 + 1, sampling_rate, mel_fmin, mel_fmax).astype(dtype)   # audio_processing_tf.py:55
     out = np.log(np.clip(mel, 1e-5, None))
     return out[0] if squeeze else out

@@ -89,8 +89,8 @@ def test_mel_frontend_edge_cases_and_device_path():
     assert dev.is_cuda and (dev.cpu().numpy() == host).all()
     with pytest.raises(ValueError):
         STFT(filter_length=1000)
-    # other supported FFT sizes, frame shorter than the FFT (zero-padded at the end like tf.signal.stft)
-    for nfft, fl, st in ((256, 200, 64), (4096, 4096, 1024)):
+    # other supported FFT sizes (frame_length == filter_length, the only arguments the reference's own matmul accepts)
+    for nfft, fl, st in ((256, 256, 64), (4096, 4096, 1024)):
         f2 = STFT(filter_length=nfft, frame_length=fl, frame_step=st)
         m = f2.mel_spectrogram(wav)
         r = A.mel_spectrogram(wav.astype(np.float64), frame_length=fl, frame_step=st, fft_length=nfft)
@@ -125,3 +125,10 @@ def test_mel_frontend_matches_committed_fixture(golden_dir):
     mel = fe.mel_spectrogram(z["wav"])
     assert mel.shape == z["mel"].shape and np.abs(mel - z["mel"]).max() <= 2e-3
     fe.close()
+
+
+def test_mel_frontend_rejects_frame_length_other_than_filter_length():
+    # the reference's own matmul fails for these constructor arguments (audio_processing_tf.py:55, 85-97)
+    from neuraltexttospeech_b200 import STFT
+    with pytest.raises(ValueError):
+        STFT(filter_length=1024, frame_length=512)

@@ -81,3 +81,13 @@ def test_oracle_reproduces_committed_adjacent_fixture(golden_dir):
     assert mel.shape == z["mel"].shape == (2, 10, 80)
     assert np.abs(mel - z["mel"]).max() < 1e-5
     assert (A.pcm16(z["wav"]) == z["pcm"]).all()
+
+
+def test_frame_length_must_equal_filter_length_like_the_reference():
+    # audio_processing_tf.py:55: the filterbank has frame_length // 2 + 1 bins, the STFT fft_length // 2 + 1: the reference's
+    # matmul raises when they differ; the restatement (and the CUDA front-end, tests/test_adjacent_gpu.py) refuse too
+    import pytest
+    wav = np.zeros(4096, np.float32)
+    with pytest.raises(ValueError):
+        A.mel_spectrogram(wav, frame_length=512, fft_length=1024)
+    assert A.mel_spectrogram(wav, frame_length=1024, fft_length=1024).shape == (13, 80)
