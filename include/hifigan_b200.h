@@ -164,6 +164,24 @@ int hfg_op_tapped_conv(int act, int engine, const void* x_dev, int B, int x_rows
                        const void* res2_dev, float out_scale, float out_slope, float* acc_dev,
                        int mrf_mode, float mrf_div, void* out_dev, void* stream);
 
+/* The same direct (engine 0) tapped convolution for callers that cannot allocate device memory (CUDA-graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * The device copy of the weights and the bias that hfg_op_tapped_conv cudaMallocs per call lives here in one
+ * static device array of HFG_NOALLOC_SCRATCH_BYTES, which every GPU that loads the library holds until the process exits:
+ * a layer needs round_up(c_out * 4, 256) + ntaps * c_in * c_out * 4 bytes of it and larger ones are rejected with
+ * HFG_ERR_NOMEM.  No cudaMalloc / cudaFree / allocating routine is called; two host-to-device copies, one clear and the
+ * kernel are enqueued on `stream` and the call returns WITHOUT synchronising (w_host / bias_host may be reused on return
+ * when pageable; page-locked ones must stay unchanged until the stream reaches the copies).  All calls share the scratch,
+ * which keeps the previous call's contents: calls on one stream are ordered, calls that overlap on the GPU (two streams
+ * without an ordering, two host threads) race.  Runs on the current device.
+ *   v = bias[co] + sum_j sum_ci lrelu(x[b, q + tap_off[j], ci], in_slope) * w[j][ci][co] + res[...];  out = lrelu(v, out_slope)
+ * c_in % 4 == 0, c_out % 8 == 0; res may be NULL; err (may be NULL) receives the message of a failure. */
+#define HFG_NOALLOC_SCRATCH_BYTES (4u << 20)
+int hfg_op_tapped_conv_noalloc(int act, const void* x_dev, int B, int x_rows, int c_in, const float* w_host,
+                               const float* bias_host, int c_out, int ntaps, const int* tap_off, int out_stride,
+                               int out_off, float in_slope, const void* res_dev, float out_slope, void* out_dev,
+                               void* stream, char* err, size_t err_cap);
+
 /* Operator-level entry: ONE fused ResBlock1 iteration, xt = convs1[m](lrelu(x)); xt = convs2[m](lrelu(xt)); x = xt + x
  * (reference model.py:71-80), as a single launch whose intermediate stays in shared memory; synchronous, for parity
  * tests.  Kernel view of 64 channels per row (a [L, C] tensor with C < 64 is passed as [L/f, 64], f = 64/C, with

@@ -68,6 +68,9 @@ SIGNATURES = {
     "hfg_op_tapped_conv": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                      C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_float,
                                      C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_int, C.c_float, C.c_void_p, C.c_void_p]),
+    "hfg_op_tapped_conv_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                             C.POINTER(C.c_int), C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_float, C.c_void_p,
+                                             C.c_void_p, C.c_char_p, C.c_size_t]),
     "hfg_op_resblock_fused": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int),
                                         C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_int), C.c_float, C.c_float, C.c_void_p,
                                         C.c_float, C.c_float, C.c_void_p, C.c_void_p]),
