@@ -2,7 +2,8 @@
 //
 //  * conv_ffma_kernel : generic tapped conv, fp32 accumulate.  It is the whole forward pass in
 //    the fp32 validation mode (north star: <=1e-5 of the fp32 reference) and the fallback for
-//    shapes the tcgen05 kernel (conv_tc.cu) does not cover (V2's 16/8-channel stages).
+//    configs outside the tcgen05 tile table (conv_tc.cu); no conv of the stock V1 / V2 / V3 configs
+//    runs here in a 16-bit or TF32 mode (time folding covers the 32 / 16 / 8-channel stages).
 //  * conv_post_kernel : lrelu(0.3) -> Conv1D(1, 7) -> tanh  (reference HiFiGAN_TF/model.py:169-171),
 //    a pure bandwidth kernel (C_out = 1), shared by all precisions.
 //  * cast_pad_kernel  : fp32 mel -> 16-bit, channel-padded, for the tensor-core conv_pre.
