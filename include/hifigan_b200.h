@@ -239,6 +239,40 @@ int hfg_mel_forward_host(hfg_mel_handle h, const float* wav_host, int B, long lo
 const char* hfg_mel_last_error(hfg_mel_handle h);
 void hfg_mel_destroy(hfg_mel_handle h);
 
+/* ---------------------------------------------------------------------------------------------------------
+ * Discriminator forward passes: `MultiPeriodDiscriminator` (reference HiFiGAN_TF/model.py:246-274, five
+ * `DiscriminatorP` model.py:176-243) and `MultiScaleDiscriminator` (model.py:349-389, three `DiscriminatorS`
+ * model.py:277-346) on ONE waveform batch; the reference's `call((y, y_hat))` is two such passes (or one pass over the
+ * concatenated batch: no op couples utterances).  fp32 arithmetic.  Callers: gan.py:32-131 (training step).
+ *   compat 0 = the reference's Keras semantics (TensorFlow SAME padding with strides, "valid" first DiscriminatorS conv,
+ *              average pooling that ignores padding); 1 = upstream torch padding (what the vendored torch copies compute).
+ * Weight names: "discriminators.<i>.convs.<l>.{v,g,b}" and "discriminators.<i>.conv_post.{v,g,b}" for
+ * WeightNormalization-wrapped layers (kernel [k, c_in / groups, c_out]; Conv2D((k, 1)) kernels [k, 1, c_in, c_out] have
+ * the same element order), or ".w" + ".b" for a kernel used as stored (SpectralNormalization at inference, model.py:353). */
+typedef struct hfg_disc_ctx* hfg_disc_handle;
+
+/* kind 0 = MultiPeriodDiscriminator (model.py:247-256), 1 = MultiScaleDiscriminator (model.py:350-364). */
+int hfg_disc_create(int kind, int compat, int device, hfg_disc_handle* out);
+int hfg_disc_set_weight(hfg_disc_handle h, const char* name, const float* host, const int64_t* shape, int ndim);
+/* Folds weight norm (w = v * g / ||v||, per output channel) and uploads; needed before a forward. */
+int hfg_disc_finalize_weights(hfg_disc_handle h);
+
+/* Number of feature maps a forward writes: sub-discriminators x (convs + conv_post) = 30 (MPD) / 24 (MSD), in the order of
+ * the reference's fmap lists (model.py:236-241, 337-342); the last map of each sub-discriminator is its score. */
+int hfg_disc_num_maps(hfg_disc_handle h, int* out);
+/* Where each map lives in the output buffer of a [B, T] forward: offsets[i] in floats, dims[4 i ..] = {B, period, len, C}
+ * in MEMORY order (period = 1 for DiscriminatorS).  The reference's DiscriminatorP maps are [B, len, period, C]: swap
+ * axes 1 and 2 of the view (model.py:235 reshapes to [b, t / period, period, c]).  offsets / dims may be NULL. */
+int hfg_disc_layout(hfg_disc_handle h, int B, long long T, long long* offsets, long long* dims, long long* total_floats);
+
+/* audio_dev: device fp32 [B, T] (the reference's [B, T, 1]); maps_dev: device fp32 [total_floats]; asynchronous on `stream`. */
+int hfg_disc_forward(hfg_disc_handle h, const float* audio_dev, int B, long long T, float* maps_dev, void* stream);
+/* Same with HOST buffers (H2D, kernels, D2H, synchronise). */
+int hfg_disc_forward_host(hfg_disc_handle h, const float* audio_host, int B, long long T, float* maps_host);
+
+const char* hfg_disc_last_error(hfg_disc_handle h);
+void hfg_disc_destroy(hfg_disc_handle h);
+
 #ifdef __cplusplus
 }
 #endif

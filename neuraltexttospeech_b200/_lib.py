@@ -84,6 +84,16 @@ SIGNATURES = {
     "hfg_mel_forward_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_longlong, C.c_void_p]),
     "hfg_mel_last_error": (C.c_char_p, [C.c_void_p]),
     "hfg_mel_destroy": (None, [C.c_void_p]),
+    "hfg_disc_create": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
+    "hfg_disc_set_weight": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.POINTER(C.c_int64), C.c_int]),
+    "hfg_disc_finalize_weights": (C.c_int, [C.c_void_p]),
+    "hfg_disc_num_maps": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),
+    "hfg_disc_layout": (C.c_int, [C.c_void_p, C.c_int, C.c_longlong, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong),
+                                  C.POINTER(C.c_longlong)]),
+    "hfg_disc_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_longlong, C.c_void_p, C.c_void_p]),
+    "hfg_disc_forward_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_longlong, C.c_void_p]),
+    "hfg_disc_last_error": (C.c_char_p, [C.c_void_p]),
+    "hfg_disc_destroy": (None, [C.c_void_p]),
 }
 
 _lib = None
@@ -134,11 +144,11 @@ def last_error(handle=None) -> str:
     return msg.decode() if msg else ""
 
 
-def check(rc: int, handle=None, what: str = "", mel: bool = False):
+def check(rc: int, handle=None, what: str = "", mel: bool = False, disc: bool = False):
     if rc == 0:
         return
-    if mel:
-        m = load().hfg_mel_last_error(handle)
+    if mel or disc:
+        m = (load().hfg_mel_last_error if mel else load().hfg_disc_last_error)(handle)
         msg = (m.decode() if m else "") or f"error {rc}"
     else:
         msg = last_error(handle) or f"error {rc}"

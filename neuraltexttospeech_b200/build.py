@@ -16,7 +16,7 @@ CSRC = os.path.join(PKG_DIR, "csrc")
 ROOT = os.path.dirname(PKG_DIR)
 BUILD_DIR = os.path.join(ROOT, "build")
 LIB_PATH = os.path.join(PKG_DIR, "libhifigan_b200.so")
-SOURCES = ("conv_ffma.cu", "conv_tc.cu", "resblock_tc.cu", "conv_tf32.cu", "engine.cu", "mel_frontend.cu", "noalloc.cu")
+SOURCES = ("conv_ffma.cu", "conv_tc.cu", "resblock_tc.cu", "conv_tf32.cu", "engine.cu", "mel_frontend.cu", "noalloc.cu", "disc.cu")
 HEADERS = (os.path.join(CSRC, "kernels.cuh"), os.path.join(CSRC, "tc_ptx.cuh"), os.path.join(ROOT, "include", "hifigan_b200.h"))
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC"]

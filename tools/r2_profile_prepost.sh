@@ -3,17 +3,11 @@
 mkdir -p gpurun_out
 for v in 1 2; do
   python tools/profile_forward.py --version $v > gpurun_out/plain_prepost_v$v.log 2>&1 || { echo "plain v$v failed"; tail -3 gpurun_out/plain_prepost_v$v.log; continue; }
-  ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k 'regex:conv_tc_kernel<__half, 128, 16,' -s 1 -c 1 -f -o gpurun_out/prof_post_v$v \
+  ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k 'regex:conv_tc_kernel<__half, \(int\)128, \(int\)16,' -s 1 -c 1 -f -o gpurun_out/prof_post_v$v \
       python tools/profile_forward.py --version $v > gpurun_out/ncu_post_v$v.log 2>&1
   echo "ncu post v$v rc=$?"
   ncu -i gpurun_out/prof_post_v$v.ncu-rep --page raw --csv > gpurun_out/prof_post_v${v}_raw.csv 2>/dev/null
   ncu -i gpurun_out/prof_post_v$v.ncu-rep --page source --csv 2>/dev/null | gzip > gpurun_out/prof_post_v${v}_source.csv.gz
   rm -f gpurun_out/prof_post_v$v.ncu-rep
 done
-python tools/profile_forward.py > gpurun_out/plain_pre.log 2>&1 && \
-ncu --set full --clock-control none -k regex:conv_tc_kernel -s 42 -c 1 -f -o gpurun_out/prof_pre python tools/profile_forward.py > gpurun_out/ncu_pre.log 2>&1
-echo "ncu pre rc=$?"
-ncu -i gpurun_out/prof_pre.ncu-rep --page raw --csv > gpurun_out/prof_pre_raw.csv 2>/dev/null
-rm -f gpurun_out/prof_pre.ncu-rep
-python tools/cpu_batch_effect.py 1 > gpurun_out/cpu_batch_effect.json 2> gpurun_out/cpu_batch_effect.err; echo "cpu batch rc=$?"
 du -sh gpurun_out
