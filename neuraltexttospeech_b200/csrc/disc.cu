@@ -82,6 +82,7 @@ struct DiscConvArgs {
   int n_seq;
   long long n_in, n_out;
   int cin, cout, cin_g, cout_g, k, stride, pad_left;
+  int tqs, spt;         // rows per sequence and sequences per block tile (set by launch_conv)
   float out_slope;
 };
 
@@ -98,26 +99,40 @@ template <int CO_TILE, int TT> struct DiscCfg {
 
 // out[n, q, co] = lrelu(bias[co] + sum_j sum_ci x[n, q * stride + j - pad_left, g(co) * cin_g + ci] * w[j][ci][co]); rows outside
 // [0, n_in) are zero (TensorFlow pads with zeros AFTER the previous layer's LeakyReLU, and lrelu(0) = 0).
-// A block = TQ output rows x CO_TILE channels of one group of one sequence; a thread = TT rows x 4 channels.
-template <int CO_TILE, int TT, bool CI4>
+// A block = TQ output rows x CO_TILE channels of one group; a thread = TT rows x 4 channels.  The deep DiscriminatorP
+// layers have hundreds of SHORT sequences (15-50 rows), so a block's TQ rows are `spt` sequences x `tqs` rows each
+// (tqs * spt <= TQ, chosen on the host to waste the fewest rows): tile row r -> sequence z * spt + r / tqs, row
+// x * tqs + r % tqs; each sequence of the tile has its own (tqs - 1) * stride + k slab rows.
+template <int CO_TILE, int TT, bool CI4, bool PACK>
 __global__ void __launch_bounds__(256) disc_conv_kernel(const DiscConvArgs a) {
   using Cfg = DiscCfg<CO_TILE, TT>;
   extern __shared__ __align__(16) float slab[];
   const int tid = threadIdx.x;
   const int cgt = tid % Cfg::CGT, tg = tid / Cfg::CGT;
-  const long long q0 = (long long)blockIdx.x * Cfg::TQ;
+  const long long q0 = (long long)blockIdx.x * a.tqs;
   const int co = blockIdx.y * CO_TILE + cgt * 4;
   const int grp = (blockIdx.y * CO_TILE) / a.cout_g;
-  const int seq = blockIdx.z;
+  const int seq0 = blockIdx.z * a.spt;
   const int cblk = a.cin_g < kCiBlk ? a.cin_g : kCiBlk;
   const int pitch = CI4 ? cblk + 4 : cblk;                     // floats; +4 keeps float4 alignment and shifts the banks
-  const int rows = (Cfg::TQ - 1) * a.stride + a.k;
+  const int rows_s = (a.tqs - 1) * a.stride + a.k;             // slab rows per sequence of the tile
+  const int rows = rows_s * a.spt;
   const long long row0 = q0 * a.stride - a.pad_left;
-  const float* __restrict__ x = a.x + (size_t)seq * a.n_in * a.cin + (size_t)grp * a.cin_g;
+  const float* __restrict__ x = a.x + (size_t)grp * a.cin_g;
 
   float acc[TT][4];
+  int srow[TT];                                                // first slab row (tap 0) of each of this thread's rows, -1 = unused
 #pragma unroll
-  for (int t = 0; t < TT; ++t) { acc[t][0] = acc[t][1] = acc[t][2] = acc[t][3] = 0.f; }
+  for (int t = 0; t < TT; ++t) {
+    acc[t][0] = acc[t][1] = acc[t][2] = acc[t][3] = 0.f;
+    const int r = t * Cfg::TG + tg;
+    if (PACK) {
+      const int sl = r / a.tqs, ql = r - sl * a.tqs;
+      srow[t] = (sl < a.spt && seq0 + sl < a.n_seq && q0 + ql < a.n_out) ? sl * rows_s + ql * a.stride : -1;
+    } else {
+      srow[t] = r * a.stride;                                  // one sequence per tile (tqs = TQ): rows past n_out are computed, not stored
+    }
+  }
 
   for (int ci0 = 0; ci0 < a.cin_g; ci0 += kCiBlk) {
     const int cib = min(kCiBlk, a.cin_g - ci0);
@@ -125,48 +140,66 @@ __global__ void __launch_bounds__(256) disc_conv_kernel(const DiscConvArgs a) {
       const int c4n = cblk / 4;
       for (int idx = tid; idx < rows * c4n; idx += Cfg::THREADS) {
         const int r = idx / c4n, c4 = idx - r * c4n;
-        const long long row = row0 + r;
+        const int sl = r / rows_s;
+        const long long row = row0 + (r - sl * rows_s);
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (row >= 0 && row < a.n_in && c4 * 4 < cib) v = __ldg(reinterpret_cast<const float4*>(x + (size_t)row * a.cin + ci0 + c4 * 4));
+        if (row >= 0 && row < a.n_in && seq0 + sl < a.n_seq && c4 * 4 < cib)
+          v = __ldg(reinterpret_cast<const float4*>(x + ((size_t)(seq0 + sl) * a.n_in + row) * a.cin + ci0 + c4 * 4));
         *reinterpret_cast<float4*>(&slab[r * pitch + c4 * 4]) = v;
       }
     } else {
       for (int idx = tid; idx < rows * cblk; idx += Cfg::THREADS) {
         const int r = idx / cblk, c = idx - r * cblk;
-        const long long row = row0 + r;
-        slab[r * pitch + c] = (row >= 0 && row < a.n_in && c < cib) ? __ldg(x + (size_t)row * a.cin + ci0 + c) : 0.f;
+        const int sl = r / rows_s;
+        const long long row = row0 + (r - sl * rows_s);
+        slab[r * pitch + c] = (row >= 0 && row < a.n_in && seq0 + sl < a.n_seq && c < cib)
+                                  ? __ldg(x + ((size_t)(seq0 + sl) * a.n_in + row) * a.cin + ci0 + c) : 0.f;
       }
     }
     __syncthreads();
-    for (int j = 0; j < a.k; ++j) {
-      const float* __restrict__ wj = a.w + ((size_t)j * a.cin_g + ci0) * a.cout + co;
-      const float* sj = &slab[(tg * a.stride + j) * pitch];
-      const int tstep = Cfg::TG * a.stride * pitch;
-      if (CI4) {
-        for (int c4 = 0; c4 < cib / 4; ++c4) {
-          const float4 w0 = __ldg(reinterpret_cast<const float4*>(wj + (size_t)(c4 * 4 + 0) * a.cout));
-          const float4 w1 = __ldg(reinterpret_cast<const float4*>(wj + (size_t)(c4 * 4 + 1) * a.cout));
-          const float4 w2 = __ldg(reinterpret_cast<const float4*>(wj + (size_t)(c4 * 4 + 2) * a.cout));
-          const float4 w3 = __ldg(reinterpret_cast<const float4*>(wj + (size_t)(c4 * 4 + 3) * a.cout));
-#pragma unroll
-          for (int t = 0; t < TT; ++t) {
-            const float4 xv = *reinterpret_cast<const float4*>(&sj[t * tstep + c4 * 4]);
-            acc[t][0] = fmaf(xv.x, w0.x, acc[t][0]); acc[t][1] = fmaf(xv.x, w0.y, acc[t][1]);
-            acc[t][2] = fmaf(xv.x, w0.z, acc[t][2]); acc[t][3] = fmaf(xv.x, w0.w, acc[t][3]);
-            acc[t][0] = fmaf(xv.y, w1.x, acc[t][0]); acc[t][1] = fmaf(xv.y, w1.y, acc[t][1]);
-            acc[t][2] = fmaf(xv.y, w1.z, acc[t][2]); acc[t][3] = fmaf(xv.y, w1.w, acc[t][3]);
-            acc[t][0] = fmaf(xv.z, w2.x, acc[t][0]); acc[t][1] = fmaf(xv.z, w2.y, acc[t][1]);
-            acc[t][2] = fmaf(xv.z, w2.z, acc[t][2]); acc[t][3] = fmaf(xv.z, w2.w, acc[t][3]);
-            acc[t][0] = fmaf(xv.w, w3.x, acc[t][0]); acc[t][1] = fmaf(xv.w, w3.y, acc[t][1]);
-            acc[t][2] = fmaf(xv.w, w3.z, acc[t][2]); acc[t][3] = fmaf(xv.w, w3.w, acc[t][3]);
-          }
+    if (CI4) {
+      // one flat loop over (tap, 4-channel group) with the NEXT step's weights already in flight (they come from L2)
+      const int c4n = cib / 4, nit = a.k * c4n;
+      const float* __restrict__ wp = a.w + (size_t)ci0 * a.cout + co;
+      const size_t tap_step = (size_t)a.cin_g * a.cout;
+      float4 w0 = __ldg(reinterpret_cast<const float4*>(wp)), w1 = __ldg(reinterpret_cast<const float4*>(wp + a.cout));
+      float4 w2 = __ldg(reinterpret_cast<const float4*>(wp + 2 * (size_t)a.cout)), w3 = __ldg(reinterpret_cast<const float4*>(wp + 3 * (size_t)a.cout));
+      int j = 0, c4 = 0;
+      for (int it = 0; it < nit; ++it) {
+        int jn = j, cn = c4 + 1;
+        if (cn == c4n) { cn = 0; ++jn; }
+        float4 n0 = w0, n1 = w1, n2 = w2, n3 = w3;
+        if (it + 1 < nit) {
+          const float* __restrict__ np = wp + (size_t)jn * tap_step + (size_t)(cn * 4) * a.cout;
+          n0 = __ldg(reinterpret_cast<const float4*>(np)); n1 = __ldg(reinterpret_cast<const float4*>(np + a.cout));
+          n2 = __ldg(reinterpret_cast<const float4*>(np + 2 * (size_t)a.cout)); n3 = __ldg(reinterpret_cast<const float4*>(np + 3 * (size_t)a.cout));
         }
-      } else {
+        const float* sj = &slab[j * pitch + c4 * 4];
+#pragma unroll
+        for (int t = 0; t < TT; ++t) {
+          if (PACK && srow[t] < 0) continue;
+          const float4 xv = *reinterpret_cast<const float4*>(&sj[srow[t] * pitch]);
+          acc[t][0] = fmaf(xv.x, w0.x, acc[t][0]); acc[t][1] = fmaf(xv.x, w0.y, acc[t][1]);
+          acc[t][2] = fmaf(xv.x, w0.z, acc[t][2]); acc[t][3] = fmaf(xv.x, w0.w, acc[t][3]);
+          acc[t][0] = fmaf(xv.y, w1.x, acc[t][0]); acc[t][1] = fmaf(xv.y, w1.y, acc[t][1]);
+          acc[t][2] = fmaf(xv.y, w1.z, acc[t][2]); acc[t][3] = fmaf(xv.y, w1.w, acc[t][3]);
+          acc[t][0] = fmaf(xv.z, w2.x, acc[t][0]); acc[t][1] = fmaf(xv.z, w2.y, acc[t][1]);
+          acc[t][2] = fmaf(xv.z, w2.z, acc[t][2]); acc[t][3] = fmaf(xv.z, w2.w, acc[t][3]);
+          acc[t][0] = fmaf(xv.w, w3.x, acc[t][0]); acc[t][1] = fmaf(xv.w, w3.y, acc[t][1]);
+          acc[t][2] = fmaf(xv.w, w3.z, acc[t][2]); acc[t][3] = fmaf(xv.w, w3.w, acc[t][3]);
+        }
+        w0 = n0; w1 = n1; w2 = n2; w3 = n3; j = jn; c4 = cn;
+      }
+    } else {
+      for (int j = 0; j < a.k; ++j) {
+        const float* __restrict__ wj = a.w + ((size_t)j * a.cin_g + ci0) * a.cout + co;
+        const float* sj = &slab[j * pitch];
         for (int c = 0; c < cib; ++c) {
           const float4 w0 = __ldg(reinterpret_cast<const float4*>(wj + (size_t)c * a.cout));
 #pragma unroll
           for (int t = 0; t < TT; ++t) {
-            const float xv = sj[t * tstep + c];
+            if (PACK && srow[t] < 0) continue;
+            const float xv = sj[srow[t] * pitch + c];
             acc[t][0] = fmaf(xv, w0.x, acc[t][0]); acc[t][1] = fmaf(xv, w0.y, acc[t][1]);
             acc[t][2] = fmaf(xv, w0.z, acc[t][2]); acc[t][3] = fmaf(xv, w0.w, acc[t][3]);
           }
@@ -179,11 +212,13 @@ __global__ void __launch_bounds__(256) disc_conv_kernel(const DiscConvArgs a) {
   const float4 bias = __ldg(reinterpret_cast<const float4*>(a.bias + co));
 #pragma unroll
   for (int t = 0; t < TT; ++t) {
-    const long long q = q0 + t * Cfg::TG + tg;
-    if (q >= a.n_out) continue;
+    const int r = t * Cfg::TG + tg;
+    const int sl = PACK ? r / a.tqs : 0;
+    const long long q = q0 + (r - sl * a.tqs);
+    if (PACK ? srow[t] < 0 : q >= a.n_out) continue;
     float4 v = make_float4(acc[t][0] + bias.x, acc[t][1] + bias.y, acc[t][2] + bias.z, acc[t][3] + bias.w);
     v.x = lrelu(v.x, a.out_slope); v.y = lrelu(v.y, a.out_slope); v.z = lrelu(v.z, a.out_slope); v.w = lrelu(v.w, a.out_slope);
-    *reinterpret_cast<float4*>(a.out + ((size_t)seq * a.n_out + q) * a.cout + co) = v;
+    *reinterpret_cast<float4*>(a.out + ((size_t)(seq0 + sl) * a.n_out + q) * a.cout + co) = v;
   }
 }
 
@@ -212,17 +247,31 @@ __global__ void __launch_bounds__(256) disc_post_kernel(const DiscConvArgs a) {
 }
 
 template <int CO_TILE, int TT, bool CI4>
-cudaError_t launch_conv_t(const DiscConvArgs& a, cudaStream_t s) {
+cudaError_t launch_conv_t(const DiscConvArgs& a0, cudaStream_t s) {
   using Cfg = DiscCfg<CO_TILE, TT>;
+  DiscConvArgs a = a0;
+  // rows per sequence in a tile: the split of TQ into spt x tqs that computes the fewest padded rows overall
+  int best_tqs = Cfg::TQ;
+  double best_eff = 0.0;
+  for (int tqs = Cfg::TQ; tqs >= 1; --tqs) {
+    if (a.n_out > Cfg::TQ / 2 && tqs != Cfg::TQ) break;        // sequences that do not fit twice: one sequence per tile
+    const int spt = Cfg::TQ / tqs;
+    if ((size_t)((tqs - 1) * a.stride + a.k) * spt * (CI4 ? (a.cin_g < kCiBlk ? a.cin_g : kCiBlk) + 4 : 1) * sizeof(float) > 96 * 1024 && tqs != Cfg::TQ) continue;
+    const long long qt = (a.n_out + tqs - 1) / tqs, zt = (a.n_seq + spt - 1) / spt;
+    const double eff = (double)a.n_out * a.n_seq / ((double)qt * zt * Cfg::TQ);
+    if (eff > best_eff + 1e-9) { best_eff = eff; best_tqs = tqs; }
+  }
+  a.tqs = best_tqs; a.spt = Cfg::TQ / best_tqs;
   const int cblk = a.cin_g < kCiBlk ? a.cin_g : kCiBlk;
   const int pitch = CI4 ? cblk + 4 : cblk;
-  const size_t smem = (size_t)((Cfg::TQ - 1) * a.stride + a.k) * pitch * sizeof(float);
-  auto kern = disc_conv_kernel<CO_TILE, TT, CI4>;
+  const size_t smem = (size_t)((a.tqs - 1) * a.stride + a.k) * a.spt * pitch * sizeof(float);
+  if (smem > 200 * 1024) return cudaErrorInvalidValue;
+  auto kern = a.spt > 1 ? disc_conv_kernel<CO_TILE, TT, CI4, true> : disc_conv_kernel<CO_TILE, TT, CI4, false>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
-  dim3 grid((unsigned)((a.n_out + Cfg::TQ - 1) / Cfg::TQ), a.cout / CO_TILE, a.n_seq);
+  dim3 grid((unsigned)((a.n_out + a.tqs - 1) / a.tqs), a.cout / CO_TILE, (unsigned)((a.n_seq + a.spt - 1) / a.spt));
   kern<<<grid, Cfg::THREADS, smem, s>>>(a);
   return cudaGetLastError();
 }

@@ -129,3 +129,20 @@ class MultiPeriodDiscriminator(_Discriminator):
 
 class MultiScaleDiscriminator(_Discriminator):
     KIND, N_SUB, N_LAYERS = 1, 3, 8
+
+
+# (c_in, c_out, kernel, groups) per layer, in forward order (model.py:186-216 / 284-332)
+_P_LAYERS = ((1, 32, 5, 1), (32, 128, 5, 1), (128, 512, 5, 1), (512, 1024, 5, 1), (1024, 1024, 5, 1), (1024, 1, 3, 1))
+_S_LAYERS = ((1, 128, 15, 1), (128, 128, 41, 4), (128, 256, 41, 16), (256, 512, 41, 16), (512, 1024, 41, 16), (1024, 1024, 41, 16),
+             (1024, 1024, 5, 1), (1024, 1, 3, 1))
+
+
+def disc_flops(model: _Discriminator, B: int, T: int):
+    """Algorithmic work of one forward over [B, T]: (FLOPs = 2 * MACs of every conv, bytes of all feature maps written)."""
+    _, dims, total = model.layout(B, T)
+    layers = _P_LAYERS if model.KIND == 0 else _S_LAYERS
+    flops = 0
+    for i, (b, p, n, c) in enumerate(dims):
+        cin, cout, k, groups = layers[i % model.N_LAYERS]
+        flops += 2 * b * p * n * cout * k * (cin // groups)
+    return flops, total * 4
