@@ -346,6 +346,30 @@ def main():
                                     "frac": fe_bytes / (fe_ms * 1e-3) / 1e9 / peaks()["hbm_gbs"],
                                     "note": "wav [B, L] fp32 resident in HBM (one step's output, L2-sized per utterance) -> log-mel [B, T, 80]"}
         fe.close()
+        # discriminator forward passes at the reference's training-step shape (config_v1.json: batch_size
+        # 16, segment_size 8192; gan.py scores y and y_hat -> 32 waveforms), cut from the audio this step produced
+        from neuraltexttospeech_b200.discriminators import MultiPeriodDiscriminator, MultiScaleDiscriminator, disc_flops
+        from neuraltexttospeech_b200.synthetic import synthetic_disc_weights
+        nb_d, seg = min(B, 32), min(L, 8192)
+        seg_wav = wav[:nb_d, :seg].contiguous()
+        drow = {"waveforms": nb_d, "samples": seg, "dtype": "f32", "bound": "fp32 FFMA (CUDA cores)",
+                "peak_tflops": 148 * 128 * 2 * 1.965e-3, "peak_source": "nominal: 148 SMs x 128 FP32 lanes x 2 x 1.965 GHz (not measured)"}
+        for kind, cls in (("mpd", MultiPeriodDiscriminator), ("msd", MultiScaleDiscriminator)):
+            dm = cls(device=local_rank).load_weights(synthetic_disc_weights(kind, "A"))
+            for _ in range(3):
+                dm.forward(seg_wav)
+            torch.cuda.synchronize()
+            f0.record(stream)
+            for _ in range(5):
+                dm.forward(seg_wav)
+            f1.record(stream)
+            torch.cuda.synchronize()
+            d_ms = f0.elapsed_time(f1) / 5
+            fl, by = disc_flops(dm, nb_d, seg)
+            drow[kind] = {"ms": d_ms, "gflop": fl / 1e9, "tflops": fl / d_ms / 1e9, "frac": fl / d_ms / 1e9 / drow["peak_tflops"],
+                          "feature_map_mbytes": by / 1e6, "launches": 35 if kind == "mpd" else 26}
+            del dm
+        adjacent["discriminators"] = drow
 
     if rank == 0:
         pk = peaks()

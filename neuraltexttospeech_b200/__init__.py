@@ -5,5 +5,6 @@ from .utils import get_padding, LRELU_SLOPE           # noqa: F401
 from .generator import Generator                      # noqa: F401
 from .audio_processing import STFT                    # noqa: F401
 from .pcm import write_wav, write_wavs                # noqa: F401
+from .discriminators import MultiPeriodDiscriminator, MultiScaleDiscriminator   # noqa: F401
 
-__all__ = ["Generator", "HParams", "STFT", "get_padding", "LRELU_SLOPE", "write_wav", "write_wavs"]
+__all__ = ["Generator", "HParams", "STFT", "MultiPeriodDiscriminator", "MultiScaleDiscriminator", "get_padding", "LRELU_SLOPE", "write_wav", "write_wavs"]

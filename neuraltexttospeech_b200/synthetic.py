@@ -48,3 +48,35 @@ def synthetic_weights(hparams, variant: str = "A", seed: int = MEL_SEED) -> Dict
         out[f"{L.name}.g"] = g.astype(np.float32)
         out[f"{L.name}.b"] = b
     return out
+
+
+def synthetic_disc_weights(kind: str, variant: str = "A", seed: int = 4321) -> Dict[str, np.ndarray]:
+    """Seeded Glorot-uniform weights for the discriminators (kind "mpd" / "msd"; discriminators.py), drawn layer by layer
+    like `synthetic_weights`.  The first DiscriminatorS is SpectralNormalization-wrapped in the reference
+    (HiFiGAN_TF/model.py:353) and gets a plain kernel `w`; every other layer gets WeightNormalization's (v, g, b)."""
+    from .discriminators import MPD_PERIODS, _P_LAYERS, _S_LAYERS
+    if kind not in ("mpd", "msd") or variant not in ("A", "B"):
+        raise ValueError("kind must be 'mpd' or 'msd', variant 'A' or 'B'")
+    n_sub, layers = (len(MPD_PERIODS), _P_LAYERS) if kind == "mpd" else (3, _S_LAYERS)
+    out: Dict[str, np.ndarray] = {}
+    n = 0
+    for i in range(n_sub):
+        for l, (cin, cout, k, groups) in enumerate(layers):
+            name = f"discriminators.{i}.convs.{l}" if l + 1 < len(layers) else f"discriminators.{i}.conv_post"
+            rng = np.random.default_rng(seed + n)
+            n += 1
+            lim = math.sqrt(6.0 / (k * (cin // groups) + k * cout))
+            v = rng.uniform(-lim, lim, size=(k, cin // groups, cout)).astype(np.float32)
+            nrm = _norm_over_leading(v)
+            g = nrm.copy()
+            b = np.zeros(cout, dtype=np.float32)
+            if variant == "B":
+                g = g * rng.uniform(0.5, 1.5, size=g.shape)
+                b = rng.uniform(-0.05, 0.05, size=cout).astype(np.float32)
+            if kind == "msd" and i == 0:
+                out[name + ".w"] = (v * (g / nrm)).astype(np.float32)
+            else:
+                out[name + ".v"] = v
+                out[name + ".g"] = g.astype(np.float32)
+            out[name + ".b"] = b
+    return out

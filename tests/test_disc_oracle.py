@@ -92,3 +92,13 @@ def test_reference_mode_shapes_follow_keras():
     yp = np.concatenate([y, y[:, -2:-6:-1]], axis=1)           # 301 -> 305 by hand
     score2, _ = D.disc_p_forward(wp, 2, 5, yp, "reference")
     np.testing.assert_allclose(score, score2, rtol=0, atol=1e-7)
+
+
+def test_package_and_oracle_weight_generators_agree():
+    """bench.py / tools may not import oracle/: the package carries its own copy of the seeded generator."""
+    from neuraltexttospeech_b200.synthetic import synthetic_disc_weights
+    for kind in ("mpd", "msd"):
+        for variant in "AB":
+            a, b = synthetic_disc_weights(kind, variant), D.synthetic_weights(kind, variant)
+            assert a.keys() == b.keys()
+            assert all(np.array_equal(a[k], b[k]) for k in a)

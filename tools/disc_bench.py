@@ -19,13 +19,13 @@ args = ap.parse_args()
 import numpy as np
 import torch
 from neuraltexttospeech_b200.discriminators import MultiPeriodDiscriminator, MultiScaleDiscriminator, disc_flops
-from oracle import disc_oracle as D     # synthetic weights only (seeded)
+from neuraltexttospeech_b200.synthetic import synthetic_disc_weights
 
 rng = np.random.default_rng(0)
 y = torch.from_numpy(rng.standard_normal((args.batch, args.samples)).astype(np.float32) * 0.3).cuda()
 rows = {}
 for kind, cls in (("mpd", MultiPeriodDiscriminator), ("msd", MultiScaleDiscriminator)):
-    m = cls().load_weights(D.synthetic_weights(kind, "A"))
+    m = cls().load_weights(synthetic_disc_weights(kind, "A"))
     for _ in range(1 if args.once else 3):
         m.forward(y)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
