@@ -14,10 +14,17 @@
 // Kernels: disc_split_kernel (reflect pad + period split), disc_pool_kernel (AveragePooling1D(4, 2, "same")),
 // disc_conv_kernel (strided, grouped Conv1D with TensorFlow SAME / VALID padding, bias and LeakyReLU fused),
 // disc_post_kernel (C_out = 1).
+// The dense stride-1 layers (1024 -> 1024, k = 5: 45 % of the MultiPeriodDiscriminator's FLOPs) run on the tensor cores at
+// fp32 accuracy ("3xTF32"): tcgen05.mma.kind::tf32 reads only the top 10 mantissa bits of an fp32 operand, so with
+// x = x_hi + x_lo (x_hi = what the tensor core sees, x_lo = the exact remainder) and w = w_hi + w_lo likewise,
+//     x . w  ~=  x_hi . w_hi + x_hi . w_lo + x_lo . w_hi          (dropped: x_lo . w_lo, ~2^-22 relative)
+// is three TF32 products accumulated in fp32 in TMEM: conv_tf32.cu's kernel run twice (x_lo with w_hi taps into a scratch
+// map, then x with [w_hi | w_lo] as 2k taps + that scratch + bias + LeakyReLU).  HFG_DISC_TC=0 keeps every layer on FFMA.
 #include <algorithm>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <string>
@@ -26,6 +33,7 @@
 #include <cuda_runtime.h>
 
 #include "../../include/hifigan_b200.h"
+#include "kernels.cuh"
 
 namespace {
 
@@ -71,6 +79,17 @@ __global__ void disc_pool_kernel(const float* __restrict__ x, float* __restrict_
       if (t >= 0 && t < n) { s += x[b * n + t]; ++cnt; }
     }
     out[i] = s / (float)(count_pad ? 4 : cnt);
+  }
+}
+
+// x_lo = x - (x with the low 13 mantissa bits cleared): the part of an fp32 operand the TF32 tensor core does not see
+__global__ void disc_lo_kernel(const float4* __restrict__ x, float4* __restrict__ lo, long long n4) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    const float4 v = x[i];
+    float4 o;
+    o.x = v.x - __uint_as_float(__float_as_uint(v.x) & 0xFFFFE000u); o.y = v.y - __uint_as_float(__float_as_uint(v.y) & 0xFFFFE000u);
+    o.z = v.z - __uint_as_float(__float_as_uint(v.z) & 0xFFFFE000u); o.w = v.w - __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u);
+    lo[i] = o;
   }
 }
 
@@ -307,6 +326,10 @@ struct DiscLayer {
   std::vector<float> v, g, b, w;        // as set by the caller (w: stored kernel, used as is)
   float* d_w = nullptr;                 // folded [k][cin_g][cout]
   float* d_b = nullptr;
+  bool tc = false;                      // dense stride-1 layer on the tensor cores (3xTF32)
+  void* d_wpk_main = nullptr;           // tf32_pack_weights image of [w_hi taps | w_lo taps] (2k taps)
+  void* d_wpk_lo = nullptr;             // tf32_pack_weights image of w_hi (k taps), for the x_lo pass
+  float* d_zero = nullptr;              // zero bias of the x_lo pass
 };
 
 struct SubDisc {
@@ -322,6 +345,7 @@ struct MapDesc { long long offset; int B, period; long long len; int C; };
 struct hfg_disc_ctx {
   int kind = 0, compat = 0, device = 0;
   bool finalized = false;
+  bool use_tc = true;                                  // HFG_DISC_TC=0: every layer on the FFMA kernel
   std::vector<SubDisc> subs;
   std::string err;
   float* ws = nullptr; size_t ws_floats = 0;           // split / pooled waveforms
@@ -407,11 +431,25 @@ int run_disc_forward(hfg_disc_ctx* h, const float* audio, int B, long long T, fl
   size_t need = 0;
   if (h->kind == 0) { for (const SubDisc& sd : h->subs) need = std::max(need, (size_t)B * sd.period * (size_t)first_len(h, sd, T)); }
   else { for (const SubDisc& sd : h->subs) if (sd.pools) need += (size_t)B * (size_t)first_len(h, sd, T); }
-  if (need > h->ws_floats) {
-    if (h->ws) { DISC_CUDA_TRY(h, cudaStreamSynchronize(s)); cudaFree(h->ws); h->ws = nullptr; h->ws_floats = 0; }
-    DISC_CUDA_TRY(h, cudaMalloc((void**)&h->ws, need * sizeof(float)));
-    h->ws_floats = need;
+  need = (need + 63) / 64 * 64;                              // the tensor-core scratch below starts 256-byte aligned
+  size_t tc_lo = 0, tc_part = 0;                             // x_lo and the x_lo . w_hi partial map of a 3xTF32 layer (largest)
+  {
+    size_t k = 0;
+    for (const SubDisc& sd : h->subs)
+      for (size_t l = 0; l < sd.layers.size(); ++l, ++k)
+        if (sd.layers[l].tc) {
+          tc_lo = std::max(tc_lo, (size_t)B * sd.period * (size_t)maps[k - 1].len * sd.layers[l].spec.cin);
+          tc_part = std::max(tc_part, (size_t)B * sd.period * (size_t)maps[k].len * sd.layers[l].spec.cout);
+        }
+    tc_lo = (tc_lo + 63) / 64 * 64;
   }
+  if (need + tc_lo + tc_part > h->ws_floats) {
+    if (h->ws) { DISC_CUDA_TRY(h, cudaStreamSynchronize(s)); cudaFree(h->ws); h->ws = nullptr; h->ws_floats = 0; }
+    DISC_CUDA_TRY(h, cudaMalloc((void**)&h->ws, (need + tc_lo + tc_part) * sizeof(float)));
+    h->ws_floats = need + tc_lo + tc_part;
+  }
+  float* const ws_lo = h->ws + need;
+  float* const ws_part = ws_lo + tc_lo;
   size_t mi = 0;
   const float* pooled = audio; long long pooled_n = T; float* ws_next = h->ws;
   for (const SubDisc& sd : h->subs) {
@@ -444,7 +482,26 @@ int run_disc_forward(hfg_disc_ctx* h, const float* audio, int B, long long T, fl
       a.cin = L.spec.cin; a.cout = L.spec.cout; a.cin_g = L.spec.cin / L.spec.groups; a.cout_g = L.spec.cout / L.spec.groups;
       a.k = L.spec.k; a.stride = L.spec.stride; a.pad_left = left;
       a.out_slope = l + 1 == sd.layers.size() ? 1.0f : kSlope;        // conv_post has no activation (model.py:241 / 342)
-      cudaError_t e = launch_conv(a, s);
+      cudaError_t e;
+      if (L.tc) {
+        const long long n4 = (long long)n_seq * n * L.spec.cin / 4;
+        disc_lo_kernel<<<(unsigned)std::min<long long>((n4 + 255) / 256, 148 * 8), 256, 0, s>>>(
+            reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(ws_lo), n4);
+        e = cudaGetLastError();
+        hfg::TcArgs t{};
+        t.B = n_seq; t.x_rows = (int)n; t.n_q = (int)n_out; t.out_rows = (int)n_out; t.out_stride = 1;
+        t.c_in = L.spec.cin; t.c_out = L.spec.cout; t.res_inv = 1.0f; t.out_scale = 1.0f; t.raw_out = 1; t.nvar = 1;
+        t.var[0].out_off = 0;
+        for (int j = 0; j < L.spec.k; ++j) t.var[0].tap_off[j] = t.var[0].tap_off[j + L.spec.k] = j - left;
+        // pass 1: partial = x_lo . w_hi
+        t.x = ws_lo; t.out = ws_part; t.bias = L.d_zero; t.out_slope = 1.0f; t.var[0].w = L.d_wpk_lo; t.var[0].ntaps = L.spec.k;
+        if (e == cudaSuccess) e = hfg::launch_conv_tf32(t, s);
+        // pass 2: out = lrelu(bias + x_hi . w_hi + x_hi . w_lo + partial)
+        t.x = x; t.out = a.out; t.bias = L.d_b; t.res2 = ws_part; t.out_slope = a.out_slope; t.var[0].w = L.d_wpk_main; t.var[0].ntaps = 2 * L.spec.k;
+        if (e == cudaSuccess) e = hfg::launch_conv_tf32(t, s);
+      } else {
+        e = launch_conv(a, s);
+      }
       if (e != cudaSuccess) return dfail(h, HFG_ERR_CUDA, "%s launch failed: %s", L.name.c_str(), cudaGetErrorString(e));
       x = a.out; n = n_out;
     }
@@ -466,6 +523,7 @@ int hfg_disc_create(int kind, int compat, int device, hfg_disc_handle* out) {
     return dfail(nullptr, HFG_ERR_CUDA, "no CUDA device %d (this library has no CPU path)", device);
   hfg_disc_ctx* h = new hfg_disc_ctx();
   h->kind = kind; h->compat = compat; h->device = device;
+  { const char* e = getenv("HFG_DISC_TC"); if (e && atoi(e) == 0) h->use_tc = false; }
   const int nsub = kind == 0 ? 5 : 3;
   for (int i = 0; i < nsub; ++i) {
     SubDisc sd;
@@ -538,6 +596,30 @@ int hfg_disc_finalize_weights(hfg_disc_handle h) {
       DISC_CUDA_TRY(h, cudaMemcpy(L.d_w, w.data(), kel * sizeof(float), cudaMemcpyHostToDevice));
       DISC_CUDA_TRY(h, cudaMalloc((void**)&L.d_b, bias.size() * sizeof(float)));
       DISC_CUDA_TRY(h, cudaMemcpy(L.d_b, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
+      // dense stride-1 layers: tensor cores at fp32 accuracy (3xTF32, see the header of this file)
+      if (L.d_wpk_main) cudaFree(L.d_wpk_main);
+      if (L.d_wpk_lo) cudaFree(L.d_wpk_lo);
+      if (L.d_zero) cudaFree(L.d_zero);
+      L.d_wpk_main = L.d_wpk_lo = nullptr; L.d_zero = nullptr;
+      L.tc = h->use_tc && L.spec.stride == 1 && L.spec.groups == 1 && cout >= 128 && cout % 128 == 0 && 2 * L.spec.k <= hfg::kMaxTaps &&
+             hfg::tf32_supported(L.spec.cin, cout, 2 * L.spec.k, L.spec.k - 1);
+      if (L.tc) {
+        std::vector<float> both(2 * kel), pk(2 * kel);
+        for (size_t i = 0; i < kel; ++i) {
+          uint32_t u; memcpy(&u, &w[i], 4);
+          u = (u + 0x0FFFu + ((u >> 13) & 1u)) & ~0x1FFFu;      // w_hi: round to nearest even at 10 mantissa bits (= tf32_pack_weights)
+          float hi; memcpy(&hi, &u, 4);
+          both[i] = hi; both[kel + i] = w[i] - hi;              // w_lo: exact in fp32
+        }
+        hfg::tf32_pack_weights(both.data(), 2 * L.spec.k, L.spec.cin, cout, pk.data());
+        DISC_CUDA_TRY(h, cudaMalloc(&L.d_wpk_main, 2 * kel * sizeof(float)));
+        DISC_CUDA_TRY(h, cudaMemcpy(L.d_wpk_main, pk.data(), 2 * kel * sizeof(float), cudaMemcpyHostToDevice));
+        hfg::tf32_pack_weights(both.data(), L.spec.k, L.spec.cin, cout, pk.data());
+        DISC_CUDA_TRY(h, cudaMalloc(&L.d_wpk_lo, kel * sizeof(float)));
+        DISC_CUDA_TRY(h, cudaMemcpy(L.d_wpk_lo, pk.data(), kel * sizeof(float), cudaMemcpyHostToDevice));
+        DISC_CUDA_TRY(h, cudaMalloc((void**)&L.d_zero, cout * sizeof(float)));
+        DISC_CUDA_TRY(h, cudaMemset(L.d_zero, 0, cout * sizeof(float)));
+      }
     }
   h->finalized = true;
   return HFG_OK;
@@ -606,7 +688,13 @@ void hfg_disc_destroy(hfg_disc_handle h) {
   if (!h) return;
   cudaSetDevice(h->device);
   for (SubDisc& sd : h->subs)
-    for (DiscLayer& L : sd.layers) { if (L.d_w) cudaFree(L.d_w); if (L.d_b) cudaFree(L.d_b); }
+    for (DiscLayer& L : sd.layers) {
+      if (L.d_w) cudaFree(L.d_w);
+      if (L.d_b) cudaFree(L.d_b);
+      if (L.d_wpk_main) cudaFree(L.d_wpk_main);
+      if (L.d_wpk_lo) cudaFree(L.d_wpk_lo);
+      if (L.d_zero) cudaFree(L.d_zero);
+    }
   if (h->ws) cudaFree(h->ws);
   if (h->d_audio) cudaFree(h->d_audio);
   if (h->d_maps) cudaFree(h->d_maps);
