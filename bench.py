@@ -352,8 +352,11 @@ def main():
         from neuraltexttospeech_b200.synthetic import synthetic_disc_weights
         nb_d, seg = min(B, 32), min(L, 8192)
         seg_wav = wav[:nb_d, :seg].contiguous()
-        drow = {"waveforms": nb_d, "samples": seg, "dtype": "f32", "bound": "fp32 FFMA (CUDA cores)",
-                "peak_tflops": 148 * 128 * 2 * 1.965e-3, "peak_source": "nominal: 148 SMs x 128 FP32 lanes x 2 x 1.965 GHz (not measured)"}
+        # every conv but the first and conv_post runs as 3xTF32 (three tcgen05 kind::tf32 products per fp32 product):
+        # the bound is a third of the TF32 tensor peak, itself taken as half of the measured bf16 peak (not measured)
+        drow = {"waveforms": nb_d, "samples": seg, "dtype": "f32 (3xTF32 on the tensor cores)", "bound": "tensor",
+                "peak_tflops": peaks()["tflops_sustained"] / 2 / 3,
+                "peak_source": "measured bf16 sustained peak / 2 (TF32) / 3 (three products per fp32 product); TF32 peak itself not measured"}
         for kind, cls in (("mpd", MultiPeriodDiscriminator), ("msd", MultiScaleDiscriminator)):
             dm = cls(device=local_rank).load_weights(synthetic_disc_weights(kind, "A"))
             for _ in range(3):
@@ -367,7 +370,7 @@ def main():
             d_ms = f0.elapsed_time(f1) / 5
             fl, by = disc_flops(dm, nb_d, seg)
             drow[kind] = {"ms": d_ms, "gflop": fl / 1e9, "tflops": fl / d_ms / 1e9, "frac": fl / d_ms / 1e9 / drow["peak_tflops"],
-                          "feature_map_mbytes": by / 1e6, "launches": 35 if kind == "mpd" else 26}
+                          "feature_map_mbytes": by / 1e6, "launches": 75 if kind == "mpd" else 62}
             del dm
         adjacent["discriminators"] = drow
 

@@ -49,11 +49,22 @@ struct TfKArgs {
   TcVariant var[kMaxVariants];
   int min_off, nks, n, n_tiles, tiles_q, slab_rows;
   uint32_t idesc, tmem_cols;
+  // extended form (TcArgs::ext_ntaps > 0): a conv of input stride `nph` is nph undilated convs over the phase
+  // sub-sequences x[nph * q + r] (one tensor map per phase r): K-slice s of phase r is one slab, and tap j of that phase
+  // reads it at row offset tap_a[ph_first[r] + j].  A grouped conv reads only its group's channels: K starts at
+  // nt * kbase_per_tile for N tile nt (the N tile is one group's output channels).
+  int ext, nph, kbase_per_tile;
+  int ph_first[5];
+  short tap_a[kTfMaxExtTaps];
 };
+
+__device__ __forceinline__ int tf_ntaps(const TfKArgs& ka, int v, int r) { return ka.ext ? ka.ph_first[r + 1] - ka.ph_first[r] : ka.var[v].ntaps; }
+__device__ __forceinline__ int tf_tap(const TfKArgs& ka, int v, int r, int j) { return ka.ext ? (int)ka.tap_a[ka.ph_first[r] + j] : ka.var[v].tap_off[j]; }
 
 template <int KS>
 __global__ void __launch_bounds__(kTfThreads, 2)
-conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ TfKArgs ka) {
+conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_x1, const __grid_constant__ CUtensorMap tm_x2,
+                 const __grid_constant__ CUtensorMap tm_x3, const __grid_constant__ TfKArgs ka) {
   constexpr int ROWB = KS * 4;
   const int n = ka.n;
   const int slab_bytes = ka.slab_rows * ROWB;
@@ -73,7 +84,10 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
   const int nt = t % ka.n_tiles; t /= ka.n_tiles;
   const int v = t % ka.nvar; t /= ka.nvar;
   const int qt = t % ka.tiles_q; const int b = t / ka.tiles_q;
-  const int ntaps = ka.var[v].ntaps;
+  const int nph = ka.ext ? ka.nph : 1;
+  int ntaps = 0, last_r = 0;                                       // taps per K-slice over all phases; last phase that has taps
+  for (int r = 0; r < nph; ++r) { const int c = tf_ntaps(ka, v, r); ntaps += c; if (c) last_r = r; }
+  const int kbase = nt * ka.kbase_per_tile;
 
   if (tid == 0) {
     for (int s = 0; s < kTfNsl; ++s) { mbar_init(&slab_full[s], 1); mbar_init(&slab_empty[s], 1); }
@@ -91,54 +105,65 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
   if (warp == 0) {
     // ===================== producer: slab slices and weight stages =====================
     const uint8_t* wsrc = reinterpret_cast<const uint8_t*>(ka.var[v].w) + (size_t)nt * ka.nks * ntaps * stage_bytes;
-    uint32_t wcnt = 0;
+    uint32_t wcnt = 0, scnt = 0;
     for (int s = 0; s < ka.nks; ++s) {
-      const int pos = s % kTfNsl;
-      mbar_wait(&slab_empty[pos], ((s / kTfNsl) & 1) ^ 1);
-      if (elect_one()) {
-        mbar_expect_tx(&slab_full[pos], (uint32_t)slab_bytes);
-        tma_load_3d(slab + pos * slab_bytes, &tm_x, s * KS, qt * 128 + ka.min_off, b, &slab_full[pos]);
-      }
-      __syncwarp();
-      for (int j = 0; j < ntaps; ++j, ++wcnt) {
-        const int st = wcnt % kTfNst;
-        mbar_wait(&w_empty[st], ((wcnt / kTfNst) & 1) ^ 1);
+      for (int r = 0; r < nph; ++r) {
+        const int nt_r = tf_ntaps(ka, v, r);
+        if (nt_r == 0) continue;
+        const int pos = scnt % kTfNsl;
+        mbar_wait(&slab_empty[pos], ((scnt / kTfNsl) & 1) ^ 1);
         if (elect_one()) {
-          mbar_expect_tx(&w_full[st], (uint32_t)stage_bytes);
-          bulk_g2s(wst + st * stage_bytes, wsrc, (uint32_t)stage_bytes, &w_full[st]);
+          const CUtensorMap* tm = r == 0 ? &tm_x : (r == 1 ? &tm_x1 : (r == 2 ? &tm_x2 : &tm_x3));
+          mbar_expect_tx(&slab_full[pos], (uint32_t)slab_bytes);
+          tma_load_3d(slab + pos * slab_bytes, tm, kbase + s * KS, qt * 128 + ka.min_off, b, &slab_full[pos]);
         }
         __syncwarp();
-        wsrc += stage_bytes;
+        ++scnt;
+        for (int j = 0; j < nt_r; ++j, ++wcnt) {
+          const int st = wcnt % kTfNst;
+          mbar_wait(&w_empty[st], ((wcnt / kTfNst) & 1) ^ 1);
+          if (elect_one()) {
+            mbar_expect_tx(&w_full[st], (uint32_t)stage_bytes);
+            bulk_g2s(wst + st * stage_bytes, wsrc, (uint32_t)stage_bytes, &w_full[st]);
+          }
+          __syncwarp();
+          wsrc += stage_bytes;
+        }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     const uint32_t slab_addr = smem_u32(slab), wst_addr = smem_u32(wst);
-    uint32_t wcnt = 0, first = 1;
+    uint32_t wcnt = 0, scnt = 0, first = 1;
     for (int s = 0; s < ka.nks; ++s) {
-      const int pos = s % kTfNsl;
-      mbar_wait(&slab_full[pos], (s / kTfNsl) & 1);
-      tc_fence_after();
-      for (int j = 0; j < ntaps; ++j, ++wcnt) {
-        const int st = wcnt % kTfNst;
-        mbar_wait(&w_full[st], (wcnt / kTfNst) & 1);
+      for (int r = 0; r < nph; ++r) {
+        const int nt_r = tf_ntaps(ka, v, r);
+        if (nt_r == 0) continue;
+        const int pos = scnt % kTfNsl;
+        mbar_wait(&slab_full[pos], (scnt / kTfNsl) & 1);
         tc_fence_after();
-        if (elect_one()) {
-          const uint32_t row_off = (uint32_t)(ka.var[v].tap_off[j] - ka.min_off);
-          const uint64_t a0 = make_desc_sw<ROWB>(slab_addr + pos * slab_bytes + row_off * ROWB);
-          const uint64_t b0 = make_desc(wst_addr + st * stage_bytes, (uint32_t)n * 16u, 128u);
+        ++scnt;
+        for (int j = 0; j < nt_r; ++j, ++wcnt) {
+          const int st = wcnt % kTfNst;
+          mbar_wait(&w_full[st], (wcnt / kTfNst) & 1);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t row_off = (uint32_t)(tf_tap(ka, v, r, j) - ka.min_off);
+            const uint64_t a0 = make_desc_sw<ROWB>(slab_addr + pos * slab_bytes + row_off * ROWB);
+            const uint64_t b0 = make_desc(wst_addr + st * stage_bytes, (uint32_t)n * 16u, 128u);
 #pragma unroll
-          for (int kk = 0; kk < KS / 8; ++kk) {
-            umma_tf32(tmem_base, a0 + (uint64_t)((kk * 32) >> 4), b0 + (uint64_t)((kk * 2 * n * 16) >> 4), ka.idesc, (first && kk == 0) ? 0u : 1u);
+            for (int kk = 0; kk < KS / 8; ++kk) {
+              umma_tf32(tmem_base, a0 + (uint64_t)((kk * 32) >> 4), b0 + (uint64_t)((kk * 2 * n * 16) >> 4), ka.idesc, (first && kk == 0) ? 0u : 1u);
+            }
+            umma_commit(&w_empty[st]);
+            if (j == nt_r - 1) {
+              umma_commit(&slab_empty[pos]);
+              if (s == ka.nks - 1 && r == last_r) umma_commit(acc_full);
+            }
           }
-          umma_commit(&w_empty[st]);
-          if (j == ntaps - 1) {
-            umma_commit(&slab_empty[pos]);
-            if (s == ka.nks - 1) umma_commit(acc_full);
-          }
+          first = 0;
+          __syncwarp();
         }
-        first = 0;
-        __syncwarp();
       }
     }
   } else {
@@ -204,6 +229,28 @@ EncodeTiledFn tf_encode_fn() {
 }
 
 inline int tf_ks(int c_in) { return c_in >= 32 ? 32 : c_in; }
+
+// Extended form: tap j at input-row offset off[j] of a stride-s conv belongs to phase r = off mod s and reads phase row
+// q + a with a = (off - r) / s.  Taps are processed phase by phase, in their given order inside a phase.
+struct TfPhases { int order[kTfMaxExtTaps]; int a[kTfMaxExtTaps]; int first[5]; int min_a, max_a; };
+inline bool tf_phases(const int* off, int ntaps, int stride, TfPhases* p) {
+  if (ntaps < 1 || ntaps > kTfMaxExtTaps || stride < 1 || stride > 4) return false;
+  int n = 0;
+  p->min_a = 1 << 30; p->max_a = -(1 << 30);
+  for (int r = 0; r < 4; ++r) {
+    p->first[r] = n;
+    if (r >= stride) continue;
+    for (int j = 0; j < ntaps; ++j) {
+      const int rr = ((off[j] % stride) + stride) % stride;
+      if (rr != r) continue;
+      const int a = (off[j] - rr) / stride;
+      p->order[n] = j; p->a[n] = a; ++n;
+      p->min_a = a < p->min_a ? a : p->min_a; p->max_a = a > p->max_a ? a : p->max_a;
+    }
+  }
+  p->first[4] = n;
+  return n == ntaps;
+}
 inline int tf_n(int c_out) { return c_out > 128 ? 128 : c_out; }
 
 template <int KS>
@@ -219,11 +266,26 @@ cudaError_t tf_launch(const TcArgs& a, cudaStream_t s) {
     ka.var[v] = a.var[v];
     for (int j = 0; j < a.var[v].ntaps; ++j) { mn = a.var[v].tap_off[j] < mn ? a.var[v].tap_off[j] : mn; mx = a.var[v].tap_off[j] > mx ? a.var[v].tap_off[j] : mx; }
   }
+  const bool ext = a.ext_ntaps > 0;
+  const int stride = ext ? a.in_stride : 1;
+  const int groups = ext && a.groups > 1 ? a.groups : 1;
+  if (ext) {
+    TfPhases ph;
+    if (a.nvar != 1 || a.out_stride != 1 || !a.ext_tap_off || !tf_phases(a.ext_tap_off, a.ext_ntaps, stride, &ph)) return cudaErrorInvalidValue;
+    if (a.x_rows < stride || a.c_in % groups || a.c_out % groups || a.cin_g != a.c_in / groups) return cudaErrorInvalidValue;
+    ka.ext = 1; ka.nph = stride;
+    for (int r = 0; r < 5; ++r) ka.ph_first[r] = ph.first[r];
+    for (int j = 0; j < a.ext_ntaps; ++j) ka.tap_a[j] = (short)ph.a[j];
+    ka.var[0].out_off = 0; ka.var[0].ntaps = a.ext_ntaps;
+    mn = ph.min_a; mx = ph.max_a;
+  }
   if (mx - mn > kTfMaxSpan) return cudaErrorInvalidValue;
   if (!(a.out_slope > 0.f && a.out_slope <= 1.f) || (a.res && !(a.res_inv >= 1.f))) return cudaErrorInvalidValue;
   if ((a.res || a.res2) && a.out_stride != 1) return cudaErrorInvalidValue;
   ka.min_off = mn;
-  ka.n = tf_n(a.c_out); ka.n_tiles = a.c_out / ka.n; ka.nks = a.c_in / KS;
+  ka.n = groups > 1 ? a.c_out / groups : tf_n(a.c_out); ka.n_tiles = a.c_out / ka.n; ka.nks = (ext ? a.cin_g : a.c_in) / KS;
+  ka.kbase_per_tile = groups > 1 ? a.cin_g : 0;
+  if (!(ka.n == 16 || (ka.n % 32 == 0 && ka.n <= 128))) return cudaErrorInvalidValue;
   ka.tiles_q = (a.n_q + 127) / 128;
   ka.slab_rows = (128 + (mx - mn) + 7) & ~7;
   ka.idesc = tf32_idesc(ka.n);
@@ -231,14 +293,17 @@ cudaError_t tf_launch(const TcArgs& a, cudaStream_t s) {
   const size_t smem = (size_t)kTfNsl * ka.slab_rows * KS * 4 + (size_t)kTfNst * KS * ka.n * 4 + (2 * kTfNsl + 2 * kTfNst + 1) * 8 + 16;
   EncodeTiledFn fn = tf_encode_fn();
   if (!fn) return cudaErrorNotSupported;
-  CUtensorMap tm_x;
-  {
-    cuuint64_t gdim[3] = {(cuuint64_t)a.c_in, (cuuint64_t)a.x_rows, (cuuint64_t)a.B};
-    cuuint64_t gstr[2] = {(cuuint64_t)a.c_in * 4, (cuuint64_t)a.c_in * 4 * (cuuint64_t)a.x_rows};
+  CUtensorMap tm[4];
+  for (int r = 0; r < 4; ++r) {
+    if (r >= stride) { tm[r] = tm[0]; continue; }
+    // phase r of a stride-s conv: rows r, r + s, r + 2 s, ... of every sequence (row pitch s * c_in)
+    cuuint64_t gdim[3] = {(cuuint64_t)a.c_in, (cuuint64_t)((a.x_rows - r + stride - 1) / stride), (cuuint64_t)a.B};
+    cuuint64_t gstr[2] = {(cuuint64_t)a.c_in * 4 * (cuuint64_t)stride, (cuuint64_t)a.c_in * 4 * (cuuint64_t)a.x_rows};
     cuuint32_t box[3] = {(cuuint32_t)KS, (cuuint32_t)ka.slab_rows, 1};
     cuuint32_t est[3] = {1, 1, 1};
     const CUtensorMapSwizzle sw = KS == 32 ? CU_TENSOR_MAP_SWIZZLE_128B : (KS == 16 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
-    if (fn(&tm_x, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(a.x), gdim, gstr, box, est, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+    void* base = const_cast<float*>(reinterpret_cast<const float*>(a.x) + (size_t)r * a.c_in);
+    if (fn(&tm[r], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, base, gdim, gstr, box, est, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return cudaErrorNotSupported;
   }
   auto kern = conv_tf32_kernel<KS>;
@@ -253,7 +318,7 @@ cudaError_t tf_launch(const TcArgs& a, cudaStream_t s) {
   }
   const long long tiles = (long long)a.B * ka.tiles_q * a.nvar * ka.n_tiles;
   if (tiles > 0x7fffffffLL) return cudaErrorInvalidValue;
-  kern<<<(unsigned)tiles, kTfThreads, smem, s>>>(tm_x, ka);
+  kern<<<(unsigned)tiles, kTfThreads, smem, s>>>(tm[0], tm[1], tm[2], tm[3], ka);
   return cudaGetLastError();
 }
 
@@ -288,9 +353,48 @@ void tf32_pack_weights(const float* w, int ntaps, int c_in, int c_out, void* dst
             }
 }
 
+bool tf32_ext_supported(int c_in, int c_out, int groups, int in_stride, int ntaps, const int* tap_off) {
+  TfPhases ph;
+  if (groups < 1 || c_in % groups || c_out % groups || !tap_off || !tf_phases(tap_off, ntaps, in_stride, &ph)) return false;
+  if (ph.max_a - ph.min_a > kTfMaxSpan) return false;
+  const int cin_g = c_in / groups, n = groups > 1 ? c_out / groups : tf_n(c_out);
+  if (!(cin_g == 8 || cin_g == 16 || (cin_g >= 32 && cin_g % 32 == 0))) return false;
+  if (groups == 1 && c_out % n) return false;
+  return n == 16 || (n % 32 == 0 && n <= 128);
+}
+
+// w fp32 [ntaps][cin_g][c_out] -> [n-tile][K-slice][tap, phase-major][KS/4 chunks][N rows][4 floats], TF32-rounded
+void tf32_pack_weights_ext(const float* w, int ntaps, const int* tap_off, int in_stride, int cin_g, int c_out, int groups, void* dst_host) {
+  float* dst = reinterpret_cast<float*>(dst_host);
+  TfPhases ph;
+  if (!tf_phases(tap_off, ntaps, in_stride, &ph)) return;
+  const int ks = tf_ks(cin_g), n = groups > 1 ? c_out / groups : tf_n(c_out);
+  size_t o = 0;
+  for (int nt = 0; nt < c_out / n; ++nt)
+    for (int s = 0; s < cin_g / ks; ++s)
+      for (int t = 0; t < ntaps; ++t)
+        for (int chunk = 0; chunk < ks / 4; ++chunk)
+          for (int row = 0; row < n; ++row)
+            for (int e = 0; e < 4; ++e) {
+              const int ci = s * ks + chunk * 4 + e, co = nt * n + row;
+              float f = w[((size_t)ph.order[t] * cin_g + ci) * c_out + co];
+              uint32_t u; memcpy(&u, &f, 4);
+              u = (u + 0x0FFFu + ((u >> 13) & 1u)) & ~0x1FFFu;
+              memcpy(&f, &u, 4);
+              dst[o++] = f;
+            }
+}
+
 cudaError_t launch_conv_tf32(const TcArgs& a, cudaStream_t s) {
   if (a.nvar < 1 || a.nvar > kMaxVariants) return cudaErrorInvalidValue;
   if (a.B <= 0 || a.n_q <= 0) return cudaSuccess;
+  if (a.ext_ntaps > 0) {
+    if (!tf32_ext_supported(a.c_in, a.c_out, a.groups > 1 ? a.groups : 1, a.in_stride, a.ext_ntaps, a.ext_tap_off)) return cudaErrorInvalidValue;
+    const int ks = tf_ks(a.cin_g);
+    if (ks == 32) return tf_launch<32>(a, s);
+    if (ks == 16) return tf_launch<16>(a, s);
+    return tf_launch<8>(a, s);
+  }
   int mxt = 0;
   for (int v = 0; v < a.nvar; ++v) mxt = a.var[v].ntaps > mxt ? a.var[v].ntaps : mxt;
   if (!tf32_supported(a.c_in, a.c_out, mxt, 0)) return cudaErrorInvalidValue;

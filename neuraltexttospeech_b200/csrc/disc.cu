@@ -14,12 +14,14 @@
 // Kernels: disc_split_kernel (reflect pad + period split), disc_pool_kernel (AveragePooling1D(4, 2, "same")),
 // disc_conv_kernel (strided, grouped Conv1D with TensorFlow SAME / VALID padding, bias and LeakyReLU fused),
 // disc_post_kernel (C_out = 1).
-// The dense stride-1 layers (1024 -> 1024, k = 5: 45 % of the MultiPeriodDiscriminator's FLOPs) run on the tensor cores at
-// fp32 accuracy ("3xTF32"): tcgen05.mma.kind::tf32 reads only the top 10 mantissa bits of an fp32 operand, so with
+// Every conv with at least 8 input channels per group and more than one output channel (all but the first conv and
+// conv_post of each sub-discriminator: > 99 % of the FLOPs) runs on the tensor cores at fp32 accuracy ("3xTF32"): tcgen05.mma.kind::tf32 reads only the top 10 mantissa bits of an fp32 operand, so with
 // x = x_hi + x_lo (x_hi = what the tensor core sees, x_lo = the exact remainder) and w = w_hi + w_lo likewise,
 //     x . w  ~=  x_hi . w_hi + x_hi . w_lo + x_lo . w_hi          (dropped: x_lo . w_lo, ~2^-22 relative)
 // is three TF32 products accumulated in fp32 in TMEM: conv_tf32.cu's kernel run twice (x_lo with w_hi taps into a scratch
-// map, then x with [w_hi | w_lo] as 2k taps + that scratch + bias + LeakyReLU).  HFG_DISC_TC=0 keeps every layer on FFMA.
+// map, then x with [w_hi | w_lo] as 2k taps + that scratch + bias + LeakyReLU).  Its extended form takes the stride as
+// `stride` undilated convs over the phase sub-sequences of the input (one TMA map per phase) and a grouped conv as N tiles
+// that read only their group's K range.  HFG_DISC_TC=0 keeps every layer on the FFMA kernel above.
 #include <algorithm>
 #include <cmath>
 #include <cstdarg>
@@ -326,9 +328,12 @@ struct DiscLayer {
   std::vector<float> v, g, b, w;        // as set by the caller (w: stored kernel, used as is)
   float* d_w = nullptr;                 // folded [k][cin_g][cout]
   float* d_b = nullptr;
-  bool tc = false;                      // dense stride-1 layer on the tensor cores (3xTF32)
-  void* d_wpk_main = nullptr;           // tf32_pack_weights image of [w_hi taps | w_lo taps] (2k taps)
-  void* d_wpk_lo = nullptr;             // tf32_pack_weights image of w_hi (k taps), for the x_lo pass
+  bool tc = false;                      // on the tensor cores (3xTF32): every conv with c_in / groups >= 8 and c_out > 1
+  std::vector<float> hi_lo;             // host [w_hi taps | w_lo taps], 2 * k * cin_g * cout floats
+  struct Packed { void* main = nullptr; void* lo = nullptr; };
+  // packed weight images, keyed by the left pad: with a stride, TensorFlow's SAME pad depends on the input length, the
+  // pad decides which input phase each tap reads, and the kernel wants its taps phase by phase.  Built on first use.
+  std::map<int, Packed> packed;
   float* d_zero = nullptr;              // zero bias of the x_lo pass
 };
 
@@ -483,7 +488,23 @@ int run_disc_forward(hfg_disc_ctx* h, const float* audio, int B, long long T, fl
       a.k = L.spec.k; a.stride = L.spec.stride; a.pad_left = left;
       a.out_slope = l + 1 == sd.layers.size() ? 1.0f : kSlope;        // conv_post has no activation (model.py:241 / 342)
       cudaError_t e;
-      if (L.tc) {
+      if (L.tc && n >= L.spec.stride) {
+        const int k = L.spec.k;
+        int off[2 * 41];
+        for (int j = 0; j < k; ++j) off[j] = off[j + k] = j - left;
+        auto it = L.packed.find(left);
+        if (it == L.packed.end()) {                              // first use of this pad: pack and upload (synchronous)
+          const size_t kel = (size_t)k * a.cin_g * a.cout;
+          std::vector<float> pk(2 * kel);
+          DiscLayer::Packed pw;
+          hfg::tf32_pack_weights_ext(L.hi_lo.data(), 2 * k, off, L.spec.stride, a.cin_g, a.cout, L.spec.groups, pk.data());
+          DISC_CUDA_TRY(h, cudaMalloc(&pw.main, 2 * kel * sizeof(float)));
+          DISC_CUDA_TRY(h, cudaMemcpy(pw.main, pk.data(), 2 * kel * sizeof(float), cudaMemcpyHostToDevice));
+          hfg::tf32_pack_weights_ext(L.hi_lo.data(), k, off, L.spec.stride, a.cin_g, a.cout, L.spec.groups, pk.data());
+          DISC_CUDA_TRY(h, cudaMalloc(&pw.lo, kel * sizeof(float)));
+          DISC_CUDA_TRY(h, cudaMemcpy(pw.lo, pk.data(), kel * sizeof(float), cudaMemcpyHostToDevice));
+          it = const_cast<DiscLayer&>(L).packed.emplace(left, pw).first;
+        }
         const long long n4 = (long long)n_seq * n * L.spec.cin / 4;
         disc_lo_kernel<<<(unsigned)std::min<long long>((n4 + 255) / 256, 148 * 8), 256, 0, s>>>(
             reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(ws_lo), n4);
@@ -491,13 +512,12 @@ int run_disc_forward(hfg_disc_ctx* h, const float* audio, int B, long long T, fl
         hfg::TcArgs t{};
         t.B = n_seq; t.x_rows = (int)n; t.n_q = (int)n_out; t.out_rows = (int)n_out; t.out_stride = 1;
         t.c_in = L.spec.cin; t.c_out = L.spec.cout; t.res_inv = 1.0f; t.out_scale = 1.0f; t.raw_out = 1; t.nvar = 1;
-        t.var[0].out_off = 0;
-        for (int j = 0; j < L.spec.k; ++j) t.var[0].tap_off[j] = t.var[0].tap_off[j + L.spec.k] = j - left;
+        t.in_stride = L.spec.stride; t.cin_g = a.cin_g; t.groups = L.spec.groups; t.ext_tap_off = off;
         // pass 1: partial = x_lo . w_hi
-        t.x = ws_lo; t.out = ws_part; t.bias = L.d_zero; t.out_slope = 1.0f; t.var[0].w = L.d_wpk_lo; t.var[0].ntaps = L.spec.k;
+        t.x = ws_lo; t.out = ws_part; t.bias = L.d_zero; t.out_slope = 1.0f; t.var[0].w = it->second.lo; t.ext_ntaps = k;
         if (e == cudaSuccess) e = hfg::launch_conv_tf32(t, s);
         // pass 2: out = lrelu(bias + x_hi . w_hi + x_hi . w_lo + partial)
-        t.x = x; t.out = a.out; t.bias = L.d_b; t.res2 = ws_part; t.out_slope = a.out_slope; t.var[0].w = L.d_wpk_main; t.var[0].ntaps = 2 * L.spec.k;
+        t.x = x; t.out = a.out; t.bias = L.d_b; t.res2 = ws_part; t.out_slope = a.out_slope; t.var[0].w = it->second.main; t.ext_ntaps = 2 * k;
         if (e == cudaSuccess) e = hfg::launch_conv_tf32(t, s);
       } else {
         e = launch_conv(a, s);
@@ -596,27 +616,26 @@ int hfg_disc_finalize_weights(hfg_disc_handle h) {
       DISC_CUDA_TRY(h, cudaMemcpy(L.d_w, w.data(), kel * sizeof(float), cudaMemcpyHostToDevice));
       DISC_CUDA_TRY(h, cudaMalloc((void**)&L.d_b, bias.size() * sizeof(float)));
       DISC_CUDA_TRY(h, cudaMemcpy(L.d_b, bias.data(), bias.size() * sizeof(float), cudaMemcpyHostToDevice));
-      // dense stride-1 layers: tensor cores at fp32 accuracy (3xTF32, see the header of this file)
-      if (L.d_wpk_main) cudaFree(L.d_wpk_main);
-      if (L.d_wpk_lo) cudaFree(L.d_wpk_lo);
+      // tensor cores at fp32 accuracy (3xTF32, see the header of this file); weight images are packed on first use
+      for (auto& kv : L.packed) { if (kv.second.main) cudaFree(kv.second.main); if (kv.second.lo) cudaFree(kv.second.lo); }
+      L.packed.clear();
       if (L.d_zero) cudaFree(L.d_zero);
-      L.d_wpk_main = L.d_wpk_lo = nullptr; L.d_zero = nullptr;
-      L.tc = h->use_tc && L.spec.stride == 1 && L.spec.groups == 1 && cout >= 128 && cout % 128 == 0 && 2 * L.spec.k <= hfg::kMaxTaps &&
-             hfg::tf32_supported(L.spec.cin, cout, 2 * L.spec.k, L.spec.k - 1);
+      L.d_zero = nullptr;
+      L.hi_lo.clear();
+      {
+        int off[2 * 41];
+        for (int j = 0; j < L.spec.k; ++j) off[j] = off[j + L.spec.k] = j - (L.spec.k - 1) / 2;
+        L.tc = h->use_tc && cout > 1 && L.spec.k <= 41 && L.spec.cin % 4 == 0 &&
+               hfg::tf32_ext_supported(L.spec.cin, cout, L.spec.groups, L.spec.stride, 2 * L.spec.k, off);
+      }
       if (L.tc) {
-        std::vector<float> both(2 * kel), pk(2 * kel);
+        L.hi_lo.resize(2 * kel);
         for (size_t i = 0; i < kel; ++i) {
           uint32_t u; memcpy(&u, &w[i], 4);
-          u = (u + 0x0FFFu + ((u >> 13) & 1u)) & ~0x1FFFu;      // w_hi: round to nearest even at 10 mantissa bits (= tf32_pack_weights)
+          u = (u + 0x0FFFu + ((u >> 13) & 1u)) & ~0x1FFFu;      // w_hi: round to nearest even at 10 mantissa bits
           float hi; memcpy(&hi, &u, 4);
-          both[i] = hi; both[kel + i] = w[i] - hi;              // w_lo: exact in fp32
+          L.hi_lo[i] = hi; L.hi_lo[kel + i] = w[i] - hi;        // w_lo: exact in fp32
         }
-        hfg::tf32_pack_weights(both.data(), 2 * L.spec.k, L.spec.cin, cout, pk.data());
-        DISC_CUDA_TRY(h, cudaMalloc(&L.d_wpk_main, 2 * kel * sizeof(float)));
-        DISC_CUDA_TRY(h, cudaMemcpy(L.d_wpk_main, pk.data(), 2 * kel * sizeof(float), cudaMemcpyHostToDevice));
-        hfg::tf32_pack_weights(both.data(), L.spec.k, L.spec.cin, cout, pk.data());
-        DISC_CUDA_TRY(h, cudaMalloc(&L.d_wpk_lo, kel * sizeof(float)));
-        DISC_CUDA_TRY(h, cudaMemcpy(L.d_wpk_lo, pk.data(), kel * sizeof(float), cudaMemcpyHostToDevice));
         DISC_CUDA_TRY(h, cudaMalloc((void**)&L.d_zero, cout * sizeof(float)));
         DISC_CUDA_TRY(h, cudaMemset(L.d_zero, 0, cout * sizeof(float)));
       }
@@ -691,8 +710,7 @@ void hfg_disc_destroy(hfg_disc_handle h) {
     for (DiscLayer& L : sd.layers) {
       if (L.d_w) cudaFree(L.d_w);
       if (L.d_b) cudaFree(L.d_b);
-      if (L.d_wpk_main) cudaFree(L.d_wpk_main);
-      if (L.d_wpk_lo) cudaFree(L.d_wpk_lo);
+      for (auto& kv : L.packed) { if (kv.second.main) cudaFree(kv.second.main); if (kv.second.lo) cudaFree(kv.second.lo); }
       if (L.d_zero) cudaFree(L.d_zero);
     }
   if (h->ws) cudaFree(h->ws);

@@ -108,7 +108,14 @@ struct TcArgs {
   int16_t* post_pcm;    // conv_post mode, when non-NULL: 16-bit PCM [B, n_q*post_f] instead of post_out
   int raw_out;          // TF32 kernel only: 1 = store the result unrounded (the running MRF sum is never an MMA operand)
   const void* w_base;   // allocation holding every variant's packed weights (256-byte aligned; the CTA-pair
-  size_t w_bytes;       // configurations read it through one TMA map), and its size (multiple of 256)
+  size_t w_bytes;       // configurations read it through one TMA map), and its size (multiple of 256)  // TF32 kernel only, extended form (discriminator layers, disc.cu): a strided and / or grouped Conv1D with up to
+  // kTfMaxExtTaps taps.  ext_ntaps > 0 selects it: nvar must be 1 and var[0].tap_off / ntaps are ignored.
+  //   out[b, q, co] = sum_j sum_ci x[b, q * in_stride + ext_tap_off[j], g(co) * cin_g + ci] * w[j][ci][co]
+  const int* ext_tap_off;   // host array [ext_ntaps]: input-row offset of tap j (j - pad_left; taps may repeat an offset)
+  int ext_ntaps;
+  int in_stride;            // 1..4
+  int cin_g;                // input channels per group (= c_in for a dense conv); the N tile is c_out / groups when grouped
+  int groups;
 };
 struct TcConfig {       // tile configuration chosen for (c_in, c_out); see conv_tc.cu
   int n, mb, ks, kbw, tps, nst, nsl, nstg, cg;   // cg = 2: CTA pairs (cta_group::2)
@@ -128,6 +135,11 @@ void tc_set_trace(long long* dev);   // debug builds (-DHFG_TC_TRACE): device bu
 bool tf32_supported(int c_in, int c_out, int ntaps, int span);
 size_t tf32_packed_weight_bytes(int c_in, int c_out, int ntaps);
 void tf32_pack_weights(const float* w, int ntaps, int c_in, int c_out, void* dst_host);
+constexpr int kTfMaxExtTaps = 96;
+// extended form: w fp32 [ntaps][cin_g][c_out] (Keras grouped-kernel layout), tap offsets as in TcArgs::ext_tap_off; the
+// packed image has ntaps * cin_g * c_out floats.  tf32_ext_supported also needs x_rows >= in_stride at launch time.
+bool tf32_ext_supported(int c_in, int c_out, int groups, int in_stride, int ntaps, const int* tap_off);
+void tf32_pack_weights_ext(const float* w, int ntaps, const int* tap_off, int in_stride, int cin_g, int c_out, int groups, void* dst_host);
 cudaError_t launch_conv_tf32(const TcArgs& a, cudaStream_t s);
 
 // ---------------------------------------------------------------- fused ResBlock1 iteration (resblock_tc.cu)

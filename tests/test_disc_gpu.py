@@ -8,9 +8,10 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-TOL = 1e-4            # max |cuda - oracle| per feature map, relative to that map's max |value|.  fp32 FFMA layers differ from
-                      # torch-CPU fp32 by summation order only (measured <= 4e-6); the dense layers on the tensor cores (3xTF32)
-                      # add the accumulator's truncating fp32 adds over 1 280 K-steps (measured <= 3.9e-5)
+TOL = 2e-4            # max |cuda - oracle| per feature map, relative to that map's max |value|.  The FFMA kernels differ from
+                      # torch-CPU fp32 by summation order only (measured <= 4e-6, TOL_FFMA); the default build runs every conv
+                      # but the first and conv_post on the tensor cores as 3xTF32, whose fp32 accumulator truncates instead of
+                      # rounding: measured <= 6.2e-5 over up to six such layers (plain TF32, TensorFlow's GPU default, is ~1e-3)
 TOL_FFMA = 2e-5
 
 
@@ -129,8 +130,8 @@ def test_errors():
 
 @pytest.mark.parametrize("kind", ["mpd", "msd"])
 def test_tensor_core_layers_match_the_ffma_path(kind, monkeypatch):
-    """The dense stride-1 layers run as 3xTF32 on the tensor cores by default; HFG_DISC_TC=0 keeps them on the FFMA
-    kernel.  Both must sit inside the oracle tolerance, and within it of each other, on every map from that layer on."""
+    """Strided, grouped and dense convs run as 3xTF32 on the tensor cores by default; HFG_DISC_TC=0 keeps them on the FFMA
+    kernel.  Both must sit inside their oracle tolerance, and within TOL of each other on every map."""
     from oracle import disc_oracle as D
     y = _waveform(2, 4099, seed=11)
     model_tc, w = _model(kind, "reference", "B")
@@ -142,12 +143,11 @@ def test_tensor_core_layers_match_the_ffma_path(kind, monkeypatch):
     o_scores, o_fmaps = (D.mpd_forward if kind == "mpd" else D.msd_forward)(w, y, compat="reference")
     _compare(s_tc, f_tc, o_scores, o_fmaps, (kind, "3xTF32"))
     _compare(s_ff, f_ff, o_scores, o_fmaps, (kind, "ffma"), tol=TOL_FFMA)
-    dense = 4 if kind == "mpd" else 6                         # index of the 1024 -> 1024, k = 5 conv
     differs = False
     for fa, fb in zip(f_tc, f_ff):
         for l, (a, b) in enumerate(zip(fa, fb)):
-            if l < dense:
-                assert np.array_equal(a, b)                   # the layers before it run the same kernel in both
+            if l == 0:
+                assert np.array_equal(a, b)                   # c_in = 1: the same FFMA kernel in both
             else:
                 differs = differs or not np.array_equal(a, b)
                 assert np.abs(a - b).max() <= TOL * np.abs(b).max()
