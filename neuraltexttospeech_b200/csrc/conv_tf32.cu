@@ -54,6 +54,10 @@ struct TfKArgs {
   // reads it at row offset tap_a[ph_first[r] + j].  A grouped conv reads only its group's channels: K starts at
   // nt * kbase_per_tile for N tile nt (the N tile is one group's output channels).
   int ext, nph, kbase_per_tile;
+  // short sequences (extended form): a 128-row M tile = pack_s consecutive sequences x pack_r slab rows each (one TMA box
+  // [KS, pack_r, pack_s], rows outside a sequence zero-filled per sequence); tile row m = sequence m / pack_r, row
+  // m % pack_r, of which the first tq are outputs (the others read the next chunk through their taps and are dropped)
+  int pack_r, pack_s, tq, n_seq, load_bytes;
   int ph_first[5];
   short tap_a[kTfMaxExtTaps];
 };
@@ -114,8 +118,8 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
         mbar_wait(&slab_empty[pos], ((scnt / kTfNsl) & 1) ^ 1);
         if (elect_one()) {
           const CUtensorMap* tm = r == 0 ? &tm_x : (r == 1 ? &tm_x1 : (r == 2 ? &tm_x2 : &tm_x3));
-          mbar_expect_tx(&slab_full[pos], (uint32_t)slab_bytes);
-          tma_load_3d(slab + pos * slab_bytes, tm, kbase + s * KS, qt * 128 + ka.min_off, b, &slab_full[pos]);
+          mbar_expect_tx(&slab_full[pos], (uint32_t)ka.load_bytes);
+          tma_load_3d(slab + pos * slab_bytes, tm, kbase + s * KS, qt * ka.tq + ka.min_off, b * ka.pack_s, &slab_full[pos]);
         }
         __syncwarp();
         ++scnt;
@@ -170,11 +174,13 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
     // ===================== epilogue: thread = output row =====================
     const int quarter = warp & 3;
     const int er = quarter * 32 + lane;
-    const int q = qt * 128 + er;
-    const bool valid = q < ka.n_q;
+    const int sl = er / ka.pack_r, ql = er - sl * ka.pack_r;         // unpacked: pack_r = 128, pack_s = 1, tq = 128
+    const int q = qt * ka.tq + ql;
+    const int bs = b * ka.pack_s + sl;
+    const bool valid = q < ka.n_q && ql < ka.tq && sl < ka.pack_s && bs < ka.n_seq;
     const uint32_t taddr = tmem_base + (((uint32_t)(quarter * 32)) << 16);
     const int n0 = nt * n;
-    const size_t orow = ((size_t)b * ka.out_rows + (size_t)q * ka.out_stride + ka.var[v].out_off) * ka.c_out + n0;
+    const size_t orow = ((size_t)bs * ka.out_rows + (size_t)q * ka.out_stride + ka.var[v].out_off) * ka.c_out + n0;
     mbar_wait(acc_full, 0);
     tc_fence_after();
     const int cw = n >= 32 ? 32 : 16;
@@ -286,8 +292,20 @@ cudaError_t tf_launch(const TcArgs& a, cudaStream_t s) {
   ka.n = groups > 1 ? a.c_out / groups : tf_n(a.c_out); ka.n_tiles = a.c_out / ka.n; ka.nks = (ext ? a.cin_g : a.c_in) / KS;
   ka.kbase_per_tile = groups > 1 ? a.cin_g : 0;
   if (!(ka.n == 16 || (ka.n % 32 == 0 && ka.n <= 128))) return cudaErrorInvalidValue;
-  ka.tiles_q = (a.n_q + 127) / 128;
+  ka.pack_r = 128; ka.pack_s = 1; ka.tq = 128; ka.n_seq = a.B;
+  if (ext && a.B > 1) {
+    // many short sequences (deep DiscriminatorP layers: 15-50 rows): chunks of tq outputs + span halo rows, as many
+    // chunks as fit 128 MMA rows; kept only when it fills the M tile better than one sequence per tile
+    const int span = mx - mn;
+    const int tq = a.n_q < 128 - span ? a.n_q : 128 - span;
+    const int r = tq + span, sq = 128 / r;
+    const long long plain = (long long)a.B * ((a.n_q + 127) / 128);
+    const long long packed = (long long)((a.B + sq - 1) / sq) * ((a.n_q + tq - 1) / tq);
+    if (sq >= 2 && packed * 10 <= plain * 8) { ka.pack_r = r; ka.pack_s = sq; ka.tq = tq; }
+  }
+  ka.tiles_q = (a.n_q + ka.tq - 1) / ka.tq;
   ka.slab_rows = (128 + (mx - mn) + 7) & ~7;
+  ka.load_bytes = (ka.pack_s > 1 ? ka.pack_s * ka.pack_r : ka.slab_rows) * KS * 4;
   ka.idesc = tf32_idesc(ka.n);
   ka.tmem_cols = ka.n <= 32 ? 32 : (ka.n <= 64 ? 64 : 128);
   const size_t smem = (size_t)kTfNsl * ka.slab_rows * KS * 4 + (size_t)kTfNst * KS * ka.n * 4 + (2 * kTfNsl + 2 * kTfNst + 1) * 8 + 16;
@@ -299,7 +317,7 @@ cudaError_t tf_launch(const TcArgs& a, cudaStream_t s) {
     // phase r of a stride-s conv: rows r, r + s, r + 2 s, ... of every sequence (row pitch s * c_in)
     cuuint64_t gdim[3] = {(cuuint64_t)a.c_in, (cuuint64_t)((a.x_rows - r + stride - 1) / stride), (cuuint64_t)a.B};
     cuuint64_t gstr[2] = {(cuuint64_t)a.c_in * 4 * (cuuint64_t)stride, (cuuint64_t)a.c_in * 4 * (cuuint64_t)a.x_rows};
-    cuuint32_t box[3] = {(cuuint32_t)KS, (cuuint32_t)ka.slab_rows, 1};
+    cuuint32_t box[3] = {(cuuint32_t)KS, (cuuint32_t)(ka.pack_s > 1 ? ka.pack_r : ka.slab_rows), (cuuint32_t)ka.pack_s};
     cuuint32_t est[3] = {1, 1, 1};
     const CUtensorMapSwizzle sw = KS == 32 ? CU_TENSOR_MAP_SWIZZLE_128B : (KS == 16 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
     void* base = const_cast<float*>(reinterpret_cast<const float*>(a.x) + (size_t)r * a.c_in);
@@ -316,7 +334,7 @@ cudaError_t tf_launch(const TcArgs& a, cudaStream_t s) {
     if (e != cudaSuccess) return e;
     configured[dev] = smem;
   }
-  const long long tiles = (long long)a.B * ka.tiles_q * a.nvar * ka.n_tiles;
+  const long long tiles = (long long)((a.B + ka.pack_s - 1) / ka.pack_s) * ka.tiles_q * a.nvar * ka.n_tiles;
   if (tiles > 0x7fffffffLL) return cudaErrorInvalidValue;
   kern<<<(unsigned)tiles, kTfThreads, smem, s>>>(tm[0], tm[1], tm[2], tm[3], ka);
   return cudaGetLastError();
