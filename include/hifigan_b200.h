@@ -265,7 +265,11 @@ int hfg_disc_num_maps(hfg_disc_handle h, int* out);
  * axes 1 and 2 of the view (model.py:235 reshapes to [b, t / period, period, c]).  offsets / dims may be NULL. */
 int hfg_disc_layout(hfg_disc_handle h, int B, long long T, long long* offsets, long long* dims, long long* total_floats);
 
-/* audio_dev: device fp32 [B, T] (the reference's [B, T, 1]); maps_dev: device fp32 [total_floats]; asynchronous on `stream`. */
+/* audio_dev: device fp32 [B, T] (the reference's [B, T, 1]); maps_dev: device fp32 [total_floats]; asynchronous on `stream`.
+ * Arithmetic: fp32 results; every conv but the first (C_in = 1) and conv_post (C_out = 1) of a sub-discriminator runs on the
+ * tensor cores as three TF32 products per fp32 product (within 2e-4 of the fp32 oracle per map, measured <= 6.2e-5;
+ * environment HFG_DISC_TC=0 at hfg_disc_create keeps everything on fp32 FFMA, <= 2e-5).  The first forward of a new
+ * (B, T) may allocate scratch and upload weight images (synchronously); forwards on one handle must not overlap. */
 int hfg_disc_forward(hfg_disc_handle h, const float* audio_dev, int B, long long T, float* maps_dev, void* stream);
 /* Same with HOST buffers (H2D, kernels, D2H, synchronise). */
 int hfg_disc_forward_host(hfg_disc_handle h, const float* audio_host, int B, long long T, float* maps_host);
