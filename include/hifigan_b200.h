@@ -274,6 +274,13 @@ int hfg_disc_forward(hfg_disc_handle h, const float* audio_dev, int B, long long
 /* Same with HOST buffers (H2D, kernels, D2H, synchronise). */
 int hfg_disc_forward_host(hfg_disc_handle h, const float* audio_host, int B, long long T, float* maps_host);
 
+/* The GAN loss terms of the reference (HiFiGAN_TF/losses.py:8-43, called from gan.py:58-92) for ONE discriminator, from the
+ * maps of a forward over the concatenated batch [y; y_hat] (2 B waveforms, real half first: what `call((y, y_hat))` runs).
+ * out_host[3 + 3 n], n = sub-discriminators: [0] feature_loss (2 x sum over every map of mean |r - g|), [1] discriminator_loss
+ * (sum of mean (1 - D(y))^2 + mean D(y_hat)^2), [2] generator_loss (sum of mean (1 - D(y_hat))^2), then r_losses[n],
+ * g_losses[n], gen_losses[n].  Deterministic (fixed summation order); synchronises `stream`.  B = waveforms per half. */
+int hfg_disc_pair_losses(hfg_disc_handle h, const float* maps_dev, int B, long long T, float* out_host, void* stream);
+
 const char* hfg_disc_last_error(hfg_disc_handle h);
 void hfg_disc_destroy(hfg_disc_handle h);
 

@@ -92,6 +92,7 @@ SIGNATURES = {
                                   C.POINTER(C.c_longlong)]),
     "hfg_disc_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_longlong, C.c_void_p, C.c_void_p]),
     "hfg_disc_forward_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_longlong, C.c_void_p]),
+    "hfg_disc_pair_losses": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_longlong, C.POINTER(C.c_float), C.c_void_p]),
     "hfg_disc_last_error": (C.c_char_p, [C.c_void_p]),
     "hfg_disc_destroy": (None, [C.c_void_p]),
 }

@@ -95,6 +95,45 @@ __global__ void disc_lo_kernel(const float4* __restrict__ x, float4* __restrict_
   }
 }
 
+// GAN loss terms of one (real, generated) pair forward (reference HiFiGAN_TF/losses.py:8-43): the maps of a forward over the
+// concatenated batch [y; y_hat] hold the real half first.  Block (x, m) sums its strided share of map m:
+//   [0] |r - g| (feature_loss, losses.py:8-17)   [1] (1 - r)^2, [2] g^2 (discriminator_loss, :20-33)   [3] (1 - g)^2 (generator_loss, :36-46)
+struct LossSeg { long long off; long long half; };   // floats: start of the map, size of one half
+constexpr int kLossBlocks = 64;
+__global__ void __launch_bounds__(256) disc_loss_kernel(const float* __restrict__ maps, const LossSeg* __restrict__ segs, float* __restrict__ partial) {
+  const LossSeg sg = segs[blockIdx.y];
+  const float* __restrict__ r = maps + sg.off;
+  const float* __restrict__ g = r + sg.half;
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < sg.half; i += 256ll * kLossBlocks) {
+    const float rv = r[i], gv = g[i];
+    a0 += fabsf(rv - gv); a1 += (1.f - rv) * (1.f - rv); a2 += gv * gv; a3 += (1.f - gv) * (1.f - gv);
+  }
+  __shared__ float sh[4][8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    a0 += __shfl_xor_sync(0xffffffffu, a0, o); a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+    a2 += __shfl_xor_sync(0xffffffffu, a2, o); a3 += __shfl_xor_sync(0xffffffffu, a3, o);
+  }
+  const int w = threadIdx.x >> 5;
+  if ((threadIdx.x & 31) == 0) { sh[0][w] = a0; sh[1][w] = a1; sh[2][w] = a2; sh[3][w] = a3; }
+  __syncthreads();
+  if (threadIdx.x < 4) {
+    float t = 0.f;
+    for (int k = 0; k < 8; ++k) t += sh[threadIdx.x][k];        // fixed order: the result does not depend on scheduling
+    partial[((size_t)blockIdx.y * kLossBlocks + blockIdx.x) * 4 + threadIdx.x] = t;
+  }
+}
+// per map: the kLossBlocks partial sums in a fixed order, in double -> means [n_maps][4]
+__global__ void disc_loss_final_kernel(const float* __restrict__ partial, const LossSeg* __restrict__ segs, float* __restrict__ out, int n_maps) {
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= n_maps * 4) return;
+  const int map = m >> 2, k = m & 3;
+  double t = 0.0;
+  for (int b = 0; b < kLossBlocks; ++b) t += (double)partial[((size_t)map * kLossBlocks + b) * 4 + k];
+  out[m] = (float)(t / (double)segs[map].half);
+}
+
 struct DiscConvArgs {
   const float* x;       // [n_seq, n_in, cin]
   const float* w;       // [k][cin_g][cout]
@@ -356,6 +395,7 @@ struct hfg_disc_ctx {
   float* ws = nullptr; size_t ws_floats = 0;           // split / pooled waveforms
   float* d_audio = nullptr; size_t audio_floats = 0;   // host path staging
   float* d_maps = nullptr; size_t maps_floats = 0;
+  void* d_loss = nullptr;                              // segs | partial sums | per-map means (hfg_disc_pair_losses)
 };
 
 namespace {
@@ -701,6 +741,46 @@ int hfg_disc_forward_host(hfg_disc_handle h, const float* audio_host, int B, lon
   return HFG_OK;
 }
 
+int hfg_disc_pair_losses(hfg_disc_handle h, const float* maps_dev, int B, long long T, float* out_host, void* stream) {
+  if (!h || !maps_dev || !out_host || B < 1 || T < 1) return h ? dfail(h, HFG_ERR_INVALID, "hfg_disc_pair_losses: bad argument") : HFG_ERR_INVALID;
+  std::vector<MapDesc> maps;
+  long long total = 0;
+  int rc = build_layout(h, 2 * B, T, &maps, &total);
+  if (rc != HFG_OK) return rc;
+  DISC_CUDA_TRY(h, cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const int nm = (int)maps.size();
+  const size_t seg_bytes = (nm * sizeof(LossSeg) + 255) / 256 * 256, part_bytes = (size_t)nm * kLossBlocks * 4 * sizeof(float);
+  if (!h->d_loss) DISC_CUDA_TRY(h, cudaMalloc(&h->d_loss, seg_bytes + part_bytes + (size_t)nm * 4 * sizeof(float)));
+  LossSeg* d_segs = reinterpret_cast<LossSeg*>(h->d_loss);
+  float* d_part = reinterpret_cast<float*>(reinterpret_cast<char*>(h->d_loss) + seg_bytes);
+  float* d_mean = d_part + (size_t)nm * kLossBlocks * 4;
+  std::vector<LossSeg> segs(nm);
+  for (int i = 0; i < nm; ++i) { segs[i].off = maps[i].offset; segs[i].half = (long long)B * maps[i].period * maps[i].len * maps[i].C; }
+  DISC_CUDA_TRY(h, cudaMemcpyAsync(d_segs, segs.data(), nm * sizeof(LossSeg), cudaMemcpyHostToDevice, s));
+  disc_loss_kernel<<<dim3(kLossBlocks, nm), 256, 0, s>>>(maps_dev, d_segs, d_part);
+  DISC_CUDA_TRY(h, cudaGetLastError());
+  disc_loss_final_kernel<<<(nm * 4 + 127) / 128, 128, 0, s>>>(d_part, d_segs, d_mean, nm);
+  DISC_CUDA_TRY(h, cudaGetLastError());
+  std::vector<float> mean((size_t)nm * 4);
+  DISC_CUDA_TRY(h, cudaMemcpyAsync(mean.data(), d_mean, mean.size() * sizeof(float), cudaMemcpyDeviceToHost, s));
+  DISC_CUDA_TRY(h, cudaStreamSynchronize(s));
+  // losses.py: feature_loss = 2 * sum over every map of mean|r - g|; discriminator_loss = sum over sub-discriminators of
+  // mean((1 - D(y))^2) + mean(D(y_hat)^2); generator_loss = sum of mean((1 - D(y_hat))^2); scores = each sub's last map
+  const int nsub = (int)h->subs.size();
+  double fm = 0.0, dl = 0.0, gl = 0.0;
+  int mi = 0;
+  for (int sd = 0; sd < nsub; ++sd) {
+    const int nl = (int)h->subs[sd].layers.size();
+    for (int l = 0; l < nl; ++l, ++mi) fm += mean[(size_t)mi * 4];
+    const float* sc = &mean[(size_t)(mi - 1) * 4];
+    out_host[3 + sd] = sc[1]; out_host[3 + nsub + sd] = sc[2]; out_host[3 + 2 * nsub + sd] = sc[3];
+    dl += (double)sc[1] + (double)sc[2]; gl += sc[3];
+  }
+  out_host[0] = (float)(2.0 * fm); out_host[1] = (float)dl; out_host[2] = (float)gl;
+  return HFG_OK;
+}
+
 const char* hfg_disc_last_error(hfg_disc_handle h) { return h ? h->err.c_str() : g_disc_create_error.c_str(); }
 
 void hfg_disc_destroy(hfg_disc_handle h) {
@@ -716,6 +796,7 @@ void hfg_disc_destroy(hfg_disc_handle h) {
   if (h->ws) cudaFree(h->ws);
   if (h->d_audio) cudaFree(h->d_audio);
   if (h->d_maps) cudaFree(h->d_maps);
+  if (h->d_loss) cudaFree(h->d_loss);
   delete h;
 }
 

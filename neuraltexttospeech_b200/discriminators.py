@@ -122,6 +122,30 @@ class _Discriminator:
 
     __call__ = call
 
+    def pair_losses(self, x):
+        """x = (y, y_hat) -> the reference's loss terms for this discriminator (HiFiGAN_TF/losses.py:8-43, as gan.py:58-92
+        combines them), reduced on the GPU from one forward over the concatenated batch: dict with feature_loss,
+        discriminator_loss, generator_loss (floats) and r_losses, g_losses, gen_losses (one float per sub-discriminator)."""
+        import torch
+        y, y_hat = x
+        if tuple(y.shape) != tuple(y_hat.shape):
+            raise ValueError("y and y_hat must have the same shape")
+        to_t = lambda a: (torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).cuda(self.device) if isinstance(a, np.ndarray) else a)
+        both = torch.cat([to_t(y), to_t(y_hat)], dim=0)
+        if both.ndim == 3:
+            both = both[:, :, 0]
+        both = both.contiguous().float()
+        B2, T = (int(v) for v in both.shape)
+        _, _, total = self.layout(B2, T)
+        maps = torch.empty(total, dtype=torch.float32, device=both.device)
+        stream = C.c_void_p(torch.cuda.current_stream(both.device).cuda_stream)
+        self._check(self._lib.hfg_disc_forward(self._h, C.c_void_p(both.data_ptr()), B2, T, C.c_void_p(maps.data_ptr()), stream), "hfg_disc_forward")
+        out = (C.c_float * (3 + 3 * self.N_SUB))()
+        self._check(self._lib.hfg_disc_pair_losses(self._h, C.c_void_p(maps.data_ptr()), B2 // 2, T, out, stream), "hfg_disc_pair_losses")
+        n = self.N_SUB
+        return {"feature_loss": out[0], "discriminator_loss": out[1], "generator_loss": out[2],
+                "r_losses": list(out[3:3 + n]), "g_losses": list(out[3 + n:3 + 2 * n]), "gen_losses": list(out[3 + 2 * n:3 + 3 * n])}
+
 
 class MultiPeriodDiscriminator(_Discriminator):
     KIND, N_SUB, N_LAYERS = 0, 5, 6

@@ -205,3 +205,30 @@ def synthetic_weights(kind, variant="A", seed=4321):
             out[name + ".g"] = g.astype(np.float32)
         out[name + ".b"] = b
     return out
+
+
+# ---------------------------------------------------------------- loss terms (reference HiFiGAN_TF/losses.py), float64
+def feature_loss(fmap_r, fmap_g):
+    """losses.py:8-17: 2 * sum over sub-discriminators and their maps of mean |real - generated|."""
+    loss = 0.0
+    for dr, dg in zip(fmap_r, fmap_g):
+        for rl, gl in zip(dr, dg):
+            loss += float(np.mean(np.abs(np.asarray(rl, np.float64) - np.asarray(gl, np.float64))))
+    return loss * 2
+
+
+def discriminator_loss(disc_real_outputs, disc_generated_outputs):
+    """losses.py:20-33 -> (loss, r_losses, g_losses)."""
+    loss, r_losses, g_losses = 0.0, [], []
+    for dr, dg in zip(disc_real_outputs, disc_generated_outputs):
+        r = float(np.mean((1 - np.asarray(dr, np.float64)) ** 2))
+        g = float(np.mean(np.asarray(dg, np.float64) ** 2))
+        loss += r + g
+        r_losses.append(r); g_losses.append(g)
+    return loss, r_losses, g_losses
+
+
+def generator_loss(disc_outputs):
+    """losses.py:36-46 -> (loss, gen_losses)."""
+    gen_losses = [float(np.mean((1 - np.asarray(dg, np.float64)) ** 2)) for dg in disc_outputs]
+    return float(sum(gen_losses)), gen_losses

@@ -152,3 +152,29 @@ def test_tensor_core_layers_match_the_ffma_path(kind, monkeypatch):
                 differs = differs or not np.array_equal(a, b)
                 assert np.abs(a - b).max() <= TOL * np.abs(b).max()
     assert differs                                            # i.e. the knob really switches kernels
+
+
+@pytest.mark.parametrize("kind", ["mpd", "msd"])
+def test_pair_losses_match_the_reference_formulas(kind):
+    """hfg_disc_pair_losses (losses.py:8-43 reduced on the GPU) against the oracle's formulas applied (a) to the maps the
+    CUDA forward itself returned -- only the reduction differs -- and (b) to the oracle's own maps."""
+    from oracle import disc_oracle as D
+    model, w = _model(kind, "reference", "B")
+    y, y_hat = _waveform(3, 2051, seed=21), _waveform(3, 2051, seed=22)
+    got = model.pair_losses((y, y_hat))
+    again = model.pair_losses((y[:, :, None], y_hat[:, :, None]))
+    assert got == again                                       # deterministic, and [B, T, 1] is accepted
+    y_d_rs, y_d_gs, fmap_rs, fmap_gs = model((y, y_hat))
+    fwd = D.mpd_forward if kind == "mpd" else D.msd_forward
+    (o_rs, o_fr), (o_gs, o_fg) = fwd(w, y), fwd(w, y_hat)
+    for tag, (rs, gs, fr, fg), tol in (("own maps", (y_d_rs, y_d_gs, fmap_rs, fmap_gs), 2e-6), ("oracle maps", (o_rs, o_gs, o_fr, o_fg), 2e-4)):
+        fm = D.feature_loss(fr, fg)
+        dl, r_l, g_l = D.discriminator_loss(rs, gs)
+        gl, gen_l = D.generator_loss(gs)
+        assert abs(got["feature_loss"] - fm) <= tol * fm, (tag, got["feature_loss"], fm)
+        assert abs(got["discriminator_loss"] - dl) <= tol * dl, tag
+        assert abs(got["generator_loss"] - gl) <= tol * gl, tag
+        np.testing.assert_allclose(got["r_losses"], r_l, rtol=tol)
+        np.testing.assert_allclose(got["g_losses"], g_l, rtol=max(tol, 1e-5), atol=1e-12)
+        np.testing.assert_allclose(got["gen_losses"], gen_l, rtol=tol)
+    assert got["feature_loss"] > 0 and len(got["r_losses"]) == model.N_SUB
