@@ -58,6 +58,7 @@ struct Layer {
     bool on = false;
     int fold = 1, cg = 2, ntaps1 = 0, ntaps2 = 0;
     int off1[kMaxTaps], off2[kMaxTaps];
+    unsigned char kz1[kMaxTaps] = {0}, kz2[kMaxTaps] = {0};   // all-zero K-steps of each tap (rb_zero_ksteps)
     void* d_w1 = nullptr; void* d_w2 = nullptr;
     float* d_b1 = nullptr; float* d_b2 = nullptr;
   } fused;
@@ -489,6 +490,7 @@ struct Runner {
     a.mode = h->cfg.resblock == 1 ? 1 : 2;
     a.B = B; a.n_q = x_rows / F.fold; a.ntaps1 = F.ntaps1; a.ntaps2 = F.ntaps2;
     memcpy(a.off1, F.off1, sizeof(int) * F.ntaps1); memcpy(a.off2, F.off2, sizeof(int) * F.ntaps2);
+    memcpy(a.kz1, F.kz1, sizeof a.kz1); memcpy(a.kz2, F.kz2, sizeof a.kz2);
     a.mid_slope = mid_slope; a.res_inv = 1.0f / slope_of_res; a.out_scale = out_scale; a.out_slope = out_slope;
     status = launch_resblock_tc(a, h->act, s);
     h->launches++;
@@ -854,10 +856,11 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
         Layer::Fused& F = A.fused;
         F.fold = f; F.cg = cg; F.ntaps1 = ra.ntaps1; F.ntaps2 = ra.ntaps2;
         memcpy(F.off1, ra.off1, sizeof(int) * ra.ntaps1); memcpy(F.off2, ra.off2, sizeof(int) * ra.ntaps2);
-        auto upload_w = [&](const KView& V, void** dptr) -> int {
+        auto upload_w = [&](const KView& V, void** dptr, unsigned char* kz) -> int {
           const int nt = (int)V.off[0].size();
           std::vector<float> w32((size_t)nt * 64 * 64);
           for (int t = 0; t < nt; ++t) memcpy(&w32[(size_t)t * 4096], V.w[0][t].data(), sizeof(float) * 4096);
+          rb_zero_ksteps(w32.data(), nt, kz);
           std::vector<char> pk(rb_packed_weight_bytes(nt));
           rb_pack_weights(w32.data(), nt, cg, h->act, pk.data());
           CUDA_TRY(h, cudaMalloc(dptr, pk.size()));
@@ -871,8 +874,8 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
           CUDA_TRY(h, cudaMemcpy(*dptr, bias.data(), 64 * sizeof(float), cudaMemcpyHostToDevice));
           return HFG_OK;
         };
-        int rc = upload_w(V1, &F.d_w1); if (rc) return rc;
-        rc = upload_w(V2, &F.d_w2); if (rc) return rc;
+        int rc = upload_w(V1, &F.d_w1, F.kz1); if (rc) return rc;
+        rc = upload_w(V2, &F.d_w2, F.kz2); if (rc) return rc;
         rc = upload_b(A, &F.d_b1); if (rc) return rc;
         rc = upload_b(Bc, &F.d_b2); if (rc) return rc;
         F.on = true;
@@ -1336,6 +1339,7 @@ int hfg_op_resblock_fused(int act, int mode, const void* x_dev, int B, int rows,
   for (int c = 0; c < 2 && e == cudaSuccess; ++c) {
     std::vector<char> pk(rb_packed_weight_bytes(nt[c]));
     rb_pack_weights(wh[c], nt[c], cg, (ActType)act, pk.data());
+    rb_zero_ksteps(wh[c], nt[c], c == 0 ? a.kz1 : a.kz2);
     e = cudaMalloc(&d_w[c], pk.size());
     if (e == cudaSuccess) e = cudaMemcpy(d_w[c], pk.data(), pk.size(), cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMalloc((void**)&d_b[c], 64 * sizeof(float));

@@ -161,7 +161,11 @@ struct RbArgs {
   int ntaps1, ntaps2;
   int off1[kMaxTaps], off2[kMaxTaps];
   float mid_slope, res_inv, out_scale, out_slope;
+  // bit kk of kz1[j] / kz2[j]: rows 16 kk .. 16 kk + 15 of tap j's 64 x 64 weight block are all zero (rb_zero_ksteps), so
+  // that K-step's MMA is not issued.  Time folding makes such blocks: a folded dilated tap reads one fold slot only.
+  unsigned char kz1[kMaxTaps], kz2[kMaxTaps];
 };
+void rb_zero_ksteps(const float* w, int ntaps, unsigned char* kz);   // w: fp32 [ntaps][64][64]
 bool rb_supported(const RbArgs& a, int* cg_out);          // needs ntaps / offsets only
 size_t rb_packed_weight_bytes(int ntaps);
 void rb_pack_weights(const float* w, int ntaps, int cg, ActType act, void* dst_host);   // w: fp32 [ntaps][64][64]

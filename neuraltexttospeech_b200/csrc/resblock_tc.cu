@@ -80,6 +80,7 @@ struct RbKArgs {
   int n_q, B;                          // kernel-view rows per utterance, utterances
   int ntaps1, ntaps2;
   int off1[kMaxTaps], off2[kMaxTaps];  // kernel-view row offsets of the taps
+  unsigned char kz1[kMaxTaps], kz2[kMaxTaps];   // per tap: bit kk = K-step kk multiplies an all-zero weight block (skipped)
   int min1, min2, span2;
   int r2;                              // valid output rows per CTA tile: MB*128 - span2
   int tiles_q, total_tiles;            // per utterance / in total (CG == 2: PAIR tiles of 2*r2 rows)
@@ -222,7 +223,7 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
       // ===================== MMA issuer (pair: leader only) =====================
       if (rank == 0 && my_tiles > 0) {
         const uint32_t slab_addr = smem_u32(slab), xt_addr = smem_u32(xt), w_addr = smem_u32(wsm);
-        auto issue = [&](uint32_t a_base, uint32_t w_base, const int* offs, int mn, int nt, uint32_t tacc, bool fresh, int bias_idx) {   // mn: offset of smem row 0
+        auto issue = [&](uint32_t a_base, uint32_t w_base, const int* offs, const unsigned char* kz, int mn, int nt, uint32_t tacc, bool fresh, int bias_idx) {   // mn: offset of smem row 0
           if (elect_one()) {
 #pragma unroll 1
             for (int mb = 0; mb < MB; ++mb) {
@@ -231,14 +232,16 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
               for (int j = 0; j < nt; ++j) {
                 const uint64_t a0 = make_desc_sw<kRbRowB>(a_base + (uint32_t)(mb * 128 + offs[j] - mn) * kRbRowB);
                 const uint64_t b0 = make_desc(w_base + j * TAP_BYTES, NB * 16, 128u);
+                const uint32_t zero = kz[j];
 #pragma unroll
                 for (int kk = 0; kk < kRbC / 16; ++kk) {
+                  if ((zero >> kk) & 1u) continue;                   // an all-zero 16 x 64 weight block (time folding): nothing to add
                   const uint64_t adesc = a0 + (uint64_t)((kk * 32) >> 4);
                   const uint64_t bdesc = b0 + (uint64_t)((kk * 2 * NB * 16) >> 4);
-                  if (CG == 2) umma_f16_2cta(tacc + mb * kRbC, adesc, bdesc, IDESC, (first && kk == 0) ? 0u : 1u);
-                  else umma_f16(tacc + mb * kRbC, adesc, bdesc, IDESC, (first && kk == 0) ? 0u : 1u);
+                  if (CG == 2) umma_f16_2cta(tacc + mb * kRbC, adesc, bdesc, IDESC, first ? 0u : 1u);
+                  else umma_f16(tacc + mb * kRbC, adesc, bdesc, IDESC, first ? 0u : 1u);
+                  first = 0;
                 }
-                first = 0;
               }
               // bias tap: acc += ones[128 x 16] . biasB[16 x 64]
               const uint64_t oa = make_desc(smem_u32(ones_s), 2048u, 128u);
@@ -257,13 +260,13 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
           const int pos = i % nsl;
           mbar_wait(&slab_full[pos], (i / nsl) & 1);
           tc_fence_after();
-          issue(slab_addr + pos * pl.slab_bytes, w_addr, ka.off1, ka.min1, ka.ntaps1, tmem_base + (i & 1) * (MB * kRbC), true, 0);
+          issue(slab_addr + pos * pl.slab_bytes, w_addr, ka.off1, ka.kz1, ka.min1, ka.ntaps1, tmem_base + (i & 1) * (MB * kRbC), true, 0);
           commit(&acc1_full[i & 1]);
         };
         auto conv2 = [&](int i) {
           mbar_wait(&mid_done[i & 1], (i >> 1) & 1);      // xt tile written, acc2 pre-loaded with the residual, acc1 drained
           tc_fence_after();
-          issue(xt_addr + (i % nxt) * pl.xt_bytes, w_addr + ka.ntaps1 * TAP_BYTES, ka.off2, ka.min2 - lead, ka.ntaps2,
+          issue(xt_addr + (i % nxt) * pl.xt_bytes, w_addr + ka.ntaps1 * TAP_BYTES, ka.off2, ka.kz2, ka.min2 - lead, ka.ntaps2,
                 tmem_base + (2 * MB + (i & 1) * MB) * kRbC, MODE == 2, 1);
           commit(&acc2_full[i & 1]);
         };
@@ -585,6 +588,8 @@ cudaError_t rb_launch_t(const RbArgs& a, const RbShape& sh, ActType act, cudaStr
   ka.n_q = a.n_q; ka.B = a.B; ka.ntaps1 = a.ntaps1; ka.ntaps2 = a.ntaps2;
   for (int j = 0; j < a.ntaps1; ++j) ka.off1[j] = a.off1[j];
   for (int j = 0; j < a.ntaps2; ++j) ka.off2[j] = a.off2[j];
+  static const bool skip_zero = rb_env_int("HFG_RB_SKIPZ", 1) != 0;     // A/B knob: 0 issues every K-step
+  if (skip_zero) { memcpy(ka.kz1, a.kz1, sizeof ka.kz1); memcpy(ka.kz2, a.kz2, sizeof ka.kz2); }
   ka.min1 = sh.min1; ka.min2 = sh.min2; ka.span2 = sh.span2;
   ka.r2 = MB * 128 - sh.span2;
   ka.tiles_q = (a.n_q + CG * ka.r2 - 1) / (CG * ka.r2);
@@ -650,6 +655,19 @@ size_t rb_packed_weight_bytes(int ntaps) { return (size_t)ntaps * kRbC * kRbRowB
 
 // fp32 [ntaps][64][64] (kernel view: [tap][c_in][c_out]) -> [tap][CTA of the pair] blocks of [8 K-chunks][64/cg rows][8 x 16-bit]
 // (K-major, no swizzle: LBO = rows * 16 bytes between K chunks, SBO = 128 bytes between 8-row groups)
+void rb_zero_ksteps(const float* w, int ntaps, unsigned char* kz) {
+  for (int j = 0; j < ntaps; ++j) {
+    unsigned m = 0;
+    for (int kk = 0; kk < kRbC / 16; ++kk) {
+      bool zero = true;
+      for (int r = kk * 16; r < kk * 16 + 16 && zero; ++r)
+        for (int c = 0; c < kRbC; ++c) if (w[((size_t)j * kRbC + r) * kRbC + c] != 0.0f) { zero = false; break; }
+      if (zero) m |= 1u << kk;
+    }
+    kz[j] = (unsigned char)m;
+  }
+}
+
 void rb_pack_weights(const float* w, int ntaps, int cg, ActType act, void* dst_host) {
   uint16_t* dst = reinterpret_cast<uint16_t*>(dst_host);
   const int nb = kRbC / cg;
