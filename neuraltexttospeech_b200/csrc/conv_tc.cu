@@ -335,23 +335,30 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
             if (elect_one()) {
               const uint32_t wb = wst_addr + st * pl.stage_bytes;
 #pragma unroll
+              uint32_t fst = first;
               for (int jj = 0; jj < TPS; ++jj) {
                 if (jj >= nj) break;
                 const uint32_t row_off = (uint32_t)(ka.var[v].tap_off[j0 + jj] - ka.min_off);
                 const uint64_t a0 = make_desc_sw<ROWB>(sl + row_off * ROWB + kb * KBW * 2);
                 const uint64_t b0 = make_desc(wb + jj * BLK_BYTES, NB * 16, 128u);
+                // K-steps of this tap whose weight rows are all zero (fold slots a shifted tap does not read, padded channels)
+                const uint32_t zero = (ka.var[v].kz[j0 + jj] >> ((s * KS + kb * KBW) / 16)) & ((1u << (KBW / 16)) - 1u);
+                if (zero == (1u << (KBW / 16)) - 1u) continue;
 #pragma unroll
                 for (int mb = 0; mb < MB; ++mb) {
+                  uint32_t f = fst;
 #pragma unroll
                   for (int kk = 0; kk < KBW / 16; ++kk) {
+                    if ((zero >> kk) & 1u) continue;
                     // descriptor start-address field counts 16-byte units: advance with plain adds
                     const uint64_t adesc = a0 + (uint64_t)((mb * 128 * ROWB + kk * 32) >> 4);
                     const uint64_t bdesc = b0 + (uint64_t)((kk * 2 * NB * 16) >> 4);
-                    if (CG == 2) umma_f16_2cta(tacc + mb * N, adesc, bdesc, IDESC, (first && kk == 0) ? 0u : 1u);
-                    else umma_f16(tacc + mb * N, adesc, bdesc, IDESC, (first && kk == 0) ? 0u : 1u);
+                    if (CG == 2) umma_f16_2cta(tacc + mb * N, adesc, bdesc, IDESC, f ? 0u : 1u);
+                    else umma_f16(tacc + mb * N, adesc, bdesc, IDESC, f ? 0u : 1u);
+                    f = 0;
                   }
                 }
-                first = 0;
+                fst = 0;
               }
               // pair: the commits arrive on the same barrier of BOTH CTAs
               if (!ka.resident) { if (CG == 2) umma_commit_2cta(&w_empty[st]); else umma_commit(&w_empty[st]); }   // frees the weight stage
@@ -360,7 +367,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
                 if (s == NKS - 1) { if (CG == 2) umma_commit_2cta(&acc_full[abuf]); else umma_commit(&acc_full[abuf]); TC_TRACE(2u, tcnt, 3u); }   // tile complete (all MMAs issued)
               }
             }
-            first = 0;
+            for (int jj = 0; jj < nj; ++jj)                       // every lane tracks whether the accumulators have been started
+              if (((ka.var[v].kz[j0 + jj] >> ((s * KS + kb * KBW) / 16)) & ((1u << (KBW / 16)) - 1u)) != (1u << (KBW / 16)) - 1u) first = 0;
             __syncwarp();
           }
         }
@@ -692,7 +700,8 @@ cudaError_t launch_t(const TcArgs& a, ActType act, cudaStream_t s, int* grid_out
   ka.bias = a.bias; ka.res2 = a.res2; ka.n_q = a.n_q; ka.c_out = a.c_out; ka.has_res = a.res != nullptr;
   ka.res_inv = a.res_inv; ka.out_scale = a.out_scale; ka.out_slope = a.out_slope;
   ka.nvar = a.nvar;
-  for (int v = 0; v < a.nvar; ++v) ka.var[v] = a.var[v];
+  static const bool skip_zero = tc_env_int("HFG_TC_SKIPZ", 1) != 0;       // A/B knob: 0 issues every K-step
+  for (int v = 0; v < a.nvar; ++v) { ka.var[v] = a.var[v]; if (!skip_zero) memset(ka.var[v].kz, 0, sizeof ka.var[v].kz); }
   int mn = a.var[0].tap_off[0], mx = mn;
   for (int v = 0; v < a.nvar; ++v)
     for (int j = 0; j < a.var[v].ntaps; ++j) { mn = a.var[v].tap_off[j] < mn ? a.var[v].tap_off[j] : mn; mx = a.var[v].tap_off[j] > mx ? a.var[v].tap_off[j] : mx; }

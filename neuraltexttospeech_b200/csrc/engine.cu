@@ -29,6 +29,7 @@ namespace {
 struct Phase {            // one output phase of a transposed conv (or the single "phase" of a conv)
   int ntaps = 0;
   int tap_off[kMaxTaps];
+  unsigned kz[kMaxTaps] = {0};   // all-zero 16-row K-steps of each tap's weight block (TcVariant::kz)
   size_t w32_off = 0;     // element offset into d_w32
   size_t wpk_off = 0;     // byte offset into d_wpk
 };
@@ -427,7 +428,7 @@ struct Runner {
       const Phase& ph = L.phases[p];
       a.var[p].w = (const char*)L.d_wpk + ph.wpk_off;
       a.var[p].ntaps = ph.ntaps; a.var[p].out_off = p;
-      for (int j = 0; j < ph.ntaps; ++j) a.var[p].tap_off[j] = ph.tap_off[j];
+      for (int j = 0; j < ph.ntaps; ++j) { a.var[p].tap_off[j] = ph.tap_off[j]; a.var[p].kz[j] = ph.kz[j]; }
     }
     a.raw_out = raw_out ? 1 : 0;
     status = h->tf32 ? launch_conv_tf32(a, s) : launch_conv_tc(a, h->act, s, nullptr);
@@ -744,7 +745,16 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
             for (int j = 0; j < L.k; ++j) taps[floordiv(sidx + j - pl, f)] = 1;
           const int nt = (int)taps.size(), span = taps.rbegin()->first - taps.begin()->first;
           if (nt > kMaxTaps || !tc_supported(cf, 16, nt, span)) continue;
-          const double cst = (double)nt * (cf / 16.0) / f;
+          // MMAs actually issued per f samples: a tap's K-step is skipped when none of the fold slots it covers is read
+          std::map<int, unsigned> used;                         // kernel-view row offset -> bit mask of 16-channel K-steps read
+          for (int sidx = 0; sidx < f; ++sidx)
+            for (int j = 0; j < L.k; ++j) {
+              const int a = floordiv(sidx + j - pl, f), slot = sidx + j - pl - a * f;
+              for (int ch = slot * L.cin; ch < (slot + 1) * L.cin; ch += 1) used[a] |= 1u << (ch / 16);
+            }
+          int issued = 0;
+          for (auto& kv : used) issued += __builtin_popcount(kv.second);
+          const double cst = (double)issued / f;
           if (cst < best) { best = cst; best_f = f; }
         }
         fi = fo = best_f;
@@ -780,6 +790,18 @@ int hfg_finalize_weights(hfg_handle h, int precision) {
         ph.tap_off[t] = V.off[p][t];
         for (int ci = 0; ci < V.cin_k; ++ci)
           memcpy(&w32[ph.w32_off + ((size_t)t * L.cin_pad + ci) * L.cout_k], &V.w[p][t][(size_t)ci * L.cout_k], sizeof(float) * L.cout_k);
+        for (int kk = 0; kk < L.cin_pad / 16 && kk < 32; ++kk) {    // zero blocks: unread fold slots of a shifted tap, padded channels
+          bool zero = true;
+          const float* blk = &w32[ph.w32_off + ((size_t)t * L.cin_pad + (size_t)kk * 16) * L.cout_k];
+          for (size_t e = 0; e < (size_t)16 * L.cout_k && zero; ++e) zero = blk[e] == 0.0f;
+          if (zero) ph.kz[t] |= 1u << kk;
+        }
+      }
+      {   // a phase whose weights are ALL zero must still start its accumulator: issue everything
+        bool any = false;
+        const unsigned full = L.cin_pad / 16 >= 32 ? 0xFFFFFFFFu : (1u << (L.cin_pad / 16)) - 1u;
+        for (int t = 0; t < ph.ntaps; ++t) any = any || (ph.kz[t] & full) != full;
+        if (!any) for (int t = 0; t < ph.ntaps; ++t) ph.kz[t] = 0;
       }
       L.phases.push_back(ph);
     }

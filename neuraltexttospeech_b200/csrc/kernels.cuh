@@ -90,6 +90,8 @@ struct TcVariant {
   int ntaps;
   int out_off;
   int tap_off[kMaxTaps];
+  unsigned kz[kMaxTaps];   // 16-bit kernel only: bit kk of kz[j] = rows 16 kk .. 16 kk + 15 of tap j's weight block are all zero
+                           // (time folding, channel padding): that K-step's MMA is not issued.  0 = issue everything
 };
 struct TcArgs {
   const void* x;
