@@ -394,6 +394,36 @@ def test_launch_path_knobs_off_in_a_subprocess():
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
 
 
+def test_skipping_all_zero_k_steps_does_not_change_a_bit():
+    """The MMA issuers skip K-steps whose weight block is all zero (unread fold slots of shifted taps, padded channels):
+    the skipped products are exact zeros, so the waveform must be bit-identical with HFG_RB_SKIPZ=0 HFG_TC_SKIPZ=0 (knobs
+    read once per process -> the other arm runs in a subprocess and hands its output back through a file)."""
+    import subprocess
+    import sys
+    import tempfile
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = ("import sys, numpy as np\n"
+            "from neuraltexttospeech_b200 import Generator, HParams\n"
+            "from neuraltexttospeech_b200.synthetic import synthetic_mel, synthetic_weights\n"
+            "outs = {}\n"
+            "for v in '123':\n"
+            "    h = HParams.builtin(v)\n"
+            "    g = Generator(h, precision='fp16').load_weights(synthetic_weights(h, 'B'))\n"
+            "    outs[v] = g(synthetic_mel(2, 41, h.num_mels, seed=3))\n"
+            "    g.close()\n"
+            "np.savez(sys.argv[1], **outs)\n")
+    with tempfile.TemporaryDirectory() as d:
+        paths = {}
+        for tag, knobs in (("skip", {}), ("all", {"HFG_RB_SKIPZ": "0", "HFG_TC_SKIPZ": "0"})):
+            paths[tag] = os.path.join(d, tag + ".npz")
+            r = subprocess.run([sys.executable, "-c", code, paths[tag]], env=dict(os.environ, **knobs), cwd=root, capture_output=True, text=True, timeout=600)
+            assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+        a, b = np.load(paths["skip"]), np.load(paths["all"])
+        for v in "123":
+            assert np.isfinite(a[v]).all() and np.abs(a[v]).max() > 1e-3
+            assert np.array_equal(a[v], b[v]), v
+
+
 @pytest.mark.parametrize("v,B,T", [("1", 2, 40), ("2", 3, 33), ("3", 2, 57), ("1", 1, 300)])
 def test_tf32_tensor_core_mode_meets_the_north_star_tolerance(v, B, T):
     """precision="tf32": tcgen05.mma.kind::tf32 with fp32 storage -- the tensor-core precision BASELINE.json's north star
