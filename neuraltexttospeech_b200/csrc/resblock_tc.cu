@@ -88,7 +88,17 @@ struct RbKArgs {
   int nsl, nxt;                        // ring depths (slab slots, xt tiles)
   int lead;                            // MODE 2: spare rows on top of the xt tile (0 in MODE 1)
   float mid_slope, xt_inv, res_inv, out_scale, out_slope;   // xt_inv = 1 / mid_slope
+  int two_issuers;                     // 1: warp 2 issues the conv1 MMAs and warp 3 the conv2 MMAs; 0: warp 2 issues both, c1(i+1) then c2(i)
+  long long* trace;                    // HFG_TC_TRACE builds: [7 roles][64 tiles][8 events] clock64 stamps of CTA 0, else unused
 };
+
+// Debug build only (-DHFG_TC_TRACE, tools/trace_resblock.py): CTA 0 stamps clock64() per role / tile / event.
+#ifdef HFG_TC_TRACE
+#define RB_TRACE(role, tile_i, ev) \
+  do { if (ka.trace && blockIdx.x == 0 && (uint32_t)(tile_i) < 64u) ka.trace[((role) * 64u + (uint32_t)(tile_i)) * 8u + (ev)] = clock64(); } while (0)
+#else
+#define RB_TRACE(role, tile_i, ev) do { } while (0)
+#endif
 
 template <typename T, int MB, int CG, int MODE>
 __global__ void __launch_bounds__(kRbThreads, 1)
@@ -184,6 +194,7 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
         int b; const int q0 = tile_q0(tile0 + i * tile_step, b);
         const int pos = i % nsl;
         mbar_wait(&slab_empty[pos], ((i / nsl) & 1) ^ 1);
+        if (lane == 0) RB_TRACE(0u, i, 0u);                          // slot free, load requested
         if (elect_one()) {
           uint8_t* dst = slab + pos * pl.slab_bytes;
           if (CG == 1) {
@@ -219,8 +230,11 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
         }
       }
       __syncwarp();
-    } else if (warp == 2) {
-      // ===================== MMA issuer (pair: leader only) =====================
+    } else {
+      // ===================== MMA issuers (pair: leader only): warp 2 issues every conv1, warp 3 every conv2 =====================
+      // One thread issues an MMA every ~60 clocks (descriptor arithmetic + tcgen05.mma), twice the 32 clocks an M = 256,
+      // N = 64, K = 16 MMA keeps the tensor pipe busy: a single issuer caps the pipe at ~50 % (role timeline,
+      // profiles/r2e_fused_issue.md).  conv1(i+1) and conv2(i) are independent streams, so each gets its own warp.
       if (rank == 0 && my_tiles > 0) {
         const uint32_t slab_addr = smem_u32(slab), xt_addr = smem_u32(xt), w_addr = smem_u32(wsm);
         auto issue = [&](uint32_t a_base, uint32_t w_base, const int* offs, const unsigned char* kz, int mn, int nt, uint32_t tacc, bool fresh, int bias_idx) {   // mn: offset of smem row 0
@@ -258,26 +272,50 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
         };
         auto conv1 = [&](int i) {
           const int pos = i % nsl;
+          if (lane == 0) RB_TRACE(1u, i, 0u);                        // conv1's turn
           mbar_wait(&slab_full[pos], (i / nsl) & 1);
+          if (lane == 0) RB_TRACE(1u, i, 1u);                        // slab landed
           tc_fence_after();
           issue(slab_addr + pos * pl.slab_bytes, w_addr, ka.off1, ka.kz1, ka.min1, ka.ntaps1, tmem_base + (i & 1) * (MB * kRbC), true, 0);
           commit(&acc1_full[i & 1]);
+          if (lane == 0) RB_TRACE(1u, i, 2u);                        // conv1 issued
         };
         auto conv2 = [&](int i) {
+          if (lane == 0) RB_TRACE(1u, i, 3u);                        // conv2's turn
           mbar_wait(&mid_done[i & 1], (i >> 1) & 1);      // xt tile written, acc2 pre-loaded with the residual, acc1 drained
+          if (lane == 0) RB_TRACE(1u, i, 4u);                        // mid pass(es) done
           tc_fence_after();
           issue(xt_addr + (i % nxt) * pl.xt_bytes, w_addr + ka.ntaps1 * TAP_BYTES, ka.off2, ka.kz2, ka.min2 - lead, ka.ntaps2,
                 tmem_base + (2 * MB + (i & 1) * MB) * kRbC, MODE == 2, 1);
           commit(&acc2_full[i & 1]);
+          if (lane == 0) RB_TRACE(1u, i, 5u);                        // conv2 issued
         };
-        mbar_wait(&w_full[0], 0);
-        tc_fence_after();
-        conv1(0);
-        mbar_wait(&w_full[1], 0);
-        tc_fence_after();
-        for (int i = 0; i < my_tiles; ++i) {
-          if (i + 1 < my_tiles) conv1(i + 1);             // acc1[(i+1)&1] was drained by mid(i-1): implied by mid_done(i-1)
-          conv2(i);
+        if (!ka.two_issuers) {
+          if (warp == 2) {                                  // one issuer, order c1(i+1), c2(i)
+            mbar_wait(&w_full[0], 0);
+            tc_fence_after();
+            conv1(0);
+            mbar_wait(&w_full[1], 0);
+            tc_fence_after();
+            for (int i = 0; i < my_tiles; ++i) {
+              if (i + 1 < my_tiles) conv1(i + 1);           // acc1[(i+1)&1] was drained by mid(i-1): implied by mid_done(i-1)
+              conv2(i);
+            }
+          }
+        } else if (warp == 2) {
+          mbar_wait(&w_full[0], 0);
+          tc_fence_after();
+          for (int i = 0; i < my_tiles; ++i) {
+            if (i >= 2) {                                   // acc1[i&1] must have been drained by mid(i-2)
+              mbar_wait(&mid_done[i & 1], ((i - 2) >> 1) & 1);
+              tc_fence_after();
+            }
+            conv1(i);
+          }
+        } else {
+          mbar_wait(&w_full[1], 0);
+          tc_fence_after();
+          for (int i = 0; i < my_tiles; ++i) conv2(i);
         }
       }
     }
@@ -292,6 +330,7 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
         const int buf = i % nxt;
         for (int mb = 0; mb < MB; ++mb) {
           mbar_wait(&out_done[2 * buf + mb], (i / nxt) & 1);
+          if (lane == 0) RB_TRACE(2u, i, (uint32_t)mb);               // output block ready, store issued
           if (elect_one()) {
             const int q = q0 + mb * 128;
             if (q < ka.n_q) tma_store_3d(mb == MB - 1 ? &tm_out_last : &tm_out, xt + buf * pl.xt_bytes + (mb * 128 + out_row0) * kRbRowB, 0, q, b);
@@ -307,6 +346,7 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
           mbar_arrive(&xt_free[buf]);
         }
         __syncwarp();
+        if (lane == 0) RB_TRACE(2u, i, 2u);                          // stores read out, tile handed back
       }
       if (elect_one()) bulk_wait_all();
       __syncwarp();
@@ -330,10 +370,13 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
 #pragma unroll 1
         for (int mb = 0; mb < MB; ++mb, ++pcnt) {
           if ((int)(pcnt % (uint32_t)EG) != grp) continue;
+          if (quarter == 0 && lane == 0) { RB_TRACE(3u + mb, i, 0u); RB_TRACE(3u + mb, i, 4u + grp); }
           mbar_wait(&acc1_full[i & 1], (i >> 1) & 1);                 // conv1 of the tile complete (hence its slab landed)
+          if (quarter == 0 && lane == 0) RB_TRACE(3u + mb, i, 1u);
           tc_fence_after();
           mbar_wait(&xt_free[xbuf], ((i / nxt) & 1) ^ 1);            // the tile's previous tenant has been stored
           mbar_wait(&acc2_free[i & 1], ((i >> 1) & 1) ^ 1);          // fin(i-2) has read acc2[i&1]
+          if (quarter == 0 && lane == 0) RB_TRACE(3u + mb, i, 2u);
           tc_fence_after();
           const int r = mb * 128 + er;                                // row of the CTA tile
           const int g = q0 + ka.min2 + r;                             // kernel-view row of this xt row (xt row 0 = q0 - h2)
@@ -397,6 +440,7 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
             if (CG == 2) mbar_arrive_cluster(mapa_u32(smem_u32(&mid_done[i & 1]), 0));
             else mbar_arrive(&mid_done[i & 1]);
           }
+          if (quarter == 0 && lane == 0) RB_TRACE(3u + mb, i, 3u);
         }
       }
       // ---------------- fin(i): acc2 -> output rows, in place in the xt tile
@@ -417,7 +461,9 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
 #pragma unroll
             for (int k = 0; k < 8; ++k) rr2[k] = rp[k];
           }
+          if (quarter == 0 && lane == 0) { RB_TRACE(5u + mb, i, 0u); RB_TRACE(5u + mb, i, 4u + grp); }
           mbar_wait(&acc2_full[i & 1], (i >> 1) & 1);                 // conv2 of the whole tile complete: xt rows are dead
+          if (quarter == 0 && lane == 0) RB_TRACE(5u + mb, i, 1u);
           tc_fence_after();
           const int orr = MODE == 2 ? r + lead - ka.min2 : r;        // MODE 2: the row of x1 (second skip connection), reused for the output
           uint8_t* orow = xt + xbuf * pl.xt_bytes + orr * kRbRowB;
@@ -471,6 +517,7 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
             mbar_arrive(&out_done[2 * xbuf + mb]);
             mbar_arrive(&acc2_free[i & 1]);
           }
+          if (quarter == 0 && lane == 0) RB_TRACE(5u + mb, i, 3u);
         }
       }
     }
@@ -522,6 +569,8 @@ bool rb_map_w(CUtensorMap* m, const void* base, size_t bytes, int box_rows) {
   return fn(m, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, const_cast<void*>(base), gdim, gstr, box, est, CU_TENSOR_MAP_INTERLEAVE_NONE,
             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
+
+long long* g_rb_trace = nullptr;       // device buffer for HFG_TC_TRACE builds (hfgdbg_set_trace)
 
 int rb_env_int(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
 
@@ -596,6 +645,12 @@ cudaError_t rb_launch_t(const RbArgs& a, const RbShape& sh, ActType act, cudaStr
   ka.total_tiles = a.B * ka.tiles_q;
   ka.box_rows = sh.box_rows; ka.nbox = sh.nbox; ka.nsl = sh.nsl; ka.nxt = sh.nxt; ka.lead = sh.lead;
   ka.xt_inv = 1.0f / a.mid_slope;
+  ka.trace = g_rb_trace;
+  // Two issuing warps double the MMA issue rate (-22 % on the k = 11 launches).  With two row blocks per tile AND the running
+  // MRF sum to read (longer fin passes) the conv1 stream runs so far ahead that mid passes queue in front of the fin passes of
+  // the same epilogue groups (+18 % measured), so those launches keep the single issuer.  HFG_RB_ISSUERS=1 / 2 forces one.
+  static const int force_issuers = rb_env_int("HFG_RB_ISSUERS", 0);
+  ka.two_issuers = force_issuers ? (force_issuers == 2) : !(MB == 2 && a.res2 != nullptr);
   ka.mid_slope = a.mid_slope; ka.res_inv = a.res_inv; ka.out_scale = a.out_scale; ka.out_slope = a.out_slope;
   if (!(a.mid_slope > 0.f && a.mid_slope <= 1.f) || !(a.out_slope > 0.f && a.out_slope <= 1.f) || !(a.res_inv >= 1.f)) return cudaErrorInvalidValue;
   const RbPlan pl = rb_plan(MB, CG, sh.nbox * sh.box_rows, sh.span2, a.ntaps1 + a.ntaps2, sh.nsl, sh.nxt, sh.lead);
@@ -642,7 +697,7 @@ cudaError_t rb_launch_t(const RbArgs& a, const RbShape& sh, ActType act, cudaStr
 
 }  // namespace
 
-void rb_set_trace(long long*) {}      // (role tracing lives in the experiment branch of this file; see profiles/r2b_*)
+void rb_set_trace(long long* dev) { g_rb_trace = dev; }
 
 bool rb_supported(const RbArgs& a, int* cg_out) {
   RbShape s;
