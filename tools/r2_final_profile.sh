@@ -1,6 +1,6 @@
 #!/bin/bash
 # final-build evidence: tests, bench lines (r2_full.sh), launch list of one forward and ncu --set full of the 18 fused launches
-bash tools/r2_full.sh
+if [ "${SKIP_FULL:-0}" != "1" ]; then bash tools/r2_full.sh; fi
 python tools/profile_forward.py > gpurun_out/plain_profile.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -s 61 -c 61 --csv --log-file gpurun_out/launches_fwd_b16.csv python tools/profile_forward.py > gpurun_out/ncu_launches.log 2>&1
 echo "launch list rc=$?"
