@@ -339,8 +339,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
               for (int jj = 0; jj < TPS; ++jj) {
                 if (jj >= nj) break;
                 const uint32_t row_off = (uint32_t)(ka.var[v].tap_off[j0 + jj] - ka.min_off);
-                const uint64_t a0 = make_desc_sw<ROWB>(sl + row_off * ROWB + kb * KBW * 2);
-                const uint64_t b0 = make_desc(wb + jj * BLK_BYTES, NB * 16, 128u);
+                // descriptor low words (start address / 16, LBO); the high words are compile-time constants, so that the issuing
+                // thread does 32-bit adds per MMA instead of rebuilding two 64-bit values (its issue cost caps small MMAs)
+                constexpr uint32_t A_HI = ((8u * ROWB) >> 4) | (1u << 14) | ((ROWB == 128 ? 2u : (ROWB == 64 ? 4u : 6u)) << 29);
+                constexpr uint32_t B_HI = (128u >> 4) | (1u << 14);
+                const uint32_t a0 = (uint32_t)make_desc_sw<ROWB>(sl + row_off * ROWB + kb * KBW * 2);
+                const uint32_t b0 = (uint32_t)make_desc(wb + jj * BLK_BYTES, NB * 16, 128u);
                 // K-steps of this tap whose weight rows are all zero (fold slots a shifted tap does not read, padded channels)
                 const uint32_t zero = (ka.var[v].kz[j0 + jj] >> ((s * KS + kb * KBW) / 16)) & ((1u << (KBW / 16)) - 1u);
                 if (zero == (1u << (KBW / 16)) - 1u) continue;
@@ -351,10 +355,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__
                   for (int kk = 0; kk < KBW / 16; ++kk) {
                     if ((zero >> kk) & 1u) continue;
                     // descriptor start-address field counts 16-byte units: advance with plain adds
-                    const uint64_t adesc = a0 + (uint64_t)((mb * 128 * ROWB + kk * 32) >> 4);
-                    const uint64_t bdesc = b0 + (uint64_t)((kk * 2 * NB * 16) >> 4);
-                    if (CG == 2) umma_f16_2cta(tacc + mb * N, adesc, bdesc, IDESC, f ? 0u : 1u);
-                    else umma_f16(tacc + mb * N, adesc, bdesc, IDESC, f ? 0u : 1u);
+                    const uint32_t adesc = a0 + (uint32_t)((mb * 128 * ROWB + kk * 32) >> 4);
+                    const uint32_t bdesc = b0 + (uint32_t)((kk * 2 * NB * 16) >> 4);
+                    if (CG == 2) umma_f16_2cta_lo<A_HI, B_HI>(tacc + mb * N, adesc, bdesc, IDESC, f ? 0u : 1u);
+                    else umma_f16_lo<A_HI, B_HI>(tacc + mb * N, adesc, bdesc, IDESC, f ? 0u : 1u);
                     f = 0;
                   }
                 }

@@ -244,16 +244,19 @@ resblock_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_consta
               uint32_t first = fresh ? 1u : 0u;
 #pragma unroll 1
               for (int j = 0; j < nt; ++j) {
-                const uint64_t a0 = make_desc_sw<kRbRowB>(a_base + (uint32_t)(mb * 128 + offs[j] - mn) * kRbRowB);
-                const uint64_t b0 = make_desc(w_base + j * TAP_BYTES, NB * 16, 128u);
+                // descriptor low words (start address / 16, LBO); the high words are compile-time constants
+                constexpr uint32_t A_HI = ((8u * kRbRowB) >> 4) | (1u << 14) | (2u << 29);   // make_desc_sw<128>: SBO, version, SWIZZLE_128B
+                constexpr uint32_t B_HI = (128u >> 4) | (1u << 14);                          // make_desc(.., sbo = 128)
+                const uint32_t a0 = (uint32_t)make_desc_sw<kRbRowB>(a_base + (uint32_t)(mb * 128 + offs[j] - mn) * kRbRowB);
+                const uint32_t b0 = (uint32_t)make_desc(w_base + j * TAP_BYTES, NB * 16, 128u);
                 const uint32_t zero = kz[j];
 #pragma unroll
                 for (int kk = 0; kk < kRbC / 16; ++kk) {
                   if ((zero >> kk) & 1u) continue;                   // an all-zero 16 x 64 weight block (time folding): nothing to add
-                  const uint64_t adesc = a0 + (uint64_t)((kk * 32) >> 4);
-                  const uint64_t bdesc = b0 + (uint64_t)((kk * 2 * NB * 16) >> 4);
-                  if (CG == 2) umma_f16_2cta(tacc + mb * kRbC, adesc, bdesc, IDESC, first ? 0u : 1u);
-                  else umma_f16(tacc + mb * kRbC, adesc, bdesc, IDESC, first ? 0u : 1u);
+                  const uint32_t adesc = a0 + (uint32_t)((kk * 32) >> 4);
+                  const uint32_t bdesc = b0 + (uint32_t)((kk * 2 * NB * 16) >> 4);
+                  if (CG == 2) umma_f16_2cta_lo<A_HI, B_HI>(tacc + mb * kRbC, adesc, bdesc, IDESC, first ? 0u : 1u);
+                  else umma_f16_lo<A_HI, B_HI>(tacc + mb * kRbC, adesc, bdesc, IDESC, first ? 0u : 1u);
                   first = 0;
                 }
               }

@@ -144,6 +144,20 @@ __device__ __forceinline__ void umma_f16_2cta(uint32_t tmem_d, uint64_t adesc, u
   asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p; }"
                ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// Same MMAs with the descriptors given as 32-bit low words + compile-time high words: the issuing thread then only does
+// 32-bit adds per MMA instead of rebuilding two 64-bit values (its ~60 clocks per MMA cap the small-N kernels).
+template <uint32_t A_HI, uint32_t B_HI>
+__device__ __forceinline__ void umma_f16_lo(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{ .reg .pred p; .reg .b64 da, db; setp.ne.b32 p, %4, 0; mov.b64 da, {%1, %5}; mov.b64 db, {%2, %6};\n"
+               "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p; }"
+               ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(accumulate), "n"(A_HI), "n"(B_HI) : "memory");
+}
+template <uint32_t A_HI, uint32_t B_HI>
+__device__ __forceinline__ void umma_f16_2cta_lo(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{ .reg .pred p; .reg .b64 da, db; setp.ne.b32 p, %4, 0; mov.b64 da, {%1, %5}; mov.b64 db, {%2, %6};\n"
+               "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %3, p; }"
+               ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(accumulate), "n"(A_HI), "n"(B_HI) : "memory");
+}
 // arrives on the barrier at the same smem offset in BOTH CTAs of the pair when the MMAs issued so far retire
 __device__ __forceinline__ void umma_commit_2cta(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
