@@ -28,9 +28,12 @@ constexpr int kTfThreads = 192;
 constexpr int kTfMaxSpan = 96;
 constexpr int kTfNsl = 2, kTfNst = 3;
 
-__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-  asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p; }"
-               ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+// descriptors as 32-bit low words (start address / 16, LBO) + compile-time high words: 32-bit adds per MMA for the issuing thread
+template <uint32_t A_HI, uint32_t B_HI>
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{ .reg .pred p; .reg .b64 da, db; setp.ne.b32 p, %4, 0; mov.b64 da, {%1, %5}; mov.b64 db, {%2, %6};\n"
+               "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %3, p; }"
+               ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(idesc), "r"(accumulate), "n"(A_HI), "n"(B_HI) : "memory");
 }
 __device__ __forceinline__ float round_tf32(float v) {
   uint32_t r; asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v)); return __uint_as_float(r);
@@ -153,11 +156,13 @@ conv_tf32_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
           tc_fence_after();
           if (elect_one()) {
             const uint32_t row_off = (uint32_t)(tf_tap(ka, v, r, j) - ka.min_off);
-            const uint64_t a0 = make_desc_sw<ROWB>(slab_addr + pos * slab_bytes + row_off * ROWB);
-            const uint64_t b0 = make_desc(wst_addr + st * stage_bytes, (uint32_t)n * 16u, 128u);
+            constexpr uint32_t A_HI = ((8u * ROWB) >> 4) | (1u << 14) | ((ROWB == 128 ? 2u : (ROWB == 64 ? 4u : 6u)) << 29);
+            constexpr uint32_t B_HI = (128u >> 4) | (1u << 14);
+            const uint32_t a0 = (uint32_t)make_desc_sw<ROWB>(slab_addr + pos * slab_bytes + row_off * ROWB);
+            const uint32_t b0 = (uint32_t)make_desc(wst_addr + st * stage_bytes, (uint32_t)n * 16u, 128u);
 #pragma unroll
             for (int kk = 0; kk < KS / 8; ++kk) {
-              umma_tf32(tmem_base, a0 + (uint64_t)((kk * 32) >> 4), b0 + (uint64_t)((kk * 2 * n * 16) >> 4), ka.idesc, (first && kk == 0) ? 0u : 1u);
+              umma_tf32<A_HI, B_HI>(tmem_base, a0 + (uint32_t)((kk * 32) >> 4), b0 + (uint32_t)((kk * 2 * n * 16) >> 4), ka.idesc, (first && kk == 0) ? 0u : 1u);
             }
             umma_commit(&w_empty[st]);
             if (j == nt_r - 1) {
