@@ -1,6 +1,7 @@
 // HiFi-GAN discriminator forward passes: MultiPeriodDiscriminator and MultiScaleDiscriminator of the
 // reference (HiFiGAN_TF/model.py:176-243 DiscriminatorP, 246-274 MPD, 277-346 DiscriminatorS, 349-389 MSD) behind the
-// hfg_disc_* C ABI.  fp32 storage and FFMA arithmetic (this row sits beside the hot path; the feature maps feed an L1 loss).
+// hfg_disc_* C ABI.  fp32 storage; convs on the tensor cores at fp32 accuracy (3xTF32, below) with an fp32 FFMA kernel for the
+// first / last conv of each sub-discriminator; hfg_disc_pair_losses reduces the reference's GAN loss terms (losses.py:8-43).
 //
 // Data layout.  Every sub-discriminator works on independent SEQUENCES of channels-last rows [n_seq, len, C]:
 //   DiscriminatorS   n_seq = B, the (pooled) waveform;
