@@ -649,11 +649,11 @@ cudaError_t rb_launch_t(const RbArgs& a, const RbShape& sh, ActType act, cudaStr
   ka.box_rows = sh.box_rows; ka.nbox = sh.nbox; ka.nsl = sh.nsl; ka.nxt = sh.nxt; ka.lead = sh.lead;
   ka.xt_inv = 1.0f / a.mid_slope;
   ka.trace = g_rb_trace;
-  // Two issuing warps double the MMA issue rate (-22 % on the k = 11 launches).  With two row blocks per tile AND the running
-  // MRF sum to read (longer fin passes) the conv1 stream runs so far ahead that mid passes queue in front of the fin passes of
-  // the same epilogue groups (+18 % measured), so those launches keep the single issuer.  HFG_RB_ISSUERS=1 / 2 forces one.
+  // Two issuing warps double the MMA issue rate (-22 % on the k = 11 launches).  Under ncu (cold, serialised) the MB = 2 launches
+  // that also read the running MRF sum looked 18 % slower with two issuers; inside bench.py they are not (V1 equal, V2 +0.6 %,
+  // V3 +2 % with two issuers everywhere), so every launch uses two.  HFG_RB_ISSUERS=1 keeps the single issuer for A/B runs.
   static const int force_issuers = rb_env_int("HFG_RB_ISSUERS", 0);
-  ka.two_issuers = force_issuers ? (force_issuers == 2) : !(MB == 2 && a.res2 != nullptr);
+  ka.two_issuers = force_issuers == 1 ? 0 : 1;
   ka.mid_slope = a.mid_slope; ka.res_inv = a.res_inv; ka.out_scale = a.out_scale; ka.out_slope = a.out_slope;
   if (!(a.mid_slope > 0.f && a.mid_slope <= 1.f) || !(a.out_slope > 0.f && a.out_slope <= 1.f) || !(a.res_inv >= 1.f)) return cudaErrorInvalidValue;
   const RbPlan pl = rb_plan(MB, CG, sh.nbox * sh.box_rows, sh.span2, a.ntaps1 + a.ntaps2, sh.nsl, sh.nxt, sh.lead);
